@@ -1,0 +1,381 @@
+// capi.cu -- the extern "C" surface declared in include/fbg_cuda.h.
+#include "../../include/fbg_cuda.h"
+#include "pipeline.cuh"
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace fbg;
+
+struct fbg_ctx {
+	Pipeline p;
+	std::string err;
+};
+
+static std::string g_create_err;
+
+namespace fbg {
+
+__global__ void rs_widen_kernel(const u32 *__restrict__ c, u64 *__restrict__ o, u64 n) {
+	u64 i = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) o[i] = c[i];
+}
+
+void Pipeline::free_index() {
+	dfree(NG); dfree(IG); dfree(RK); dfree(NIA); dfree(start); dfree(rowlen); dfree(lastcol);
+	dfree(T); dfree(col); dfree(ISA); dfree(SA); dfree(PLCP); dfree(NLCP);
+	dfree(f); dfree(bnd); dfree(dp_a); dfree(dp_b); dfree(dp_v);
+	have_index = have_f = have_seg = false;
+}
+void Pipeline::free_all() {
+	free_index();
+	dfree(msa);
+	have_msa = false;
+}
+
+} // namespace fbg
+
+static const char *KNAMES[K_COUNT] = {"pack", "kmer", "radix_hist", "radix_scatter", "scan", "doubling_aux", "lcp", "fcol", "dp", "graph"};
+
+#define FBG_TRY(ctx) try {
+#define FBG_CATCH(ctx)                                                         \
+	}                                                                          \
+	catch (const fbg::cuda_error &e) { (ctx)->err = e.what(); cudaGetLastError(); return FBG_ERR_CUDA; } \
+	catch (const std::exception &e) { (ctx)->err = e.what(); return FBG_ERR_CUDA; }
+
+static u64 arena_need(const Pipeline &p) {
+	// largest scratch consumer is K1: 2 key + 2 value ping-pong buffers, head words,
+	// four u32 work arrays, the count matrix (see suffix.cu); upper bound on N is m*n+m+1
+	u64 N = p.m * p.n + p.m + 1;
+	u64 ntiles = (N + RS_TILE - 1) / RS_TILE;
+	u64 k1 = N * 72 + ntiles * RS_BINS * 12 + (1u << 20); // K1 uses 52 B/char; K4 up to 64 B per (row,block) record
+	u64 W = p.W, NC = (W + 127) / 128;
+	u64 k0 = NC * p.m * 16 + (1u << 20);
+	return (k1 > k0 ? k1 : k0) + (16u << 20);
+}
+
+extern "C" {
+
+const char *fbg_kernel_name(int idx) { return (idx >= 0 && idx < K_COUNT) ? KNAMES[idx] : ""; }
+
+int fbg_ctx_create(fbg_ctx **out, int device) {
+	if (!out) return FBG_ERR_ARG;
+	*out = nullptr;
+	int count = 0;
+	cudaError_t e = cudaGetDeviceCount(&count);
+	if (e != cudaSuccess || count == 0) {
+		g_create_err = std::string("no CUDA device: ") + cudaGetErrorString(e) + " (this library has no CPU fallback)";
+		cudaGetLastError();
+		return FBG_ERR_CUDA;
+	}
+	if (device < 0) { if (cudaGetDevice(&device) != cudaSuccess) device = 0; }
+	if (device >= count) { g_create_err = "device index out of range"; return FBG_ERR_ARG; }
+	cudaDeviceProp prop;
+	if (cudaGetDeviceProperties(&prop, device) != cudaSuccess || prop.major < 10) {
+		g_create_err = "device is not sm_100 class; this library is built for sm_100a only";
+		cudaGetLastError();
+		return FBG_ERR_CUDA;
+	}
+	fbg_ctx *c = new fbg_ctx();
+	try {
+		FBG_CUDA(cudaSetDevice(device));
+		c->p.dev.device = device;
+		FBG_CUDA(cudaStreamCreateWithFlags(&c->p.dev.stream, cudaStreamNonBlocking));
+	} catch (const std::exception &ex) {
+		g_create_err = ex.what();
+		delete c;
+		return FBG_ERR_CUDA;
+	}
+	*out = c;
+	return FBG_OK;
+}
+
+void fbg_ctx_destroy(fbg_ctx *ctx) {
+	if (!ctx) return;
+	cudaSetDevice(ctx->p.dev.device);
+	cudaStreamSynchronize(ctx->p.dev.stream);
+	ctx->p.free_all();
+	dfree(ctx->p.scalars);
+	if (ctx->p.h_scalars) cudaFreeHost(ctx->p.h_scalars);
+	ctx->p.dev.destroy();
+	if (ctx->p.dev.stream) cudaStreamDestroy(ctx->p.dev.stream);
+	delete ctx;
+}
+
+const char *fbg_last_error(const fbg_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+
+int fbg_set_options(fbg_ctx *ctx, int elastic, int64_t gap_limit, const uint8_t *ignore_chars, size_t n_ignore, int disable_tricks) {
+	if (!ctx) return FBG_ERR_ARG;
+	if (gap_limit < 0) { ctx->err = "Gap limit needs to be non-negative."; return FBG_ERR_ARG; }
+	Options &o = ctx->p.opt;
+	o.elastic = elastic != 0; o.gap_limit = gap_limit; o.disable_tricks = disable_tricks != 0;
+	for (int q = 0; q < 8; q++) o.ignore_bits[q] = 0;
+	o.n_ignore = 0;
+	// ignore characters only take part in the elastic path (fbg.cpp:3393)
+	if (elastic && ignore_chars)
+		for (size_t i = 0; i < n_ignore; i++) { u8 c = ignore_chars[i]; o.ignore_bits[c >> 5] |= 1u << (c & 31); o.n_ignore++; }
+	ctx->p.have_f = ctx->p.have_seg = false;
+	return FBG_OK;
+}
+
+static int upload_common(fbg_ctx *ctx, const void *rows, uint64_t m, uint64_t n, bool device) {
+	if (!ctx || !rows || m == 0 || n == 0) { if (ctx) ctx->err = "empty MSA"; return FBG_ERR_ARG; }
+	if (m >= (1u << 24)) { ctx->err = "more than 2^24 rows"; return FBG_ERR_UNSUPPORTED; }
+	FBG_TRY(ctx)
+	FBG_CUDA(cudaSetDevice(ctx->p.dev.device));
+	if (device) k0_upload_device(ctx->p, (const u8 *) rows, m, n);
+	else k0_upload_host(ctx->p, (const u8 *) rows, m, n);
+	ctx->p.dev.reserve(arena_need(ctx->p));
+	FBG_CATCH(ctx)
+	return FBG_OK;
+}
+int fbg_upload_msa(fbg_ctx *ctx, const uint8_t *rows, uint64_t m, uint64_t n) { return upload_common(ctx, rows, m, n, false); }
+int fbg_upload_msa_device(fbg_ctx *ctx, const void *rows, uint64_t m, uint64_t n) { return upload_common(ctx, rows, m, n, true); }
+
+int fbg_build_index(fbg_ctx *ctx) {
+	if (!ctx || !ctx->p.have_msa) { if (ctx) ctx->err = "no MSA uploaded"; return FBG_ERR_ARG; }
+	FBG_TRY(ctx)
+	Pipeline &p = ctx->p;
+	FBG_CUDA(cudaSetDevice(p.dev.device));
+	if (p.have_index) return FBG_OK;
+	k0_pack(p);
+	k1_suffix_array(p);
+	k1_lcp(p);
+	p.have_index = true;
+	FBG_CATCH(ctx)
+	return FBG_OK;
+}
+
+int fbg_compute_f(fbg_ctx *ctx) {
+	if (!ctx) return FBG_ERR_ARG;
+	int rc = fbg_build_index(ctx);
+	if (rc) return rc;
+	FBG_TRY(ctx)
+	Pipeline &p = ctx->p;
+	if (p.have_f) return FBG_OK;
+	// non-elastic: v[j] is defined through f without the row-end tricks and without
+	// ignore characters (fbg.cpp:552-611 has neither)
+	bool saved = p.opt.disable_tricks;
+	if (!p.opt.elastic) p.opt.disable_tricks = true;
+	k2_compute_f(p);
+	p.opt.disable_tricks = saved;
+	FBG_CATCH(ctx)
+	return FBG_OK;
+}
+
+int fbg_segment(fbg_ctx *ctx, uint64_t *n_blocks, uint64_t *score) {
+	if (!ctx) return FBG_ERR_ARG;
+	int rc = fbg_compute_f(ctx);
+	if (rc) return rc;
+	FBG_TRY(ctx)
+	Pipeline &p = ctx->p;
+	if (!p.have_seg) {
+		if (p.opt.elastic && p.opt.disable_tricks) {
+			// fbg.cpp:1932-1937: f[0] == n -> "No valid segmentation found!"
+			u32 f0 = 0;
+			FBG_CUDA(cudaMemcpyAsync(&f0, p.f, sizeof(u32), cudaMemcpyDeviceToHost, p.dev.stream));
+			FBG_CUDA(cudaStreamSynchronize(p.dev.stream));
+			if (f0 == p.n) { p.seg_status = 1; p.nb = 0; p.score = 0; p.have_seg = true; }
+		}
+		if (!p.have_seg) k3_segment(p);
+	}
+	if (n_blocks) *n_blocks = p.nb;
+	if (score) *score = p.score;
+	if (p.seg_status) { ctx->err = p.opt.elastic || p.opt.gap_limit != 1 ? "No valid segmentation found!" : "No proper segmentation exists."; return FBG_ERR_NOSEG; }
+	FBG_CATCH(ctx)
+	return FBG_OK;
+}
+
+static int copy_u32_as_u64(fbg_ctx *ctx, const u32 *src, u64 count, uint64_t *out) {
+	FBG_TRY(ctx)
+	std::vector<u32> tmp(count);
+	if (count) FBG_CUDA(cudaMemcpyAsync(tmp.data(), src, count * sizeof(u32), cudaMemcpyDeviceToHost, ctx->p.dev.stream));
+	FBG_CUDA(cudaStreamSynchronize(ctx->p.dev.stream));
+	for (u64 i = 0; i < count; i++) out[i] = tmp[i];
+	FBG_CATCH(ctx)
+	return FBG_OK;
+}
+
+int fbg_get_boundaries(fbg_ctx *ctx, uint64_t *out) {
+	if (!ctx || !out || !ctx->p.have_seg || ctx->p.seg_status) { if (ctx) ctx->err = "no segmentation available"; return FBG_ERR_ARG; }
+	return copy_u32_as_u64(ctx, ctx->p.bnd, ctx->p.nb, out);
+}
+
+struct GraphHolder { Graph g; std::vector<u64> dummy; };
+
+int fbg_build_graph(fbg_ctx *ctx, int want_paths, fbg_graph *out) {
+	if (!ctx || !out || !ctx->p.have_seg || ctx->p.seg_status) { if (ctx) ctx->err = "no segmentation available"; return FBG_ERR_ARG; }
+	std::memset(out, 0, sizeof *out);
+	GraphHolder *h = new GraphHolder();
+	try {
+		k4_graph(ctx->p, h->g, want_paths != 0);
+	} catch (const std::exception &e) {
+		ctx->err = e.what(); cudaGetLastError(); delete h; return FBG_ERR_CUDA;
+	}
+	Graph &g = h->g;
+	out->n_blocks = g.heights.size(); out->n_nodes = g.node_block.size(); out->n_edges = g.edge_src.size();
+	out->n_rows = ctx->p.m; out->label_total = g.label_total;
+	u64 mh = 0;
+	for (u64 v : g.heights) mh = v > mh ? v : mh;
+	out->max_height = mh;
+	out->block_height = g.heights.data(); out->node_block = g.node_block.data(); out->node_row = g.node_row.data();
+	out->edge_src = g.edge_src.data(); out->edge_dst = g.edge_dst.data();
+	out->node_of = g.node_of.empty() ? nullptr : g.node_of.data();
+	out->opaque = h;
+	return FBG_OK;
+}
+
+void fbg_graph_free(fbg_graph *g) {
+	if (!g || !g->opaque) return;
+	delete static_cast<GraphHolder *>(g->opaque);
+	std::memset(g, 0, sizeof *g);
+}
+
+static int run_common(fbg_ctx *ctx, const void *rows, uint64_t m, uint64_t n, bool device, int want_paths, uint64_t *n_blocks, uint64_t *score, fbg_graph *out) {
+	int rc = upload_common(ctx, rows, m, n, device);
+	if (rc) return rc;
+	rc = fbg_segment(ctx, n_blocks, score);
+	if (rc) return rc;
+	if (out) rc = fbg_build_graph(ctx, want_paths, out);
+	if (rc) return rc;
+	FBG_TRY(ctx)
+	ctx->p.dev.resolve();
+	FBG_CATCH(ctx)
+	return FBG_OK;
+}
+int fbg_run(fbg_ctx *ctx, const uint8_t *rows, uint64_t m, uint64_t n, int want_paths, uint64_t *n_blocks, uint64_t *score, fbg_graph *out) {
+	return run_common(ctx, rows, m, n, false, want_paths, n_blocks, score, out);
+}
+int fbg_run_device(fbg_ctx *ctx, const void *rows, uint64_t m, uint64_t n, int want_paths, uint64_t *n_blocks, uint64_t *score, fbg_graph *out) {
+	return run_common(ctx, rows, m, n, true, want_paths, n_blocks, score, out);
+}
+
+int fbg_get_stats(fbg_ctx *ctx, fbg_stats *out) {
+	if (!ctx || !out) return FBG_ERR_ARG;
+	FBG_TRY(ctx)
+	Pipeline &p = ctx->p;
+	FBG_CUDA(cudaStreamSynchronize(p.dev.stream));
+	p.dev.resolve();
+	std::memset(out, 0, sizeof *out);
+	out->m = p.m; out->n = p.n; out->text_len = p.N; out->gaps = p.gaps; out->to_ignore = p.toignore;
+	out->sa_rounds = p.sa_rounds; out->arena_peak_bytes = p.dev.arena_peak;
+	for (int k = 0; k < K_COUNT; k++) {
+		out->kernel_ms[k] = p.dev.stats[k].ms; out->kernel_bytes[k] = p.dev.stats[k].bytes; out->kernel_launches[k] = p.dev.stats[k].launches;
+	}
+	FBG_CATCH(ctx)
+	return FBG_OK;
+}
+
+void fbg_reset_stats(fbg_ctx *ctx) {
+	if (!ctx) return;
+	try { cudaStreamSynchronize(ctx->p.dev.stream); ctx->p.dev.resolve(); } catch (...) {}
+	ctx->p.dev.reset_stats();
+}
+
+int fbg_get_f(fbg_ctx *ctx, uint64_t *out) {
+	if (!ctx || !out || !ctx->p.have_f) { if (ctx) ctx->err = "f not computed"; return FBG_ERR_ARG; }
+	return copy_u32_as_u64(ctx, ctx->p.f, ctx->p.n, out);
+}
+int fbg_get_text(fbg_ctx *ctx, uint8_t *out) {
+	if (!ctx || !out || !ctx->p.have_index) { if (ctx) ctx->err = "index not built"; return FBG_ERR_ARG; }
+	FBG_TRY(ctx)
+	FBG_CUDA(cudaMemcpyAsync(out, ctx->p.T, ctx->p.N, cudaMemcpyDeviceToHost, ctx->p.dev.stream));
+	FBG_CUDA(cudaStreamSynchronize(ctx->p.dev.stream));
+	FBG_CATCH(ctx)
+	return FBG_OK;
+}
+int fbg_get_sa(fbg_ctx *ctx, uint64_t *out) {
+	if (!ctx || !out || !ctx->p.have_index) { if (ctx) ctx->err = "index not built"; return FBG_ERR_ARG; }
+	return copy_u32_as_u64(ctx, ctx->p.SA, ctx->p.N, out);
+}
+int fbg_get_isa(fbg_ctx *ctx, uint64_t *out) {
+	if (!ctx || !out || !ctx->p.have_index) { if (ctx) ctx->err = "index not built"; return FBG_ERR_ARG; }
+	return copy_u32_as_u64(ctx, ctx->p.ISA, ctx->p.N, out);
+}
+int fbg_get_lcp(fbg_ctx *ctx, uint64_t *out) {
+	if (!ctx || !out || !ctx->p.have_index) { if (ctx) ctx->err = "index not built"; return FBG_ERR_ARG; }
+	FBG_TRY(ctx)
+	Pipeline &p = ctx->p;
+	std::vector<u32> plcp(p.N), sa(p.N);
+	FBG_CUDA(cudaMemcpyAsync(plcp.data(), p.PLCP, p.N * sizeof(u32), cudaMemcpyDeviceToHost, p.dev.stream));
+	FBG_CUDA(cudaMemcpyAsync(sa.data(), p.SA, p.N * sizeof(u32), cudaMemcpyDeviceToHost, p.dev.stream));
+	FBG_CUDA(cudaStreamSynchronize(p.dev.stream));
+	for (u64 k = 0; k < p.N; k++) out[k] = plcp[sa[k]];
+	FBG_CATCH(ctx)
+	return FBG_OK;
+}
+int fbg_get_dp(fbg_ctx *ctx, uint64_t *a, uint64_t *b, uint64_t *v) {
+	if (!ctx || !ctx->p.have_seg || !ctx->p.dp_a) { if (ctx) ctx->err = "DP not computed"; return FBG_ERR_ARG; }
+	Pipeline &p = ctx->p;
+	u64 cnt = p.opt.elastic ? p.n + 1 : p.n;
+	int rc = FBG_OK;
+	if (a) rc = copy_u32_as_u64(ctx, p.dp_a, cnt, a);
+	if (!rc && b) rc = copy_u32_as_u64(ctx, p.dp_b, cnt, b);
+	if (!rc && v && !p.opt.elastic) rc = copy_u32_as_u64(ctx, p.dp_v, p.n, v);
+	return rc;
+}
+
+int fbg_radix_sort_pairs(fbg_ctx *ctx, uint64_t *keys, uint32_t *vals, uint64_t count, int lo_bit, int hi_bit) {
+	if (!ctx || !keys || !vals || lo_bit < 0 || hi_bit > 64 || hi_bit < lo_bit) return FBG_ERR_ARG;
+	FBG_TRY(ctx)
+	Dev &d = ctx->p.dev;
+	FBG_CUDA(cudaSetDevice(d.device));
+	u64 ntiles = (count + RS_TILE - 1) / RS_TILE;
+	d.reserve(count * 24 + ntiles * RS_BINS * 12 + (8u << 20));
+	u64 mk = d.mark();
+	RadixBuffers rb;
+	rb.k[0] = d.alloc<u64>(count); rb.k[1] = d.alloc<u64>(count);
+	rb.v[0] = d.alloc<u32>(count); rb.v[1] = d.alloc<u32>(count);
+	rb.cur = 0;
+	FBG_CUDA(cudaMemcpyAsync(rb.k[0], keys, count * 8, cudaMemcpyHostToDevice, d.stream));
+	FBG_CUDA(cudaMemcpyAsync(rb.v[0], vals, count * 4, cudaMemcpyHostToDevice, d.stream));
+	int cur = radix_sort<u64, true>(d, rb, count, lo_bit, hi_bit);
+	FBG_CUDA(cudaMemcpyAsync(keys, rb.k[cur], count * 8, cudaMemcpyDeviceToHost, d.stream));
+	FBG_CUDA(cudaMemcpyAsync(vals, rb.v[cur], count * 4, cudaMemcpyDeviceToHost, d.stream));
+	FBG_CUDA(cudaStreamSynchronize(d.stream));
+	d.release(mk);
+	FBG_CATCH(ctx)
+	return FBG_OK;
+}
+
+__global__ void bench_fill_kernel(u64 *k, u32 *v, u64 n, u64 seed) {
+	u64 i = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	u64 z = (i + seed) * 0x9E3779B97F4A7C15ull;
+	z ^= z >> 30; z *= 0xBF58476D1CE4E5B9ull; z ^= z >> 27; z *= 0x94D049BB133111EBull; z ^= z >> 31;
+	k[i] = z; v[i] = (u32) i;
+}
+
+int fbg_radix_sort_bench(fbg_ctx *ctx, uint64_t count, int lo_bit, int hi_bit, int reps, double *ms_per_sort) {
+	if (!ctx || !ms_per_sort || reps < 1) return FBG_ERR_ARG;
+	FBG_TRY(ctx)
+	Dev &d = ctx->p.dev;
+	FBG_CUDA(cudaSetDevice(d.device));
+	u64 ntiles = (count + RS_TILE - 1) / RS_TILE;
+	d.reserve(count * 24 + ntiles * RS_BINS * 12 + (8u << 20));
+	u64 mk = d.mark();
+	RadixBuffers rb;
+	rb.k[0] = d.alloc<u64>(count); rb.k[1] = d.alloc<u64>(count);
+	rb.v[0] = d.alloc<u32>(count); rb.v[1] = d.alloc<u32>(count);
+	cudaEvent_t a, b;
+	FBG_CUDA(cudaEventCreate(&a)); FBG_CUDA(cudaEventCreate(&b));
+	double total = 0;
+	for (int r = 0; r < reps + 1; r++) {
+		rb.cur = 0;
+		bench_fill_kernel<<<div_up(count, 256), 256, 0, d.stream>>>((u64 *) rb.k[0], rb.v[0], count, (u64) r * 7919);
+		FBG_CUDA(cudaEventRecord(a, d.stream));
+		radix_sort<u64, true>(d, rb, count, lo_bit, hi_bit);
+		FBG_CUDA(cudaEventRecord(b, d.stream));
+		FBG_CUDA(cudaStreamSynchronize(d.stream));
+		float ms;
+		FBG_CUDA(cudaEventElapsedTime(&ms, a, b));
+		if (r > 0) total += ms; // first repetition is the warm-up
+	}
+	cudaEventDestroy(a); cudaEventDestroy(b);
+	*ms_per_sort = total / reps;
+	d.release(mk);
+	FBG_CATCH(ctx)
+	return FBG_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,253 @@
+// segdp.cu -- K3: segmentation DP + backtrack.
+//
+// Elastic (fbg.cpp:1940-2039): the reference sweeps j = 1..n with arrival /
+// expiry lists; its result has the closed form
+//   V_j = {x < j : f[x]+1 <= j, mml[x] <= n},  A = {x in V_j : j-x <= mml[x]},  B = V_j \ A
+//   I* = min_{A} mml[x],  S* = j - max B
+//   A != {} and (B = {} or I* < S*):  mml[j] = I*, backtrack[j] = max{x in A : mml[x] = I*}
+//   else                              mml[j] = S*, backtrack[j] = max B
+// Every candidate at distance d = j-x has value >= d, so a downward scan from
+// u(j) = max{x : f[x]+1 <= j} that stops once d exceeds the best value seen is
+// exact, including the tie rules.  u(j) comes from a scatter-max + prefix-max
+// scan.  The recurrence is a chain, so one warp advances a wavefront: lanes whose
+// candidates are all final (u(j) < frontier) evaluate their column concurrently.
+//
+// Non-elastic: v[j] (fbg.cpp:552-611) = max{jp : f_notricks(jp) <= j} through a
+// counting scan when f is monotone (always, for gapless rows), else the
+// reference's one-directional two-pointer; s/prev DP of fbg.cpp:622-643 as the
+// same wavefront; greedy recurrence of fbg.cpp:827-846 for gap_limit != 1.
+#include "pipeline.cuh"
+
+namespace fbg {
+
+__device__ __forceinline__ u32 ld_vol(const u32 *p) { return *reinterpret_cast<const volatile u32 *>(p); }
+
+// ---------------------------------------------------------------- elastic
+__global__ void k3_scatter_u_kernel(const u32 *__restrict__ f, u64 n, u32 *__restrict__ U) {
+	u64 x = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (x >= n) return;
+	u64 e = (u64) f[x] + 1;
+	if (e <= n) atomicMax(&U[e], (u32) x + 1);
+}
+
+// single warp. mml/bt have n+1 entries. out[0] = nb, out[1] = mml[n]
+__global__ void __launch_bounds__(32) k3_elastic_dp_kernel(const u32 *__restrict__ f, const u32 *__restrict__ U, u64 n, u32 *mml, u32 *bt, u32 *rev, u32 *bnd, u64 *out) {
+	const u32 l = lane_id();
+	const u32 INV = (u32) n + 1;
+	if (l == 0) { mml[0] = 0; bt[0] = 0; }
+	__syncwarp();
+	u64 F = 1;
+	while (F <= n) {
+		u64 j = F + l;
+		u32 uj = j <= n ? U[j] : 0;
+		bool ready = j <= n && (uj == 0 || (u64) uj - 1 < F);
+		u32 rb = __ballot_sync(0xffffffffu, ready);
+		u32 r = rb == 0xffffffffu ? 32u : (u32) (__ffs(~rb) - 1);
+		if (l < r) {
+			u32 best = U32_MAX, bx = U32_MAX;
+			if (uj) {
+				u64 x = (u64) uj - 1;
+				for (;;) {
+					u64 dd = j - x;
+					if (dd > best) break;
+					u64 ex = (u64) f[x] + 1;
+					u32 mx = ld_vol(&mml[x]);
+					if (ex <= j && mx <= (u32) n) {
+						if (dd > mx) { best = (u32) dd; bx = (u32) x; break; }      // B candidate, ties go to B
+						else if (mx < best) { best = mx; bx = (u32) x; }            // A candidate, largest x wins ties
+					}
+					if (x == 0) break;
+					x--;
+				}
+			}
+			if (bx == U32_MAX) { mml[j] = INV; bt[j] = U32_MAX; }
+			else { mml[j] = best; bt[j] = bx; }
+		}
+		__threadfence_block();
+		__syncwarp();
+		F += r;
+	}
+	// backtrack, fbg.cpp:2026-2039
+	if (l == 0) {
+		u64 nb = 0, j = n;
+		rev[nb++] = (u32) n;
+		while (true) {
+			u32 b = ld_vol(&bt[j]);
+			if (b == 0 || b == U32_MAX) break;
+			rev[nb++] = b - 1;
+			j = b;
+		}
+		for (u64 a = 0; a < nb; a++) bnd[a] = rev[nb - 1 - a];
+		out[0] = nb; out[1] = ld_vol(&mml[n]);
+	}
+}
+
+// ------------------------------------------------------------ non-elastic
+__global__ void k3_monotone_kernel(const u32 *__restrict__ f, u64 n, u32 *__restrict__ nonmono, u32 *__restrict__ cnt) {
+	u64 x = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (x >= n) return;
+	u32 fx = f[x];
+	if (x + 1 < n && f[x + 1] < fx) *nonmono = 1;
+	atomicAdd(&cnt[fx < (u32) n ? fx : (u32) n], 1u);
+}
+
+// C = inclusive counts; v[j] = C[j]-1 or j+1
+__global__ void k3_v_from_counts_kernel(const u32 *__restrict__ C, u64 n, u32 *__restrict__ v) {
+	u64 j = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (j < n) v[j] = C[j] ? C[j] - 1 : (u32) j + 1;
+}
+
+// reference two-pointer (only when f is not monotone, i.e. gapped rows)
+__global__ void k3_v_sequential_kernel(const u32 *__restrict__ f, u64 n, const u32 *__restrict__ nonmono, u32 *__restrict__ v) {
+	if (blockIdx.x || threadIdx.x || !*nonmono) return;
+	u64 jp = n;
+	for (u64 j = n; j-- > 0;) {
+		u32 vj = (u32) j + 1;
+		for (;;) {
+			if (jp < n && f[jp] <= j) { vj = (u32) jp; break; }
+			if (jp == 0) break;
+			jp--;
+		}
+		v[j] = vj;
+	}
+}
+
+// single warp wavefront over fbg.cpp:622-643; out[0]=nb, out[1]=s[n-1], out[2]=status
+__global__ void __launch_bounds__(32) k3_nonelastic_dp_kernel(const u32 *__restrict__ v, u64 n, u32 *s, u32 *prev, u32 *rev, u32 *bnd, u64 *out) {
+	const u32 l = lane_id();
+	u64 F = 0;
+	while (F < n) {
+		u64 j = F + l;
+		u32 vj = j < n ? v[j] : 0;
+		bool ready = j < n && (vj > j || vj <= F);
+		u32 rb = __ballot_sync(0xffffffffu, ready);
+		u32 r = rb == 0xffffffffu ? 32u : (u32) (__ffs(~rb) - 1);
+		if (l < r) {
+			u32 sj = (u32) j + 2, pj = (u32) j + 1;
+			if (vj <= j) {
+				u64 jp = vj;
+				for (;;) {
+					u32 sp = jp ? ld_vol(&s[jp - 1]) : 0u;
+					if (jp != 0 && sp == (u32) jp + 1) { jp--; continue; }
+					u32 len = (u32) (j - jp + 1);
+					u32 cand = sp > len ? sp : len;
+					if (sj > cand) { sj = cand; pj = (u32) jp; }
+					if (sj == len) break;
+					if (jp == 0) break;
+					jp--;
+				}
+			}
+			s[j] = sj; prev[j] = pj;
+		}
+		__threadfence_block();
+		__syncwarp();
+		F += r;
+	}
+	if (l == 0) {
+		u32 sc = ld_vol(&s[n - 1]);
+		out[1] = sc;
+		if (sc == (u32) n + 1) { out[0] = 0; out[2] = 1; return; }
+		u64 nb = 0, j = n - 1;
+		rev[nb++] = (u32) j;
+		for (;;) {
+			u32 pv = ld_vol(&prev[j]);
+			if (pv == 0) break;
+			rev[nb++] = pv - 1;
+			j = pv - 1;
+		}
+		for (u64 a = 0; a < nb; a++) bnd[a] = rev[nb - 1 - a];
+		out[0] = nb; out[2] = 0;
+	}
+}
+
+// fbg.cpp:827-865 (greedy, not optimal by design); sequential by construction
+__global__ void k3_greedy_dp_kernel(const u32 *__restrict__ v, u64 n, u32 *s, u32 *prev, u32 *rev, u32 *bnd, u64 *out) {
+	if (blockIdx.x || threadIdx.x) return;
+	const u64 INV = n + 1;
+	// size_t arithmetic of the reference, including its wrap-around on prev = n+1
+	u64 sp = INV, pp = INV; // s[j-1], prev[j-1]
+	s[0] = (u32) INV; prev[0] = (u32) INV;
+	for (u64 j = 1; j < n; j++) {
+		u64 jp = v[j];
+		u64 sj = INV, pj = INV;
+		if (jp > j) {
+			// keep defaults
+		} else if (jp == 0) {
+			sj = j + 1; pj = 0;
+		} else {
+			u64 a0 = s[jp - 1], a1 = j - jp + 1;
+			u64 a = a0 > a1 ? a0 : a1;
+			u64 b1 = j - pp + 1; // wraps like size_t when pp = n+1
+			u64 b = sp > b1 ? sp : b1;
+			if (a < b) { sj = a; pj = jp; }
+			else { sj = b; pj = pp; }
+		}
+		// the reference stores size_t; values above 2^32 only arise from the wrap and
+		// behave as "huge" in later comparisons: clamp to U32_MAX-1 keeps that order
+		s[j] = sj > 0xFFFFFFFEull ? 0xFFFFFFFEu : (u32) sj;
+		prev[j] = (u32) pj;
+		sp = sj; pp = pj;
+	}
+	u64 sc = n == 1 ? INV : sp;
+	out[1] = sc;
+	if (sc == INV) { out[0] = 0; out[2] = 1; return; }
+	u64 nb = 0, j = n - 1;
+	rev[nb++] = (u32) j;
+	while (prev[j] != 0) { rev[nb++] = prev[j] - 1; j = prev[j] - 1; }
+	for (u64 a = 0; a < nb; a++) bnd[a] = rev[nb - 1 - a];
+	out[0] = nb; out[2] = 0;
+}
+
+void k3_segment(Pipeline &p) {
+	Dev &d = p.dev;
+	const u64 n = p.n;
+	if (!p.bnd) p.bnd = dmalloc<u32>(n + 2);
+	if (!p.dp_a) { p.dp_a = dmalloc<u32>(n + 2); p.dp_b = dmalloc<u32>(n + 2); p.dp_v = dmalloc<u32>(n + 2); }
+	u64 mk = d.mark();
+	u32 *rev = d.alloc<u32>(n + 2);
+	u64 *out = p.scalars + 16;
+	FBG_CUDA(cudaMemsetAsync(out, 0, 4 * sizeof(u64), d.stream));
+	u32 g = div_up(n, 256);
+	if (p.opt.elastic) {
+		u32 *U = d.alloc<u32>(n + 2);
+		FBG_CUDA(cudaMemsetAsync(U, 0, (n + 2) * sizeof(u32), d.stream));
+		d.begin(K_DP);
+		k3_scatter_u_kernel<<<g, 256, 0, d.stream>>>(p.f, n, U);
+		FBG_LAUNCH_CHECK();
+		d.end((double) n * 8.0);
+		device_scan<OpMaxU32, false>(d, U, U, n + 1);
+		d.begin(K_DP);
+		k3_elastic_dp_kernel<<<1, 32, 0, d.stream>>>(p.f, U, n, p.dp_a, p.dp_b, rev, p.bnd, out);
+		FBG_LAUNCH_CHECK();
+		d.end((double) n * 24.0);
+	} else {
+		u32 *cnt = d.alloc<u32>(n + 2);
+		u32 *nonmono = reinterpret_cast<u32 *>(p.scalars + 24);
+		FBG_CUDA(cudaMemsetAsync(cnt, 0, (n + 2) * sizeof(u32), d.stream));
+		FBG_CUDA(cudaMemsetAsync(nonmono, 0, sizeof(u64), d.stream));
+		d.begin(K_DP);
+		k3_monotone_kernel<<<g, 256, 0, d.stream>>>(p.f, n, nonmono, cnt);
+		FBG_LAUNCH_CHECK();
+		d.end((double) n * 12.0);
+		device_scan<OpSumU32, false>(d, cnt, cnt, n + 1);
+		d.begin(K_DP);
+		k3_v_from_counts_kernel<<<g, 256, 0, d.stream>>>(cnt, n, p.dp_v);
+		k3_v_sequential_kernel<<<1, 32, 0, d.stream>>>(p.f, n, nonmono, p.dp_v);
+		if (p.opt.gap_limit == 1)
+			k3_nonelastic_dp_kernel<<<1, 32, 0, d.stream>>>(p.dp_v, n, p.dp_a, p.dp_b, rev, p.bnd, out);
+		else
+			k3_greedy_dp_kernel<<<1, 32, 0, d.stream>>>(p.dp_v, n, p.dp_a, p.dp_b, rev, p.bnd, out);
+		FBG_LAUNCH_CHECK();
+		d.end((double) n * 24.0);
+		d.note_launches(K_DP, 2);
+	}
+	FBG_CUDA(cudaMemcpyAsync(p.h_scalars + 16, out, 4 * sizeof(u64), cudaMemcpyDeviceToHost, d.stream));
+	FBG_CUDA(cudaStreamSynchronize(d.stream));
+	p.nb = p.h_scalars[16];
+	p.score = p.h_scalars[17];
+	p.seg_status = (int) p.h_scalars[18];
+	p.have_seg = true;
+	d.release(mk);
+}
+
+} // namespace fbg

@@ -1,0 +1,134 @@
+/* fbg_cuda.h -- C ABI of libfbg_cuda.so: the B200 (sm_100a) implementation of the
+ * founderblockgraphs hot path (semi-repeat-free segmentation + founder-block
+ * construction).
+ *
+ * The reference (algbio/founderblockgraphs @5c852c2) has no FFI of its own: the
+ * whole path lives in one anonymous namespace of founderblockgraph.cpp ("fbg.cpp")
+ * behind the `founderblockgraph` executable.  Each entry point
+ * below therefore replaces the call main() makes at the cited line; the new host
+ * executable (csrc/host/cli.cpp, same flags) and any other binding (ctypes, cgo,
+ * JNI) call exactly these.  See INTEGRATION.md for the reference-side stub.
+ *
+ * Conventions: plain pointers and sizes, caller-owned host buffers unless stated,
+ * no exceptions across the boundary, int status (0 = FBG_OK, < 0 = error with text
+ * in fbg_last_error()).  One context per host thread; calls on one context are
+ * serialised by the caller.  There is NO CPU fallback: every compute entry point
+ * fails with FBG_ERR_CUDA when no sm_100 device is usable.
+ */
+#ifndef FBG_CUDA_H
+#define FBG_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FBG_OK 0
+#define FBG_ERR_CUDA (-1)       /* CUDA runtime / device failure */
+#define FBG_ERR_ARG (-2)        /* bad argument or call order */
+#define FBG_ERR_NOSEG (-3)      /* "No proper segmentation exists." / "No valid segmentation found!" */
+#define FBG_ERR_UNSUPPORTED (-4)
+
+#define FBG_NO_NODE UINT32_MAX  /* node_of[] entry of a row whose label in that block is empty */
+
+typedef struct fbg_ctx fbg_ctx;
+
+/* Result of fbg_build_graph; arrays are owned by the library until fbg_graph_free. */
+typedef struct fbg_graph {
+	uint64_t n_blocks, n_nodes, n_edges, n_rows;
+	uint64_t label_total;        /* "total length of node labels=" (fbg.cpp:695) */
+	uint64_t max_height;         /* "#founders=" (fbg.cpp:701) */
+	const uint64_t *block_height;/* [n_blocks] distinct non-empty labels: the B line (fbg.cpp:1210-1220) */
+	const uint64_t *node_block;  /* [n_nodes] */
+	const uint64_t *node_row;    /* [n_nodes] first-occurrence row; the host slices the label from its MSA copy */
+	const uint64_t *edge_src;    /* [n_edges] grouped by destination block, ascending (src,dst) inside (fbg.cpp:1253) */
+	const uint64_t *edge_dst;
+	const uint32_t *node_of;     /* [n_blocks][n_rows] or NULL; FBG_NO_NODE = empty label (P lines, fbg.cpp:1263-1300) */
+	void *opaque;
+} fbg_graph;
+
+/* Per-kernel accounting for the roofline: accumulated CUDA-event milliseconds,
+ * algorithmic bytes (DESIGN.md states the per-unit figures) and launch counts. */
+#define FBG_N_KERNELS 10
+typedef struct fbg_stats {
+	uint64_t m, n, text_len;      /* N = non-gap cells + m + 1 */
+	uint64_t gaps, to_ignore;     /* fbg.cpp:1858-1859 */
+	uint64_t sa_rounds;           /* prefix-doubling rounds incl. the k-mer round */
+	uint64_t arena_peak_bytes;
+	double kernel_ms[FBG_N_KERNELS];
+	double kernel_bytes[FBG_N_KERNELS];
+	uint64_t kernel_launches[FBG_N_KERNELS];
+} fbg_stats;
+
+/* index -> name for the arrays above ("pack", "kmer", "radix_hist", ...) */
+const char *fbg_kernel_name(int idx);
+
+/* device < 0: current device. */
+int fbg_ctx_create(fbg_ctx **out, int device);
+void fbg_ctx_destroy(fbg_ctx *ctx);
+const char *fbg_last_error(const fbg_ctx *ctx);  /* ctx may be NULL: error of the last failed fbg_ctx_create */
+
+/* Mode flags exactly as main() reads them (fbg.cpp:3308-3340): --elastic,
+ * --gap-limit, --ignore-chars, --disable-elastic-tricks. */
+int fbg_set_options(fbg_ctx *ctx, int elastic, int64_t gap_limit, const uint8_t *ignore_chars, size_t n_ignore, int disable_tricks);
+
+/* Rows already filtered by the host (read_input, fbg.cpp:151-201), row-major m x n
+ * ASCII bytes, '-' = gap.  Host buffer (pinned recommended); copied before return
+ * of the next synchronising call.  Replaces what load_cst consumes (fbg.cpp:361). */
+int fbg_upload_msa(fbg_ctx *ctx, const uint8_t *rows_rowmajor, uint64_t m, uint64_t n);
+/* Same, from a device buffer on the context's device (inputs resident in HBM). */
+int fbg_upload_msa_device(fbg_ctx *ctx, const void *device_rows_rowmajor, uint64_t m, uint64_t n);
+
+/* K0+K1: text, suffix array, inverse, LCP. Replaces load_cst -> sdsl::construct (fbg.cpp:3378, 428). */
+int fbg_build_index(fbg_ctx *ctx);
+/* K2: f(x). Replaces compute_f / compute_f_range (fbg.cpp:1923, 2278-2289); in non-elastic
+ * mode computes f with tricks disabled, the quantity v[j] is derived from (fbg.cpp:552-611). */
+int fbg_compute_f(fbg_ctx *ctx);
+/* K3: DP + backtrack. Replaces fbg.cpp:1940-2039 (elastic), 622-663 (gap_limit == 1),
+ * 827-865 (otherwise).  Runs the earlier stages if needed.  *score = mml[n] ("optimal
+ * segment length") or s[n-1] ("Optimal score").  FBG_ERR_NOSEG when the reference would
+ * print its no-segmentation message and exit 1. */
+int fbg_segment(fbg_ctx *ctx, uint64_t *n_blocks, uint64_t *score);
+/* out[n_blocks]: inclusive 0-based end column of every block; elastic mode keeps the
+ * reference's quirk that the last element is n (fbg.cpp:2026-2039). */
+int fbg_get_boundaries(fbg_ctx *ctx, uint64_t *out);
+/* K4: nodes + edges (fbg.cpp:1222-1260 / 666-728). want_paths != 0 also fills node_of. */
+int fbg_build_graph(fbg_ctx *ctx, int want_paths, fbg_graph *out);
+void fbg_graph_free(fbg_graph *g);
+
+/* Whole path in one call: upload (host buffer) -> index -> f -> DP -> graph. */
+int fbg_run(fbg_ctx *ctx, const uint8_t *rows_rowmajor, uint64_t m, uint64_t n, int want_paths,
+            uint64_t *n_blocks, uint64_t *score, fbg_graph *out);
+/* Same with the MSA already resident in device memory. */
+int fbg_run_device(fbg_ctx *ctx, const void *device_rows, uint64_t m, uint64_t n, int want_paths,
+                   uint64_t *n_blocks, uint64_t *score, fbg_graph *out);
+
+int fbg_get_stats(fbg_ctx *ctx, fbg_stats *out);
+void fbg_reset_stats(fbg_ctx *ctx);
+
+/* Parity / debug read-backs (host buffers sized by the caller). */
+int fbg_get_f(fbg_ctx *ctx, uint64_t *out /* n */);
+int fbg_get_text(fbg_ctx *ctx, uint8_t *out /* text_len */);
+int fbg_get_sa(fbg_ctx *ctx, uint64_t *out /* text_len */);
+int fbg_get_isa(fbg_ctx *ctx, uint64_t *out /* text_len */);
+int fbg_get_lcp(fbg_ctx *ctx, uint64_t *out /* text_len, SA order: LCP[k] */);
+int fbg_get_dp(fbg_ctx *ctx, uint64_t *a /* mml[n+1] or s[n] */, uint64_t *b /* backtrack[n+1] or prev[n] */, uint64_t *v /* n, non-elastic only, may be NULL */);
+
+/* Standalone primitive, exported for the parity tests of the radix passes:
+ * stable LSD sort of (key,value) pairs on bits [lo_bit,hi_bit). Host buffers. */
+int fbg_radix_sort_pairs(fbg_ctx *ctx, uint64_t *keys, uint32_t *vals, uint64_t count, int lo_bit, int hi_bit);
+/* Device-resident variant used by bench.py to time one radix pass set in isolation:
+ * sorts `count` pseudo-random 64-bit keys generated on the device; returns elapsed ms. */
+int fbg_radix_sort_bench(fbg_ctx *ctx, uint64_t count, int lo_bit, int hi_bit, int reps, double *ms_per_sort);
+
+/* Host-side xGFA formatting, byte-identical to output_efg (fbg.cpp:1185-1301).
+ * msa = the same filtered row-major rows; ids = m header strings (used when output_paths). */
+int fbg_write_xgfa(const char *path, const uint8_t *rows_rowmajor, uint64_t m, uint64_t n,
+                   const uint64_t *boundaries, const fbg_graph *g, int output_paths, const char *const *ids);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FBG_CUDA_H */

@@ -1,0 +1,291 @@
+"""GPU (-m gpu): the CUDA path, called through the C ABI, against
+  * the golden vectors generated from the reference binary (tests/golden/cases.json),
+  * the CPU oracle (oracle/fbg_oracle.c) on seeded inputs,
+  * size-independent properties at larger sizes.
+Integer work throughout: every comparison is bit-exact."""
+import os
+
+import numpy as np
+import pytest
+
+import founderblockgraphs_b200 as pkg
+from founderblockgraphs_b200 import synth
+from oracle import oracle as O
+from util import FIXTURES, case_id, elastic_cases, flags_to_opts, nonelastic_cases, stat_lines
+
+pytestmark = pytest.mark.gpu
+
+
+# ------------------------------------------------------------------ radix passes
+@pytest.mark.parametrize("count", [0, 1, 2, 31, 4095, 4096, 4097, 100_003, 1_000_000])
+@pytest.mark.parametrize("bits", [(0, 64), (0, 50), (5, 29), (0, 8), (32, 57)])
+def test_radix_sort_pairs_stable(gpu_ctx, count, bits):
+    rng = np.random.default_rng(count + bits[1])
+    keys = rng.integers(0, 2**63, size=count, dtype=np.uint64) * np.uint64(2) + rng.integers(0, 2, size=count, dtype=np.uint64)
+    if count > 10:
+        keys[: count // 3] &= np.uint64(0xFF00FF)  # many duplicates: stability matters
+    vals = np.arange(count, dtype=np.uint32)
+    k2, v2 = gpu_ctx.radix_sort_pairs(keys, vals, bits[0], bits[1])
+    lo, hi = bits
+    mask = np.uint64((1 << (hi - lo)) - 1) if hi - lo < 64 else np.uint64(0xFFFFFFFFFFFFFFFF)
+    field = (keys >> np.uint64(lo)) & mask
+    order = np.argsort(field, kind="stable")
+    assert np.array_equal(v2, vals[order])
+    assert np.array_equal(k2, keys[order])
+
+
+# ---------------------------------------------------------------- SA / ISA / LCP
+def _check_index(ctx, msa):
+    ctx.set_options(elastic=True)
+    ctx.upload(msa)
+    ctx.build_index()
+    T, start, rowlen, colof = O.text(msa)
+    assert np.array_equal(ctx.text(), T)
+    SA, ISA, LCP = O.sa_lcp(T)
+    assert np.array_equal(ctx.sa(), SA.astype(np.uint64))
+    assert np.array_equal(ctx.isa(), ISA.astype(np.uint64))
+    assert np.array_equal(ctx.lcp(), LCP.astype(np.uint64))
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_suffix_array_lcp_small_random(gpu_ctx, seed):
+    rng = np.random.default_rng(seed)
+    m, n = int(rng.integers(1, 12)), int(rng.integers(1, 300))
+    msa = synth.random_small_msa(rng, m, n, gap_p=float(rng.choice([0, 0.2])), n_p=float(rng.choice([0, 0.05])),
+                                 alphabet=bytes(rng.choice([b"A", b"AC", b"ACGT", b"ACGTRYKMSWacgt"])))
+    _check_index(gpu_ctx, msa)
+
+
+def test_suffix_array_lcp_degenerate(gpu_ctx):
+    # identical rows (LCP ~ n, crossing '#'), a single symbol, all-gap rows, one column
+    _check_index(gpu_ctx, np.tile(np.frombuffer(b"ACGTTGCAAC" * 30, np.uint8), (7, 1)))
+    _check_index(gpu_ctx, np.full((3, 500), ord("A"), np.uint8))
+    a = np.full((4, 40), ord("-"), np.uint8)
+    a[1, 5:9] = np.frombuffer(b"ACGT", np.uint8)
+    _check_index(gpu_ctx, a)
+    _check_index(gpu_ctx, np.frombuffer(b"ACAG", np.uint8).reshape(4, 1).copy())
+    _check_index(gpu_ctx, np.frombuffer(b"A", np.uint8).reshape(1, 1).copy())
+
+
+def test_suffix_array_lcp_msa_like(gpu_ctx):
+    _check_index(gpu_ctx, synth.make_msa(60, 5000, snp=0.002, gap_div=500, seed=11))
+
+
+# ----------------------------------------------------------------- golden (reference)
+@pytest.mark.parametrize("case", elastic_cases(), ids=case_id)
+def test_elastic_golden(gpu_ctx, case, tmp_path):
+    o = flags_to_opts(case["flags"])
+    msa, ids = pkg.read_input(os.path.join(FIXTURES, case["fixture"]), 1, True, o["paths"])
+    ctx = gpu_ctx
+    ctx.set_options(elastic=True, ignore_chars=o["ignore"], disable_tricks=o["tricks_off"])
+    ctx.upload(msa)
+    f = ctx.compute_f()
+    st = stat_lines(case)
+    s = ctx.stats()
+    assert s["gaps"] == st["gaps"] and s["to_ignore"] == st["toignore"]
+    if "f" in case:
+        assert f.tolist() == case["f"]
+    if case["exit"] != 0:
+        with pytest.raises(pkg.NoSegmentation):
+            ctx.segment()
+        return
+    b, score = ctx.segment()
+    assert score == st["L"]
+    if "boundaries" in case:
+        n = msa.shape[1]
+        assert b.tolist() == case["boundaries"]
+        mml, bt = ctx.dp(True)
+        ok = np.array(case["mml"]) <= n
+        assert mml[ok].tolist() == np.array(case["mml"])[ok].tolist()
+        assert bt[ok].tolist() == np.array(case["backtrack"])[ok].tolist()
+    out = str(tmp_path / "o.xgfa")
+    pkg.output_efg(b, msa, o["paths"], ids, out, ctx)
+    assert open(out, "rb").read() == case["xgfa"]
+
+
+@pytest.mark.parametrize("case", nonelastic_cases(), ids=case_id)
+def test_nonelastic_golden(gpu_ctx, case):
+    gl = int(case["flags"][0].split("=")[1])
+    msa, _ = pkg.read_input(os.path.join(FIXTURES, case["fixture"]), gl, False)
+    if msa.size == 0:
+        assert case["exit"] == 1
+        return
+    ctx = gpu_ctx
+    ctx.set_options(elastic=False, gap_limit=gl)
+    ctx.upload(msa)
+    st = stat_lines(case)
+    if case["harness_status"] == 1:
+        with pytest.raises(pkg.NoSegmentation):
+            ctx.segment()
+        assert ctx.score == st["Optimal score: "]
+        return
+    b, score = ctx.segment()
+    assert score == st["Optimal score: "]
+    s, prev, v = ctx.dp(False)
+    assert v.tolist() == case["v"] and b.tolist() == case["boundaries"]
+    assert s.tolist() == case["s"] and prev.tolist() == case["prev"]
+    g = ctx.build_graph()
+    assert len(b) == st["Number of segments: "] and g.n_nodes == st["#nodes="]
+    assert g.label_total == st["total length of node labels="] and g.max_height == st["#founders="] and g.n_edges == st["#edges="]
+
+
+def test_cli_end_to_end_golden(tmp_path):
+    """The drop-in executable, byte for byte, on the reference's own fixtures."""
+    for case in elastic_cases():
+        if case["exit"] != 0:
+            continue
+        out = str(tmp_path / "o.xgfa")
+        if os.path.exists(out):
+            os.remove(out)
+        pr = pkg.main(["--input", os.path.join(FIXTURES, case["fixture"]), "--output", out] + case["flags"], capture_output=True)
+        assert pr.returncode == 0, pr.stderr.decode()
+        assert open(out, "rb").read() == case["xgfa"], case_id(case)
+        err = pr.stderr.decode().splitlines()
+        for l in case["stderr"]:
+            assert l in err, (l, err)
+
+
+# ------------------------------------------------------------------ oracle, seeded
+def _check_elastic(ctx, msa, ignore=b"", tricks_off=False, tmp=None):
+    ctx.set_options(elastic=True, ignore_chars=ignore, disable_tricks=tricks_off)
+    ctx.upload(msa)
+    f = ctx.compute_f()
+    f_ref = O.compute_f(msa, ignore, tricks_off)
+    assert np.array_equal(f, f_ref)
+    n = msa.shape[1]
+    if tricks_off and f_ref[0] == n:
+        with pytest.raises(pkg.NoSegmentation):
+            ctx.segment()
+        return
+    b, score = ctx.segment()
+    mml_ref, bt_ref, b_ref = O.dp_elastic(f_ref)
+    mml, bt = ctx.dp(True)
+    ok = mml_ref <= n
+    assert np.array_equal(mml[ok], mml_ref[ok]) and np.array_equal(bt[ok], bt_ref[ok])
+    assert np.all(mml[~ok] > n)
+    assert np.array_equal(b, b_ref) and score == mml_ref[-1]
+    g = ctx.build_graph(want_paths=True)
+    go = O.graph(msa, b_ref)
+    assert np.array_equal(g.block_height, go["heights"])
+    assert np.array_equal(g.node_block, go["node_block"]) and np.array_equal(g.node_row, go["node_row"])
+    assert np.array_equal(g.edge_src, go["edge_src"]) and np.array_equal(g.edge_dst, go["edge_dst"])
+    node_of = go["node_of"].copy()
+    node_of[node_of == O.INVALID] = pkg.api.FBG_NO_NODE
+    assert np.array_equal(g.node_of.astype(np.uint64), node_of)
+    assert g.label_total == go["label_total"]
+    if tmp is not None and not (msa == 45).all(axis=1).any():
+        ids = [b"row%d" % i for i in range(msa.shape[0])]
+        a, bpath = str(tmp / "gpu.xgfa"), str(tmp / "cpu.xgfa")
+        ctx.write_xgfa(a, msa, b, ids)
+        O.write_xgfa(bpath, msa, b_ref, ids)
+        assert open(a, "rb").read() == open(bpath, "rb").read()
+
+
+@pytest.mark.parametrize("seed", range(24))
+def test_elastic_random_small(gpu_ctx, seed, tmp_path):
+    rng = np.random.default_rng(500 + seed)
+    m, n = int(rng.integers(1, 40)), int(rng.integers(1, 150))
+    n_p = float(rng.choice([0, 0.05]))
+    msa = synth.random_small_msa(rng, m, n, gap_p=float(rng.choice([0, 0.1, 0.3])), n_p=n_p, alphabet=bytes(rng.choice([b"AC", b"ACGT"])))
+    _check_elastic(gpu_ctx, msa, b"N" if n_p else b"", bool(rng.random() < 0.3), tmp_path)
+
+
+def test_elastic_edge_shapes(gpu_ctx, tmp_path):
+    _check_elastic(gpu_ctx, np.frombuffer(b"A", np.uint8).reshape(1, 1).copy())
+    _check_elastic(gpu_ctx, np.frombuffer(b"ACAG", np.uint8).reshape(4, 1).copy(), tmp=tmp_path)
+    _check_elastic(gpu_ctx, np.tile(np.frombuffer(b"ACGTACGGTACA", np.uint8), (5, 1)), tmp=tmp_path)  # duplicate rows
+    a = synth.random_small_msa(np.random.default_rng(1), 6, 64, gap_p=0.2)
+    a[2, :] = 45  # an all-gap row
+    a[:, :3] = 45  # all-gap leading columns
+    a[:, -2:] = 45  # all-gap trailing columns
+    _check_elastic(gpu_ctx, a)
+    _check_elastic(gpu_ctx, a, tricks_off=True)
+    _check_elastic(gpu_ctx, synth.random_small_msa(np.random.default_rng(2), 33, 97, gap_p=0.1), tmp=tmp_path)   # m just above a warp
+    _check_elastic(gpu_ctx, synth.random_small_msa(np.random.default_rng(3), 129, 70, gap_p=0.1), tmp=tmp_path)  # m just above 128
+
+
+@pytest.mark.parametrize("name,scale", [("cfg3", 0.004), ("cfg4", 0.0008), ("cfg5", 0.0002)])
+def test_elastic_config_twins(gpu_ctx, name, scale, tmp_path):
+    """Scaled-down twins (fewer columns and rows) of the BASELINE elastic configs."""
+    c = synth.CONFIGS[name]
+    m = min(c["m"], 300)
+    n = max(200, int(c["n"] * scale))
+    msa = synth.make_msa(m, n, c["snp"] * 5, max(20, c["gap_div"] // 20), c["n_div"] // 200 if c["n_div"] else 0, seed=31)
+    _check_elastic(gpu_ctx, msa, c["ignore"], False, tmp_path)
+
+
+def _check_nonelastic(ctx, msa, gl):
+    ctx.set_options(elastic=False, gap_limit=gl)
+    ctx.upload(msa)
+    f_ref = O.compute_f(msa, b"", True)
+    assert np.array_equal(ctx.compute_f(), f_ref)
+    v_ref = O.v_from_f(f_ref)
+    failed, s_ref, prev_ref, b_ref, score_ref = O.dp_nonelastic(v_ref, greedy=(gl != 1))
+    if failed:
+        with pytest.raises(pkg.NoSegmentation):
+            ctx.segment()
+        assert ctx.score == score_ref
+        return
+    b, score = ctx.segment()
+    s, prev, v = ctx.dp(False)
+    assert np.array_equal(v, v_ref) and np.array_equal(s, s_ref) and np.array_equal(prev, prev_ref)
+    assert np.array_equal(b, b_ref) and score == score_ref
+    g = ctx.build_graph()
+    go = O.graph(msa, b_ref)
+    assert g.n_nodes == len(go["node_row"]) and g.n_edges == len(go["edge_src"]) and g.label_total == go["label_total"]
+    assert np.array_equal(g.edge_src, go["edge_src"]) and np.array_equal(g.edge_dst, go["edge_dst"])
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_nonelastic_random_small(gpu_ctx, seed):
+    rng = np.random.default_rng(900 + seed)
+    m, n = int(rng.integers(1, 30)), int(rng.integers(1, 200))
+    gapped = seed % 2 == 1
+    msa = synth.random_small_msa(rng, m, n, gap_p=(0.1 if gapped else 0.0), alphabet=bytes(rng.choice([b"AC", b"ACGT"])), div=0.5)
+    _check_nonelastic(gpu_ctx, msa, 0 if gapped else 1)
+
+
+def test_nonelastic_cfg2_twin(gpu_ctx):
+    """cfg2 (1000 x 30 kbp, 0.1 % SNP, gapless, non-elastic) at n/10."""
+    msa = synth.make_msa(1000, 3000, snp=0.001, seed=2)
+    _check_nonelastic(gpu_ctx, msa, 1)
+
+
+# ------------------------------------------------- full-size, size-independent properties
+def test_cfg2_full_size_properties(gpu_ctx):
+    """cfg2 at BASELINE size: SA is a permutation with ISA its inverse, f is valid
+    (monotone for gapless rows, f[x] >= x), blocks tile [0,n) and respect f, node ids are
+    dense, every row's path reproduces the row."""
+    msa, c = synth.make_config("cfg2")
+    m, n = msa.shape
+    ctx = gpu_ctx
+    ctx.set_options(elastic=False, gap_limit=1)
+    ctx.upload(msa)
+    ctx.build_index()
+    sa, isa = ctx.sa(), ctx.isa()
+    N = len(sa)
+    assert N == m * n + m + 1
+    assert np.array_equal(isa[sa.astype(np.int64)], np.arange(N, dtype=np.uint64))
+    lcp = ctx.lcp()
+    T = ctx.text()
+    rng = np.random.default_rng(0)
+    for k in rng.integers(1, N, size=300):  # spot-check order + LCP by direct comparison
+        a, b = int(sa[k - 1]), int(sa[k])
+        l = int(lcp[k])
+        assert np.array_equal(T[a:a + l], T[b:b + l])
+        assert a + l >= N or b + l >= N or T[a + l] < T[b + l]
+    f = ctx.compute_f()
+    assert np.all(f >= np.arange(n, dtype=np.uint64)) and np.all(np.diff(f.astype(np.int64)) >= 0)
+    b, score = ctx.segment()
+    starts = np.concatenate([[0], b[:-1] + 1]).astype(np.int64)
+    assert b[-1] == n - 1 and np.all(b.astype(np.int64) >= starts)
+    assert np.all(f[starts] <= b) and int((b.astype(np.int64) - starts + 1).max()) == score
+    g = ctx.build_graph(want_paths=True)
+    assert np.all(np.diff(g.node_block.astype(np.int64)) >= 0) and g.n_nodes == int(g.block_height.sum())
+    # round trip: labels of row i's path concatenate back to row i
+    for i in (0, m // 2, m - 1):
+        parts = []
+        for j in range(len(b)):
+            rep = int(g.node_row[int(g.node_of[j, i])])
+            parts.append(msa[rep, starts[j]: int(b[j]) + 1])
+        assert np.array_equal(np.concatenate(parts), msa[i])
