@@ -46,7 +46,7 @@ class FbgStats(C.Structure):
 EXPORTS = [
     "fbg_kernel_name", "fbg_ctx_create", "fbg_ctx_destroy", "fbg_last_error", "fbg_set_options", "fbg_upload_msa",
     "fbg_upload_msa_device", "fbg_build_index", "fbg_compute_f", "fbg_segment", "fbg_get_boundaries", "fbg_build_graph",
-    "fbg_graph_free", "fbg_run", "fbg_run_device", "fbg_get_stats", "fbg_reset_stats", "fbg_get_f", "fbg_get_text",
+    "fbg_graph_free", "fbg_run", "fbg_run_device", "fbg_get_stream", "fbg_get_stats", "fbg_reset_stats", "fbg_get_f", "fbg_get_text",
     "fbg_get_sa", "fbg_get_isa", "fbg_get_lcp", "fbg_get_dp", "fbg_radix_sort_pairs", "fbg_radix_sort_bench", "fbg_write_xgfa",
 ]
 
@@ -91,6 +91,8 @@ def load_library():
     lib.fbg_graph_free.restype = None
     lib.fbg_run.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_int, _u64p, _u64p, C.POINTER(FbgGraph)]
     lib.fbg_run_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_int, _u64p, _u64p, C.POINTER(FbgGraph)]
+    lib.fbg_get_stream.argtypes = [C.c_void_p]
+    lib.fbg_get_stream.restype = C.c_void_p
     lib.fbg_get_stats.argtypes = [C.c_void_p, C.POINTER(FbgStats)]
     lib.fbg_reset_stats.argtypes = [C.c_void_p]
     lib.fbg_reset_stats.restype = None
@@ -226,6 +228,9 @@ class Context:
                                      C.byref(self._graph), int(ids is not None), arr)
         if rc != FBG_OK:
             raise FbgError(rc, "cannot write " + path)
+
+    def stream_ptr(self) -> int:
+        return int(self.lib.fbg_get_stream(self.h) or 0)
 
     def stats(self) -> dict:
         st = FbgStats()

@@ -250,6 +250,8 @@ int fbg_run_device(fbg_ctx *ctx, const void *rows, uint64_t m, uint64_t n, int w
 	return run_common(ctx, rows, m, n, true, want_paths, n_blocks, score, out);
 }
 
+void *fbg_get_stream(fbg_ctx *ctx) { return ctx ? (void *) ctx->p.dev.stream : nullptr; }
+
 int fbg_get_stats(fbg_ctx *ctx, fbg_stats *out) {
 	if (!ctx || !out) return FBG_ERR_ARG;
 	FBG_TRY(ctx)

@@ -105,6 +105,10 @@ int fbg_run(fbg_ctx *ctx, const uint8_t *rows_rowmajor, uint64_t m, uint64_t n, 
 int fbg_run_device(fbg_ctx *ctx, const void *device_rows, uint64_t m, uint64_t n, int want_paths,
                    uint64_t *n_blocks, uint64_t *score, fbg_graph *out);
 
+/* The CUDA stream (cudaStream_t) every kernel of this context is launched on, so a caller
+ * can bracket the work with its own events. */
+void *fbg_get_stream(fbg_ctx *ctx);
+
 int fbg_get_stats(fbg_ctx *ctx, fbg_stats *out);
 void fbg_reset_stats(fbg_ctx *ctx);
 
