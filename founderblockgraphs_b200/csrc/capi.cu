@@ -35,7 +35,7 @@ void Pipeline::free_all() {
 
 } // namespace fbg
 
-static const char *KNAMES[K_COUNT] = {"pack", "kmer", "radix_hist", "radix_scatter", "scan", "doubling_aux", "lcp", "fcol", "dp", "graph"};
+static const char *KNAMES[K_COUNT] = {"pack", "kmer", "radix_hist", "radix_scatter", "scan", "doubling_aux", "lcp", "fcol", "dp", "graph", "tile_sort"};
 
 #define FBG_TRY(ctx) try {
 #define FBG_CATCH(ctx)                                                         \
@@ -48,7 +48,7 @@ static u64 arena_need(const Pipeline &p) {
 	// four u32 work arrays, the count matrix (see suffix.cu); upper bound on N is m*n+m+1
 	u64 N = p.m * p.n + p.m + 1;
 	u64 ntiles = (N + RS_TILE - 1) / RS_TILE;
-	u64 k1 = N * 72 + ntiles * RS_BINS * 12 + (1u << 20); // K1 uses 52 B/char; K4 up to 64 B per (row,block) record
+	u64 k1 = N * 76 + ntiles * RS_BINS * 12 + (1u << 20); // K1 uses 74 B/char (suffix.cu); K4 up to 64 B per (row,block) record
 	u64 W = p.W, NC = (W + 127) / 128;
 	u64 k0 = NC * p.m * 16 + (1u << 20);
 	return (k1 > k0 ? k1 : k0) + (16u << 20);

@@ -47,6 +47,7 @@ enum KernelId {
 	K_FCOL,          // K2: per-column f(x)
 	K_DP,            // K3: segmentation DP + backtrack
 	K_GRAPH,         // K4: label hash / dedup / edges
+	K_TILE_SORT,     // K1: bucket-local shared-memory sort of tied suffixes
 	K_COUNT
 };
 

@@ -112,13 +112,20 @@ __global__ void k0_chunk_apply_kernel(const u32 *__restrict__ NG, const u32 *__r
 	}
 }
 
-// start[i] = sum_{i'<i} (rowlen[i'] + 1); start[m] = total; N = start[m] + 1
-__global__ void k0_starts_kernel(const u32 *__restrict__ rowlen, u64 m, u32 *__restrict__ start, u64 *__restrict__ totals) {
-	if (blockIdx.x || threadIdx.x) return;
-	u64 run = 0;
-	for (u64 i = 0; i < m; i++) { start[i] = (u32) run; run += (u64) rowlen[i] + 1; }
-	start[m] = (u32) run;
-	totals[2] = run + 1;
+// start[i] = sum_{i'<i} (rowlen[i'] + 1); start[m] = total; N = start[m] + 1.  One CTA,
+// chunks of 1024 rows scanned in shared memory.
+__global__ void __launch_bounds__(1024) k0_starts_kernel(const u32 *__restrict__ rowlen, u64 m, u32 *__restrict__ start, u64 *__restrict__ totals) {
+	__shared__ u64 sm[32];
+	u64 carry = 0;
+	for (u64 base = 0; base < m; base += 1024) {
+		u64 i = base + threadIdx.x;
+		u64 v = i < m ? (u64) rowlen[i] + 1 : 0;
+		u64 tot;
+		u64 ex = block_excl_scan<OpSumU64>(v, sm, &tot);
+		if (i < m) start[i] = (u32) (carry + ex);
+		carry += tot;
+	}
+	if (threadIdx.x == 0) { start[m] = (u32) carry; totals[2] = carry + 1; }
 }
 
 // one thread per (row, 32-column tile): scatter non-gap bytes and their columns
@@ -189,7 +196,7 @@ void k0_pack(Pipeline &p) {
 	k0_chunk_sum_kernel<<<div_up(NC * m, 256), 256, 0, d.stream>>>(p.NG, p.IG, m, W, NC, CS, CL, CI, CG);
 	k0_chunk_scan_kernel<<<div_up(m, 128), 128, 0, d.stream>>>(m, NC, CS, CL, CI, CG, p.rowlen, p.lastcol, p.scalars);
 	k0_chunk_apply_kernel<<<div_up(NC * m, 256), 256, 0, d.stream>>>(p.NG, p.IG, m, W, NC, CS, CI, p.RK, p.NIA);
-	k0_starts_kernel<<<1, 32, 0, d.stream>>>(p.rowlen, m, p.start, p.scalars);
+	k0_starts_kernel<<<1, 1024, 0, d.stream>>>(p.rowlen, m, p.start, p.scalars);
 	FBG_LAUNCH_CHECK();
 	FBG_CUDA(cudaMemcpyAsync(p.h_scalars, p.scalars, 8 * sizeof(u64), cudaMemcpyDeviceToHost, d.stream));
 	FBG_CUDA(cudaStreamSynchronize(d.stream));

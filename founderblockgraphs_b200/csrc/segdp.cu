@@ -30,11 +30,17 @@ __global__ void k3_scatter_u_kernel(const u32 *__restrict__ f, u64 n, u32 *__res
 	if (e <= n) atomicMax(&U[e], (u32) x + 1);
 }
 
+// The chain only ever looks back about one segment length, so the last DP_RING values
+// live in shared memory (slot x & (DP_RING-1)); a slot is trusted while no column that
+// aliases it can have been written: x + DP_RING > F + 31.  Older values come from HBM.
+constexpr u32 DP_RING = 8192;
+
 // single warp. mml/bt have n+1 entries. out[0] = nb, out[1] = mml[n]
 __global__ void __launch_bounds__(32) k3_elastic_dp_kernel(const u32 *__restrict__ f, const u32 *__restrict__ U, u64 n, u32 *mml, u32 *bt, u32 *rev, u32 *bnd, u64 *out) {
+	__shared__ u32 ring[DP_RING];
 	const u32 l = lane_id();
 	const u32 INV = (u32) n + 1;
-	if (l == 0) { mml[0] = 0; bt[0] = 0; }
+	if (l == 0) { mml[0] = 0; bt[0] = 0; ring[0] = 0; }
 	__syncwarp();
 	u64 F = 1;
 	while (F <= n) {
@@ -51,7 +57,7 @@ __global__ void __launch_bounds__(32) k3_elastic_dp_kernel(const u32 *__restrict
 					u64 dd = j - x;
 					if (dd > best) break;
 					u64 ex = (u64) f[x] + 1;
-					u32 mx = ld_vol(&mml[x]);
+					u32 mx = (x + DP_RING > F + 31) ? ring[x & (DP_RING - 1)] : ld_vol(&mml[x]);
 					if (ex <= j && mx <= (u32) n) {
 						if (dd > mx) { best = (u32) dd; bx = (u32) x; break; }      // B candidate, ties go to B
 						else if (mx < best) { best = mx; bx = (u32) x; }            // A candidate, largest x wins ties
@@ -60,8 +66,9 @@ __global__ void __launch_bounds__(32) k3_elastic_dp_kernel(const u32 *__restrict
 					x--;
 				}
 			}
-			if (bx == U32_MAX) { mml[j] = INV; bt[j] = U32_MAX; }
-			else { mml[j] = best; bt[j] = bx; }
+			if (bx == U32_MAX) { best = INV; bx = U32_MAX; }
+			mml[j] = best; bt[j] = bx;
+			ring[j & (DP_RING - 1)] = best;
 		}
 		__threadfence_block();
 		__syncwarp();
@@ -114,6 +121,7 @@ __global__ void k3_v_sequential_kernel(const u32 *__restrict__ f, u64 n, const u
 
 // single warp wavefront over fbg.cpp:622-643; out[0]=nb, out[1]=s[n-1], out[2]=status
 __global__ void __launch_bounds__(32) k3_nonelastic_dp_kernel(const u32 *__restrict__ v, u64 n, u32 *s, u32 *prev, u32 *rev, u32 *bnd, u64 *out) {
+	__shared__ u32 ring[DP_RING];
 	const u32 l = lane_id();
 	u64 F = 0;
 	while (F < n) {
@@ -127,7 +135,8 @@ __global__ void __launch_bounds__(32) k3_nonelastic_dp_kernel(const u32 *__restr
 			if (vj <= j) {
 				u64 jp = vj;
 				for (;;) {
-					u32 sp = jp ? ld_vol(&s[jp - 1]) : 0u;
+					u32 sp = 0u;
+					if (jp) { u64 x = jp - 1; sp = (x + DP_RING > F + 31) ? ring[x & (DP_RING - 1)] : ld_vol(&s[x]); }
 					if (jp != 0 && sp == (u32) jp + 1) { jp--; continue; }
 					u32 len = (u32) (j - jp + 1);
 					u32 cand = sp > len ? sp : len;
@@ -138,6 +147,7 @@ __global__ void __launch_bounds__(32) k3_nonelastic_dp_kernel(const u32 *__restr
 				}
 			}
 			s[j] = sj; prev[j] = pj;
+			ring[j & (DP_RING - 1)] = sj;
 		}
 		__threadfence_block();
 		__syncwarp();

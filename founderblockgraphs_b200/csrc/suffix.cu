@@ -13,6 +13,7 @@
 // its sub-bucket.  LCP is computed at irreducible positions only (BWT[k] !=
 // BWT[k-1]) by direct comparison and filled with PLCP[p] = max_{q<=p,irr}(PLCP[q]+q) - p.
 #include "pipeline.cuh"
+#include "tilesort.cuh"
 
 namespace fbg {
 
@@ -56,8 +57,22 @@ __global__ void __launch_bounds__(KM_THREADS) k1_kmer_kernel(const u8 *__restric
 }
 
 // ------------------------------------------------------------- doubling rounds
-// HH[t] = (index of bucket head << 32) | index of sub-bucket head, 0 where not a head
-__global__ void k1_heads_kernel(const u64 *__restrict__ keys, u64 na, int hi_shift, u64 *__restrict__ HH) {
+// Tied suffixes live in two lists, each with every bucket contiguous:
+//   S  buckets of <= BSMALL suffixes: (lp, lr, r2) = text position, bucket rank,
+//      rank of the suffix h further on.  One CTA sorts a tile of whole buckets in
+//      shared memory (k1_tile_sort_kernel).
+//   B  larger buckets: 64-bit keys (lr << nbits | r2) + position, sorted by the
+//      device-wide radix passes.
+// A rank is the SA index of the bucket head, so a sub-bucket's new rank is the old
+// rank plus its offset inside the (sorted) bucket.  All rank look-ups R[p+h] of a
+// round are done by the compaction kernel of the round before, i.e. before any
+// rank of the round changes.
+constexpr u32 BSMALL = 8192;     // largest bucket the tile path takes (CAP_max / 2)
+constexpr u32 CLS_DROP = 0, CLS_SMALL = 1, CLS_BIG = 2;
+
+// HH[t] = (bucket head index << 32) | sub-bucket head index, 0 where not a head;
+// HR[na-1-t] = na - t at sub-bucket heads (a max-scan of HR gives the next head)
+__global__ void k1_heads_kernel(const u64 *__restrict__ keys, u64 na, int hi_shift, u64 *__restrict__ HH, u32 *__restrict__ HR) {
 	u64 t = (u64) blockIdx.x * blockDim.x + threadIdx.x;
 	if (t >= na) return;
 	u64 k = keys[t];
@@ -65,47 +80,262 @@ __global__ void k1_heads_kernel(const u64 *__restrict__ keys, u64 na, int hi_shi
 	bool hs = (t == 0) || (k != kp);
 	bool hb = (t == 0) || (hi_shift < 64 && (k >> hi_shift) != (kp >> hi_shift));
 	HH[t] = ((hb ? t : 0) << 32) | (hs ? t : 0);
+	HR[na - 1 - t] = hs ? (u32) (na - t) : 0u;
 }
 
-// new rank = bucket rank + (sub-head index - bucket-head index); flag = still tied
-__global__ void k1_update_kernel(const u64 *__restrict__ keys, const u32 *__restrict__ vals, const u64 *__restrict__ HH, u64 na, int hi_shift,
-                                 u32 *__restrict__ R, u32 *__restrict__ newr, u32 *__restrict__ flag) {
+// new rank = bucket rank + (sub-head index - bucket-head index); class by sub-bucket size
+__global__ void __launch_bounds__(256) k1_update_kernel(const u64 *__restrict__ keys, const u32 *__restrict__ vals, const u64 *__restrict__ HH, const u32 *__restrict__ HR,
+                                                        u64 na, int hi_shift, u32 *__restrict__ R, u32 *__restrict__ newr, u8 *__restrict__ cls, u32 *__restrict__ maxb) {
+	__shared__ u32 smax[8];
 	u64 t = (u64) blockIdx.x * blockDim.x + threadIdx.x;
-	if (t >= na) return;
-	u64 k = keys[t];
-	u64 hh = HH[t];
-	u32 hb = (u32) (hh >> 32), hs = (u32) hh;
-	u32 base = hi_shift < 64 ? (u32) (k >> hi_shift) : 0u;
-	u32 nr = base + (hs - hb);
-	bool single = (hs == (u32) t) && (t + 1 == na || keys[t + 1] != k);
-	R[vals[t]] = nr;
-	newr[t] = nr;
-	flag[t] = single ? 0u : 1u;
+	u32 small_size = 0;
+	if (t < na) {
+		u64 k = keys[t];
+		u64 hh = HH[t];
+		u32 hb = (u32) (hh >> 32), hs = (u32) hh;
+		u32 base = hi_shift < 64 ? (u32) (k >> hi_shift) : 0u;
+		u32 nr = base + (hs - hb);
+		u32 nh = (t + 1 < na) ? (u32) na - HR[na - 2 - t] : (u32) na; // HR scanned: 0 = no head after t
+		u32 size = nh - hs;
+		u32 c = size == 1 ? CLS_DROP : (size <= BSMALL ? CLS_SMALL : CLS_BIG);
+		R[vals[t]] = nr;
+		newr[t] = nr;
+		cls[t] = (u8) c;
+		if (c == CLS_SMALL && hs == (u32) t) small_size = size;
+	}
+	small_size = warp_reduce_max(small_size);
+	if (lane_id() == 0) smax[threadIdx.x >> 5] = small_size;
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		u32 v = 0;
+		for (int w = 0; w < 8; w++) v = smax[w] > v ? smax[w] : v;
+		if (v) atomicMax(maxb, v);
+	}
 }
 
-__global__ void k1_compact_kernel(const u32 *__restrict__ vals, const u32 *__restrict__ newr, const u32 *__restrict__ flag, const u32 *__restrict__ pos, u64 na,
-                                  u32 *__restrict__ lp, u32 *__restrict__ lr) {
-	u64 t = (u64) blockIdx.x * blockDim.x + threadIdx.x;
-	if (t >= na) return;
-	if (flag[t]) { u32 q = pos[t]; lp[q] = vals[t]; lr[q] = newr[t]; }
+// ---- compaction of (lp, lr, cls) into the next S and B lists, with the rank look-up fused
+constexpr int CP_THREADS = 256;
+constexpr int CP_ITEMS = 16;
+constexpr int CP_TILE = CP_THREADS * CP_ITEMS;
+
+__device__ __forceinline__ u64 cls_count16(uint4 v) {
+	// bytes equal to 1 -> low word, equal to 2 -> high word
+	u32 w[4] = {v.x, v.y, v.z, v.w};
+	u32 s = 0, b = 0;
+#pragma unroll
+	for (int q = 0; q < 4; q++) {
+		u32 one = w[q] & 0x01010101u, two = (w[q] >> 1) & 0x01010101u;
+		s += __popc(one & ~two);
+		b += __popc(two & ~one);
+	}
+	return ((u64) b << 32) | s;
 }
 
-// key = (rank[p] << nbits) | rank[p+h]; tied suffixes never contain the sentinel in
-// their first h symbols, so p+h <= N-1
-__global__ void k1_keys_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, const u32 *__restrict__ R, u64 na, u64 h, u64 N, int nbits,
-                               u64 *__restrict__ keys, u32 *__restrict__ vals) {
-	u64 t = (u64) blockIdx.x * blockDim.x + threadIdx.x;
-	if (t >= na) return;
-	u32 p = lp[t];
-	u64 q = (u64) p + h;
-	u32 r2 = q < N ? R[q] : 0u;
-	keys[t] = ((u64) lr[t] << nbits) | r2;
-	vals[t] = p;
+__global__ void __launch_bounds__(CP_THREADS) k1_cls_count_kernel(const u8 *__restrict__ cls, u64 na, u64 *__restrict__ partial) {
+	__shared__ u64 sm[32];
+	u64 base = (u64) blockIdx.x * CP_TILE + (u64) threadIdx.x * CP_ITEMS;
+	u64 c = 0;
+	if (base + CP_ITEMS <= na) c = cls_count16(*reinterpret_cast<const uint4 *>(cls + base));
+	else for (u64 i = base; i < na; i++) { u8 v = cls[i]; c += v == CLS_SMALL ? 1ull : (v == CLS_BIG ? (1ull << 32) : 0ull); }
+	u64 tot;
+	block_excl_scan<OpSumU64>(c, sm, &tot);
+	if (threadIdx.x == 0) partial[blockIdx.x] = tot;
+}
+
+struct CompactOut {
+	u32 *Slp, *Slr, *Sr2;  // next S list
+	u64 *Bkey; u32 *Bval;  // next B list
+};
+
+// partial: exclusive-scanned per-tile (small | big << 32) counts; base: device word with
+// the offsets this call appends at (same packing), or null for 0.
+__global__ void __launch_bounds__(CP_THREADS) k1_cls_write_kernel(const u8 *__restrict__ cls, const u32 *__restrict__ lp, const u32 *__restrict__ lr, u64 na,
+                                                                  const u64 *__restrict__ partial, const u64 *__restrict__ base,
+                                                                  const u32 *__restrict__ R, u64 hnext, u64 N, int nbits, CompactOut o) {
+	__shared__ u64 sm[32];
+	const u64 b0 = (u64) blockIdx.x * CP_TILE + (u64) threadIdx.x * CP_ITEMS;
+	u8 c[CP_ITEMS];
+	u64 cnt = 0;
+#pragma unroll
+	for (int i = 0; i < CP_ITEMS; i++) {
+		c[i] = b0 + i < na ? cls[b0 + i] : (u8) CLS_DROP;
+		cnt += c[i] == CLS_SMALL ? 1ull : (c[i] == CLS_BIG ? (1ull << 32) : 0ull);
+	}
+	u64 tot;
+	u64 ex = block_excl_scan<OpSumU64>(cnt, sm, &tot);
+	ex += partial[blockIdx.x] + (base ? *base : 0ull);
+	u32 qs = (u32) ex, qb = (u32) (ex >> 32);
+#pragma unroll
+	for (int i = 0; i < CP_ITEMS; i++) {
+		if (c[i] == CLS_DROP) continue;
+		u32 p = lp[b0 + i], r = lr[b0 + i];
+		u64 q = (u64) p + hnext;
+		u32 r2 = q < N ? R[q] : 0u;
+		if (c[i] == CLS_SMALL) { o.Slp[qs] = p; o.Slr[qs] = r; o.Sr2[qs] = r2; qs++; }
+		else { o.Bkey[qb] = ((u64) r << nbits) | r2; o.Bval[qb] = p; qb++; }
+	}
+}
+
+// ---- bucket-local sort of the S list
+// CTA b owns the buckets whose head lies in [b*tile, (b+1)*tile) and loads the window
+// [b*tile, b*tile + CAP); tile <= CAP - (largest bucket), so every owned bucket fits.
+// Key = bucket head offset | r2 | offset in the window, sorted by the shared-memory
+// bitonic network; sub-bucket heads by a max-scan; ranks, classes and R updates follow.
+template <int CAP> struct TileCfg { static constexpr int THREADS = CAP >= 8192 ? 1024 : CAP / 8; };
+
+template <int CAP> __global__ void __launch_bounds__(TileCfg<CAP>::THREADS)
+k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, const u32 *__restrict__ r2, u64 na, u32 tile,
+                    u32 *__restrict__ R, u32 *__restrict__ lp_out, u32 *__restrict__ lr_out, u8 *__restrict__ cls_out, u32 *__restrict__ scal) {
+	constexpr int THREADS = TileCfg<CAP>::THREADS;
+	constexpr int ITEMS = CAP / THREADS;
+	constexpr int NW = THREADS / 32;
+	constexpr int WCH = 32 * ITEMS;
+	constexpr int LOGC = CAP == 16384 ? 14 : CAP == 8192 ? 13 : CAP == 4096 ? 12 : CAP == 2048 ? 11 : CAP == 1024 ? 10 : -1;
+	static_assert(LOGC > 0, "unsupported tile capacity");
+	extern __shared__ __align__(16) unsigned char k1_raw[];
+	u64 *key = reinterpret_cast<u64 *>(k1_raw);
+	__shared__ u32 s_first, s_end, s_wtot[32];
+	const u32 tid = threadIdx.x, w = tid >> 5, l = tid & 31;
+	const u64 w0 = (u64) blockIdx.x * tile;
+	const u32 wlen = (u32) (na - w0 < (u64) CAP ? na - w0 : (u64) CAP);
+	const u32 tlen = tile < wlen ? tile : wlen;
+	if (tid == 0) { s_first = U32_MAX; s_end = U32_MAX; }
+	__syncthreads();
+
+	// 1. bucket heads in the window; hbv = inclusive max-scan of (head ? idx+1 : 0)
+	u32 hbv[ITEMS];
+	u32 carry = 0, fmin = U32_MAX, emin = U32_MAX;
+#pragma unroll
+	for (int i = 0; i < ITEMS; i++) {
+		u32 idx = w * WCH + i * 32 + l;
+		u32 v = 0;
+		if (idx < wlen) {
+			u64 t = w0 + idx;
+			bool head = (t == 0) || (lr[t - 1] != lr[t]);
+			if (head) {
+				v = idx + 1;
+				if (idx < tlen) fmin = idx < fmin ? idx : fmin;
+				else emin = idx < emin ? idx : emin;
+			}
+		}
+		u32 inc = warp_incl_max(v);
+		inc = inc > carry ? inc : carry;
+		hbv[i] = inc;
+		carry = __shfl_sync(0xffffffffu, inc, 31);
+	}
+	if (l == 31) s_wtot[w] = carry;
+	fmin = ~warp_reduce_max(~fmin);
+	emin = ~warp_reduce_max(~emin);
+	if (l == 0) {
+		if (fmin != U32_MAX) atomicMin(&s_first, fmin);
+		if (emin != U32_MAX) atomicMin(&s_end, emin);
+	}
+	__syncthreads();
+	const u32 first = s_first;
+	if (first == U32_MAX) return; // no bucket starts in this tile
+	u32 endidx = s_end;
+	if (endidx == U32_MAX) {
+		if (w0 + wlen == na) endidx = wlen;
+		else { if (tid == 0) scal[1] = 1u; return; } // a bucket larger than CAP - tile: host contract broken
+	}
+	const u32 cnt = endidx - first;
+	u32 wpre = 0;
+	for (u32 ww = 0; ww < w; ww++) { u32 x = s_wtot[ww]; wpre = x > wpre ? x : wpre; }
+
+	// 2. keys
+#pragma unroll
+	for (int i = 0; i < ITEMS; i++) {
+		u32 idx = w * WCH + i * 32 + l;
+		u64 k = ~0ull;
+		if (idx >= first && idx < endidx) {
+			u32 hb1 = hbv[i] > wpre ? hbv[i] : wpre;
+			u32 hb_rel = hb1 - 1 - first;
+			k = ((u64) hb_rel << (32 + LOGC)) | ((u64) r2[w0 + idx] << LOGC) | (u64) (idx - first);
+		}
+		key[idx] = k;
+	}
+	__syncthreads();
+
+	// 3. sort
+	tile_bitonic_sort<CAP, THREADS>(key);
+
+	// 4. sub-bucket heads: hsv = inclusive max-scan of (sub-head ? s+1 : 0)
+	u32 hsv[ITEMS];
+	carry = 0;
+#pragma unroll
+	for (int i = 0; i < ITEMS; i++) {
+		u32 s = w * WCH + i * 32 + l;
+		u32 v = 0;
+		if (s < cnt) {
+			bool sh = s == 0;
+			if (!sh) sh = (key[s] >> LOGC) != (key[s - 1] >> LOGC);
+			if (sh) v = s + 1;
+		}
+		u32 inc = warp_incl_max(v);
+		inc = inc > carry ? inc : carry;
+		hsv[i] = inc;
+		carry = __shfl_sync(0xffffffffu, inc, 31);
+	}
+	if (l == 31) s_wtot[w] = carry;
+	__syncthreads();
+	wpre = 0;
+	for (u32 ww = 0; ww < w; ww++) { u32 x = s_wtot[ww]; wpre = x > wpre ? x : wpre; }
+
+	// 5. ranks, classes, outputs
+	const u64 g0 = w0 + first;
+	u32 mx = 0;
+#pragma unroll
+	for (int i = 0; i < ITEMS; i++) {
+		u32 s = w * WCH + i * 32 + l;
+		if (s < cnt) {
+			u64 k = key[s];
+			u32 hs = (hsv[i] > wpre ? hsv[i] : wpre) - 1;
+			u32 hb = (u32) (k >> (32 + LOGC));
+			u32 irel = (u32) k & (u32) (CAP - 1);
+			bool last = (s + 1 >= cnt) || ((key[s + 1] >> LOGC) != (k >> LOGC));
+			u32 nr = lr[g0 + hb] + (hs - hb);
+			u32 p = lp[g0 + irel];
+			R[p] = nr;
+			lp_out[g0 + s] = p;
+			lr_out[g0 + s] = nr;
+			cls_out[g0 + s] = (u8) ((hs == s && last) ? CLS_DROP : CLS_SMALL);
+			if (last && s != hs) { u32 sz = s - hs + 1; mx = sz > mx ? sz : mx; }
+		}
+	}
+	mx = warp_reduce_max(mx);
+	if (l == 0 && mx) atomicMax(&scal[0], mx);
+}
+
+template <int CAP> static void launch_tile_sort(Dev &d, const u32 *lp, const u32 *lr, const u32 *r2, u64 na, u32 maxb,
+                                                u32 *R, u32 *lp_out, u32 *lr_out, u8 *cls_out, u32 *scal) {
+	u32 tile = (u32) CAP - maxb;
+	size_t smem = (size_t) CAP * 8;
+	FBG_CUDA(cudaFuncSetAttribute(k1_tile_sort_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+	k1_tile_sort_kernel<CAP><<<div_up(na, tile), TileCfg<CAP>::THREADS, smem, d.stream>>>(lp, lr, r2, na, tile, R, lp_out, lr_out, cls_out, scal);
+	FBG_LAUNCH_CHECK();
 }
 
 __global__ void k1_invert_kernel(const u32 *__restrict__ R, u64 N, u32 *__restrict__ SA) {
 	u64 p = (u64) blockIdx.x * blockDim.x + threadIdx.x;
 	if (p < N) SA[R[p]] = (u32) p;
+}
+
+// Appends the survivors of one sorted list to the next S / B lists.  *total_out receives
+// this call's (small | big << 32) counts; base (device word, same packing) = where to append.
+static void compact_lists(Dev &d, const u8 *cls, const u32 *lp, const u32 *lr, u64 na, const u64 *base, u64 *total_out,
+                          const u32 *R, u64 hnext, u64 N, int nbits, CompactOut o) {
+	if (na == 0) { FBG_CUDA(cudaMemsetAsync(total_out, 0, sizeof(u64), d.stream)); return; }
+	u32 nt = div_up(na, CP_TILE);
+	u64 mk = d.mark();
+	u64 *partial = d.alloc<u64>(nt);
+	d.begin(K_DOUBLING_AUX);
+	k1_cls_count_kernel<<<nt, CP_THREADS, 0, d.stream>>>(cls, na, partial);
+	scan_partials_kernel<OpSumU64><<<1, 1024, 0, d.stream>>>(partial, nt, total_out);
+	k1_cls_write_kernel<<<nt, CP_THREADS, 0, d.stream>>>(cls, lp, lr, na, partial, base, R, hnext, N, nbits, o);
+	FBG_LAUNCH_CHECK();
+	d.end((double) na * (2.0 + 8.0 + 4.0 + 12.0));
+	d.note_launches(K_DOUBLING_AUX, 2);
+	d.release(mk);
 }
 
 void k1_suffix_array(Pipeline &p) {
@@ -138,10 +368,14 @@ void k1_suffix_array(Pipeline &p) {
 	rb.v[0] = d.alloc<u32>(N); rb.v[1] = d.alloc<u32>(N);
 	rb.cur = 0;
 	u64 *HH = d.alloc<u64>(N);
-	u32 *newr = d.alloc<u32>(N), *flag = d.alloc<u32>(N), *pos = d.alloc<u32>(N);
-	u32 *lp = d.alloc<u32>(N), *lr = d.alloc<u32>(N);
-	u32 *total = reinterpret_cast<u32 *>(p.scalars + 8);
-	u32 *h_total = reinterpret_cast<u32 *>(p.h_scalars + 8);
+	u32 *HR = d.alloc<u32>(N), *newr = d.alloc<u32>(N);
+	u8 *clsB = d.alloc<u8>(N + 16), *clsS = d.alloc<u8>(N + 16);
+	u32 *Slp[2], *Slr[2], *Sr2[2];
+	for (int q = 0; q < 2; q++) { Slp[q] = d.alloc<u32>(N); Slr[q] = d.alloc<u32>(N); Sr2[q] = d.alloc<u32>(N); }
+	u32 *lp_out = d.alloc<u32>(N), *lr_out = d.alloc<u32>(N);
+	u32 *sc32 = reinterpret_cast<u32 *>(p.scalars + 8);  // [0] maxb, [1] err
+	u64 *sc64 = p.scalars + 9;                          // (small | big << 32) survivor counts of the [0] S path, [1] B path
+	u64 *h_sc = p.h_scalars + 8;                        // mirror of scalars[8..11]
 
 	k1_kmer_kernel<<<div_up(N, KM_TILE), KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, (u64 *) rb.k[0], rb.v[0]);
 	FBG_LAUNCH_CHECK();
@@ -150,40 +384,60 @@ void k1_suffix_array(Pipeline &p) {
 
 	int nbits = 1;
 	while ((1ull << nbits) < N) nbits++;
-	u64 na = N;
-	u64 h = (u64) K;
-	int hi_shift = 64; // round 0: a single level of buckets
+	u64 nS = 0, nB = N;   // round 0: every suffix goes through the device-wide sort
+	u32 maxb = 0;
+	u64 h = (u64) K;      // depth the current ranks are exact to after the round being run
+	int hi_shift = 64;    // round 0: a single level of buckets
 	int key_bits = K * b;
+	int sc = 0;           // current S list
 	p.sa_rounds = 0;
 	for (;;) {
-		int cur = radix_sort<u64, true>(d, rb, na, 0, key_bits);
-		const u64 *sk = (const u64 *) rb.k[cur];
-		const u32 *sv = rb.v[cur];
-		u32 g = div_up(na, 256);
-		d.begin(K_DOUBLING_AUX);
-		k1_heads_kernel<<<g, 256, 0, d.stream>>>(sk, na, hi_shift, HH);
-		FBG_LAUNCH_CHECK();
-		d.end((double) na * 16.0);
-		device_scan<OpMax2x32, false>(d, HH, HH, na);
-		d.begin(K_DOUBLING_AUX);
-		k1_update_kernel<<<g, 256, 0, d.stream>>>(sk, sv, HH, na, hi_shift, p.ISA, newr, flag);
-		FBG_LAUNCH_CHECK();
-		d.end((double) na * (8.0 + 4.0 + 8.0 + 4.0 + 4.0 + 4.0));
-		device_scan<OpSumU32, true>(d, flag, pos, na, total);
-		d.begin(K_DOUBLING_AUX);
-		k1_compact_kernel<<<g, 256, 0, d.stream>>>(sv, newr, flag, pos, na, lp, lr);
-		FBG_LAUNCH_CHECK();
-		d.end((double) na * 16.0);
-		FBG_CUDA(cudaMemcpyAsync(h_total, total, sizeof(u32), cudaMemcpyDeviceToHost, d.stream));
+		FBG_CUDA(cudaMemsetAsync(p.scalars + 8, 0, 4 * sizeof(u64), d.stream));
+		// ---- S path
+		if (nS) {
+			d.begin(K_TILE_SORT);
+			if (2 * maxb <= 2048) launch_tile_sort<2048>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, lp_out, lr_out, clsS, sc32);
+			else if (2 * maxb <= 8192) launch_tile_sort<8192>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, lp_out, lr_out, clsS, sc32);
+			else launch_tile_sort<16384>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, lp_out, lr_out, clsS, sc32);
+			d.end((double) nS * (12.0 + 4.0 + 9.0));
+		}
+		// ---- B path
+		const u32 *sv = nullptr;
+		if (nB) {
+			int cur = radix_sort<u64, true>(d, rb, nB, 0, key_bits);
+			const u64 *sk = (const u64 *) rb.k[cur];
+			sv = rb.v[cur];
+			u32 g = div_up(nB, 256);
+			d.begin(K_DOUBLING_AUX);
+			k1_heads_kernel<<<g, 256, 0, d.stream>>>(sk, nB, hi_shift, HH, HR);
+			FBG_LAUNCH_CHECK();
+			d.end((double) nB * 20.0);
+			device_scan<OpMax2x32, false>(d, HH, HH, nB);
+			device_scan<OpMaxU32, false>(d, HR, HR, nB);
+			d.begin(K_DOUBLING_AUX);
+			k1_update_kernel<<<g, 256, 0, d.stream>>>(sk, sv, HH, HR, nB, hi_shift, p.ISA, newr, clsB, sc32);
+			FBG_LAUNCH_CHECK();
+			d.end((double) nB * (8.0 + 4.0 + 8.0 + 4.0 + 4.0 + 4.0 + 1.0));
+		}
+		// ---- next lists (all rank updates of this round are enqueued before these look-ups)
+		u64 hnext = h;
+		CompactOut o;
+		o.Slp = Slp[sc ^ 1]; o.Slr = Slr[sc ^ 1]; o.Sr2 = Sr2[sc ^ 1];
+		o.Bkey = (u64 *) rb.k[rb.cur ^ 1]; o.Bval = rb.v[rb.cur ^ 1];
+		compact_lists(d, clsS, lp_out, lr_out, nS, nullptr, sc64, p.ISA, hnext, N, nbits, o);
+		compact_lists(d, clsB, sv, newr, nB, sc64, sc64 + 1, p.ISA, hnext, N, nbits, o);
+		FBG_CUDA(cudaMemcpyAsync(h_sc, p.scalars + 8, 4 * sizeof(u64), cudaMemcpyDeviceToHost, d.stream));
 		FBG_CUDA(cudaStreamSynchronize(d.stream));
 		p.sa_rounds++;
-		na = *h_total;
-		if (na == 0) break;
+		const u32 *h32 = reinterpret_cast<const u32 *>(h_sc);
+		if (h32[1]) throw cuda_error("bucket-local suffix sort met a bucket larger than its tile");
+		maxb = h32[0];
+		nS = (u64) (u32) h_sc[1] + (u64) (u32) h_sc[2];
+		nB = h_sc[2] >> 32;
+		if (nB) rb.cur ^= 1; // the compaction wrote the next B list into the other ping-pong half
+		sc ^= 1;
+		if (nS + nB == 0) break;
 		if (h >= N) throw cuda_error("prefix doubling did not converge");
-		d.begin(K_DOUBLING_AUX);
-		k1_keys_kernel<<<div_up(na, 256), 256, 0, d.stream>>>(lp, lr, p.ISA, na, h, N, nbits, (u64 *) rb.k[rb.cur], rb.v[rb.cur]);
-		FBG_LAUNCH_CHECK();
-		d.end((double) na * (4.0 + 4.0 + 4.0 + 8.0 + 4.0));
 		hi_shift = nbits;
 		key_bits = 2 * nbits;
 		h *= 2;

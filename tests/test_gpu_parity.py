@@ -67,6 +67,22 @@ def test_suffix_array_lcp_degenerate(gpu_ctx):
     _check_index(gpu_ctx, np.frombuffer(b"A", np.uint8).reshape(1, 1).copy())
 
 
+def test_suffix_array_lcp_bucket_classes(gpu_ctx):
+    """Bucket sizes on both sides of every tile-capacity switch of the bucket-local sorter:
+    <= 1024 (2048-key tiles), <= 4096 (8192), <= 8192 (16384), and > 8192 (device-wide radix path)."""
+    rng = np.random.default_rng(5)
+    for rows, cols in [(3, 300), (2, 1500), (3, 2400), (4, 3800)]:
+        _check_index(gpu_ctx, np.full((rows, cols), ord("A"), np.uint8))
+    # periodic rows: huge buckets that split slowly, mixed with unique material
+    a = np.tile(np.frombuffer(b"ACGTAC" * 700, np.uint8), (5, 1)).copy()
+    a[:, 2000:2200] = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, size=(5, 200))]
+    _check_index(gpu_ctx, a)
+    # many mid-sized buckets next to each other (tiles own several whole buckets)
+    b = np.tile(np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, size=400)], (300, 1))
+    b[rng.random(b.shape) < 0.002] = ord("T")
+    _check_index(gpu_ctx, b)
+
+
 def test_suffix_array_lcp_msa_like(gpu_ctx):
     _check_index(gpu_ctx, synth.make_msa(60, 5000, snp=0.002, gap_div=500, seed=11))
 
