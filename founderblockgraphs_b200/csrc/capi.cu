@@ -21,16 +21,13 @@ __global__ void rs_widen_kernel(const u32 *__restrict__ c, u64 *__restrict__ o, 
 	if (i < n) o[i] = c[i];
 }
 
-void Pipeline::free_index() {
-	dfree(NG); dfree(IG); dfree(RK); dfree(NIA); dfree(start); dfree(rowlen); dfree(lastcol);
-	dfree(T); dfree(col); dfree(ISA); dfree(SA); dfree(PLCP); dfree(NLCP);
-	dfree(f); dfree(bnd); dfree(dp_a); dfree(dp_b); dfree(dp_v);
-	have_index = have_f = have_seg = false;
-}
+// every per-MSA array lives in the persistent arena: dropping them is resetting the bump pointer
 void Pipeline::free_all() {
-	free_index();
-	dfree(msa);
-	have_msa = false;
+	NG = IG = RK = NIA = start = rowlen = lastcol = nullptr;
+	T = nullptr; msa = nullptr;
+	col = ISA = SA = PLCP = NLCP = f = bnd = dp_a = dp_b = dp_v = nullptr;
+	dev.pers_top = 0;
+	have_msa = have_index = have_f = have_seg = false;
 }
 
 } // namespace fbg
@@ -95,7 +92,7 @@ void fbg_ctx_destroy(fbg_ctx *ctx) {
 	cudaSetDevice(ctx->p.dev.device);
 	cudaStreamSynchronize(ctx->p.dev.stream);
 	ctx->p.free_all();
-	dfree(ctx->p.scalars);
+	if (ctx->p.scalars) cudaFree(ctx->p.scalars);
 	if (ctx->p.h_scalars) cudaFreeHost(ctx->p.h_scalars);
 	ctx->p.dev.destroy();
 	if (ctx->p.dev.stream) cudaStreamDestroy(ctx->p.dev.stream);

@@ -134,7 +134,7 @@ __global__ void __launch_bounds__(1024) k2_fcol_kernel(FcolArgs a) {
 
 void k2_compute_f(Pipeline &p) {
 	Dev &d = p.dev;
-	if (!p.f) p.f = dmalloc<u32>(p.n + 1);
+	if (!p.f) p.f = p.dev.palloc<u32>(p.n + 1);
 	GroupCfg gc = group_cfg(p.m);
 	u32 mpad = gc.mpad;
 	if (mpad > 8192) throw cuda_error("more than 8192 rows per column group is not supported by the shared-memory f(x) kernel yet");

@@ -159,8 +159,10 @@ __global__ void __launch_bounds__(256) k0_text_kernel(const u8 *__restrict__ msa
 static void alloc_msa(Pipeline &p, u64 m, u64 n) {
 	p.free_all();
 	p.m = m; p.n = n; p.pitch = round_up(n, 32); p.W = p.pitch / 32;
-	p.msa = dmalloc<u8>(m * p.pitch);
-	if (!p.scalars) p.scalars = dmalloc<u64>(64);
+	if (persistent_need(m, n) > p.dev.pers_cap) FBG_CUDA(cudaStreamSynchronize(p.dev.stream)); // about to free the old arena
+	p.dev.reserve_pers(persistent_need(m, n));
+	p.msa = p.dev.palloc<u8>(m * p.pitch);
+	if (!p.scalars) FBG_CUDA(cudaMalloc(&p.scalars, 64 * sizeof(u64)));
 	if (!p.h_scalars) FBG_CUDA(cudaMallocHost(&p.h_scalars, 64 * sizeof(u64)));
 	if (p.pitch != n) FBG_CUDA(cudaMemsetAsync(p.msa, 0x2D, m * p.pitch, p.dev.stream));
 }
@@ -181,9 +183,9 @@ void k0_pack(Pipeline &p) {
 	Dev &d = p.dev;
 	const u64 m = p.m, n = p.n, W = p.W;
 	const u64 NC = (W + CH - 1) / CH;
-	p.NG = dmalloc<u32>(W * m); p.IG = dmalloc<u32>(W * m);
-	p.RK = dmalloc<u32>(W * m); p.NIA = dmalloc<u32>(W * m);
-	p.start = dmalloc<u32>(m + 1); p.rowlen = dmalloc<u32>(m); p.lastcol = dmalloc<u32>(m);
+	p.NG = p.dev.palloc<u32>(W * m); p.IG = p.dev.palloc<u32>(W * m);
+	p.RK = p.dev.palloc<u32>(W * m); p.NIA = p.dev.palloc<u32>(W * m);
+	p.start = p.dev.palloc<u32>(m + 1); p.rowlen = p.dev.palloc<u32>(m); p.lastcol = p.dev.palloc<u32>(m);
 	IgnoreSet ign;
 	for (int q = 0; q < 8; q++) ign.bits[q] = p.opt.ignore_bits[q];
 
@@ -206,8 +208,8 @@ void k0_pack(Pipeline &p) {
 	p.N = p.h_scalars[2];
 	if (p.N >= 0xFFFFFFF0ull)
 		throw cuda_error("text length " + std::to_string(p.N) + " needs 64-bit suffix indices: shard the MSA across GPUs (not in this build)");
-	p.T = dmalloc<u8>(p.N + 64);
-	p.col = dmalloc<u32>(p.N + 1);
+	p.T = p.dev.palloc<u8>(p.N + 64);
+	p.col = p.dev.palloc<u32>(p.N + 1);
 	FBG_CUDA(cudaMemsetAsync(p.T + p.N, 0, 64, d.stream)); // zero tail so k-mer windows can over-read
 	u64 wb = div_up(W, 256);
 	k0_text_kernel<<<(u32) (wb * m), 256, 0, d.stream>>>(p.msa, p.pitch, m, n, W, wb, p.RK, p.start, p.rowlen, p.T, p.col, p.N);

@@ -60,7 +60,6 @@ struct Pipeline {
 	int seg_status = 0; // 0 ok, 1 "no segmentation"
 
 	void free_all();
-	void free_index();
 };
 
 // phases (each enqueues on p.dev.stream; those that need a host decision synchronise)
@@ -73,11 +72,10 @@ void k2_compute_f(Pipeline &p);
 void k3_segment(Pipeline &p);
 void k4_graph(Pipeline &p, Graph &g, bool want_node_of);
 
-template <typename T> static inline T *dmalloc(u64 count) {
-	T *p = nullptr;
-	FBG_CUDA(cudaMalloc(&p, (count ? count : 1) * sizeof(T)));
-	return p;
+// bytes of the persistent arena one m x n MSA can need (N <= m*n + m + 1)
+static inline u64 persistent_need(u64 m, u64 n) {
+	u64 pitch = round_up(n, 32), W = pitch / 32, N = m * n + m + 1;
+	return m * pitch + 16 * W * m + 12 * (m + 1) + (N + 64) + 5 * 4 * (N + 1) + 6 * 4 * (n + 2) + 64 * 256;
 }
-template <typename T> static inline void dfree(T *&p) { if (p) cudaFree(p); p = nullptr; }
 
 } // namespace fbg

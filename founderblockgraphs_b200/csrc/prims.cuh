@@ -39,6 +39,25 @@ struct Dev {
 		if (arena_top > arena_peak) arena_peak = arena_top;
 		return reinterpret_cast<T *>(arena + off);
 	}
+	// second bump arena for the arrays that live as long as one MSA (text, SA, ISA, LCP, f, ...):
+	// grown, never shrunk, so a context that builds graph after graph makes no cudaMalloc calls
+	u8 *pers = nullptr;
+	u64 pers_cap = 0, pers_top = 0;
+	void reserve_pers(u64 bytes) {
+		if (bytes <= pers_cap) return;
+		if (pers) FBG_CUDA(cudaFree(pers));
+		pers = nullptr; pers_cap = 0;
+		FBG_CUDA(cudaMalloc(&pers, bytes));
+		pers_cap = bytes;
+	}
+	template <typename T> T *palloc(u64 count) {
+		u64 off = round_up(pers_top, 256);
+		u64 need = off + (count ? count : 1) * sizeof(T);
+		if (need > pers_cap)
+			throw cuda_error("persistent device arena exhausted: need " + std::to_string(need) + " of " + std::to_string(pers_cap));
+		pers_top = need;
+		return reinterpret_cast<T *>(pers + off);
+	}
 	u64 mark() const { return arena_top; }
 	void release(u64 m) { arena_top = m; }
 
@@ -77,6 +96,8 @@ struct Dev {
 		recs.clear(); pool.clear();
 		if (arena) cudaFree(arena);
 		arena = nullptr; arena_cap = 0;
+		if (pers) cudaFree(pers);
+		pers = nullptr; pers_cap = 0; pers_top = 0;
 	}
 };
 

@@ -33,19 +33,68 @@ __global__ void k3_scatter_u_kernel(const u32 *__restrict__ f, u64 n, u32 *__res
 // The chain only ever looks back about one segment length, so the last DP_RING values
 // live in shared memory (slot x & (DP_RING-1)); a slot is trusted while no column that
 // aliases it can have been written: x + DP_RING > F + 31.  Older values come from HBM.
-constexpr u32 DP_RING = 8192;
+// Inputs (U / v, f) are staged DP_CH columns at a time with coalesced loads, so the chain
+// itself never waits on an HBM round trip.
+constexpr u32 DP_RING = 4096;
+constexpr u32 DP_CH = 1024;
+
+// Walks a predecessor chain backwards through chunks staged in shared memory; every lane
+// follows the same chain, lane 0 records it.  STEP(b, j): false = stop, else sets the value
+// to record and the next j.
+template <class STEP> __device__ __forceinline__ u64 dp_chase(const u32 *link, u64 j, u64 nb, u32 *rev, u32 *stage, STEP step) {
+	const u32 l = lane_id();
+	__threadfence_block();
+	for (;;) {
+		u64 cb = j + 1 >= DP_CH ? j + 1 - DP_CH : 0;
+		__syncwarp();
+		for (u32 i = l; i < DP_CH && cb + i <= j; i += 32) stage[i] = __ldcg(&link[cb + i]);
+		__syncwarp();
+		bool done = false;
+		for (;;) {
+			u32 rec; u64 nj;
+			if (!step(stage[j - cb], rec, nj)) { done = true; break; }
+			if (l == 0) rev[nb] = rec;
+			nb++;
+			j = nj;
+			if (j < cb) break;
+		}
+		if (done) break;
+	}
+	return nb;
+}
+
+// bnd[a] = rev[nb-1-a]; nb read from the device word the DP kernel left
+__global__ void k3_reverse_kernel(const u32 *__restrict__ rev, const u64 *__restrict__ out, u32 *__restrict__ bnd) {
+	u64 nb = out[0];
+	for (u64 a = (u64) blockIdx.x * blockDim.x + threadIdx.x; a < nb; a += (u64) gridDim.x * blockDim.x) bnd[a] = rev[nb - 1 - a];
+}
 
 // single warp. mml/bt have n+1 entries. out[0] = nb, out[1] = mml[n]
-__global__ void __launch_bounds__(32) k3_elastic_dp_kernel(const u32 *__restrict__ f, const u32 *__restrict__ U, u64 n, u32 *mml, u32 *bt, u32 *rev, u32 *bnd, u64 *out) {
-	__shared__ u32 ring[DP_RING];
+__global__ void __launch_bounds__(32) k3_elastic_dp_kernel(const u32 *__restrict__ f, const u32 *__restrict__ U, u64 n, u32 *mml, u32 *bt, u32 *rev, u64 *out) {
+	__shared__ u32 ring[DP_RING];   // mml
+	__shared__ u32 fring[DP_RING];  // f
+	__shared__ u32 uch[DP_CH];      // U[base .. base+DP_CH)
 	const u32 l = lane_id();
 	const u32 INV = (u32) n + 1;
 	if (l == 0) { mml[0] = 0; bt[0] = 0; ring[0] = 0; }
-	__syncwarp();
-	u64 F = 1;
+	u64 base = 0, F = 1;
+	bool need_stage = true;
 	while (F <= n) {
+		if (need_stage || F + 32 > base + DP_CH) {
+			base = need_stage ? 0 : F;
+			need_stage = false;
+			__threadfence_block();
+			__syncwarp();
+#pragma unroll 8
+			for (u32 i = l; i < DP_CH; i += 32) {
+				u64 x = base + i;
+				uch[i] = x <= n ? U[x] : 0u;
+				fring[x & (DP_RING - 1)] = x < n ? f[x] : 0u;
+			}
+			__syncwarp();
+		}
 		u64 j = F + l;
-		u32 uj = j <= n ? U[j] : 0;
+		u32 uj = j <= n ? uch[j - base] : 0;
 		bool ready = j <= n && (uj == 0 || (u64) uj - 1 < F);
 		u32 rb = __ballot_sync(0xffffffffu, ready);
 		u32 r = rb == 0xffffffffu ? 32u : (u32) (__ffs(~rb) - 1);
@@ -56,7 +105,7 @@ __global__ void __launch_bounds__(32) k3_elastic_dp_kernel(const u32 *__restrict
 				for (;;) {
 					u64 dd = j - x;
 					if (dd > best) break;
-					u64 ex = (u64) f[x] + 1;
+					u64 ex = (u64) ((x + DP_RING >= base + DP_CH) ? fring[x & (DP_RING - 1)] : f[x]) + 1;
 					u32 mx = (x + DP_RING > F + 31) ? ring[x & (DP_RING - 1)] : ld_vol(&mml[x]);
 					if (ex <= j && mx <= (u32) n) {
 						if (dd > mx) { best = (u32) dd; bx = (u32) x; break; }      // B candidate, ties go to B
@@ -70,23 +119,17 @@ __global__ void __launch_bounds__(32) k3_elastic_dp_kernel(const u32 *__restrict
 			mml[j] = best; bt[j] = bx;
 			ring[j & (DP_RING - 1)] = best;
 		}
-		__threadfence_block();
 		__syncwarp();
 		F += r;
 	}
 	// backtrack, fbg.cpp:2026-2039
-	if (l == 0) {
-		u64 nb = 0, j = n;
-		rev[nb++] = (u32) n;
-		while (true) {
-			u32 b = ld_vol(&bt[j]);
-			if (b == 0 || b == U32_MAX) break;
-			rev[nb++] = b - 1;
-			j = b;
-		}
-		for (u64 a = 0; a < nb; a++) bnd[a] = rev[nb - 1 - a];
-		out[0] = nb; out[1] = ld_vol(&mml[n]);
-	}
+	if (l == 0) rev[0] = (u32) n;
+	u64 nb = dp_chase(bt, n, 1, rev, uch, [](u32 b, u32 &rec, u64 &nj) {
+		if (b == 0 || b == U32_MAX) return false;
+		rec = b - 1; nj = b;
+		return true;
+	});
+	if (l == 0) { out[0] = nb; out[1] = ld_vol(&mml[n]); }
 }
 
 // ------------------------------------------------------------ non-elastic
@@ -120,13 +163,24 @@ __global__ void k3_v_sequential_kernel(const u32 *__restrict__ f, u64 n, const u
 }
 
 // single warp wavefront over fbg.cpp:622-643; out[0]=nb, out[1]=s[n-1], out[2]=status
-__global__ void __launch_bounds__(32) k3_nonelastic_dp_kernel(const u32 *__restrict__ v, u64 n, u32 *s, u32 *prev, u32 *rev, u32 *bnd, u64 *out) {
+__global__ void __launch_bounds__(32) k3_nonelastic_dp_kernel(const u32 *__restrict__ v, u64 n, u32 *s, u32 *prev, u32 *rev, u64 *out) {
 	__shared__ u32 ring[DP_RING];
+	__shared__ u32 vch[DP_CH];
 	const u32 l = lane_id();
-	u64 F = 0;
+	u64 F = 0, base = 0;
+	bool need_stage = true;
 	while (F < n) {
+		if (need_stage || F + 32 > base + DP_CH) {
+			base = F;
+			need_stage = false;
+			__threadfence_block();
+			__syncwarp();
+#pragma unroll 8
+			for (u32 i = l; i < DP_CH; i += 32) vch[i] = base + i < n ? v[base + i] : 0u;
+			__syncwarp();
+		}
 		u64 j = F + l;
-		u32 vj = j < n ? v[j] : 0;
+		u32 vj = j < n ? vch[j - base] : 0;
 		bool ready = j < n && (vj > j || vj <= F);
 		u32 rb = __ballot_sync(0xffffffffu, ready);
 		u32 r = rb == 0xffffffffu ? 32u : (u32) (__ffs(~rb) - 1);
@@ -149,29 +203,23 @@ __global__ void __launch_bounds__(32) k3_nonelastic_dp_kernel(const u32 *__restr
 			s[j] = sj; prev[j] = pj;
 			ring[j & (DP_RING - 1)] = sj;
 		}
-		__threadfence_block();
 		__syncwarp();
 		F += r;
 	}
-	if (l == 0) {
-		u32 sc = ld_vol(&s[n - 1]);
-		out[1] = sc;
-		if (sc == (u32) n + 1) { out[0] = 0; out[2] = 1; return; }
-		u64 nb = 0, j = n - 1;
-		rev[nb++] = (u32) j;
-		for (;;) {
-			u32 pv = ld_vol(&prev[j]);
-			if (pv == 0) break;
-			rev[nb++] = pv - 1;
-			j = pv - 1;
-		}
-		for (u64 a = 0; a < nb; a++) bnd[a] = rev[nb - 1 - a];
-		out[0] = nb; out[2] = 0;
-	}
+	__threadfence_block();
+	u32 sc = ld_vol(&s[n - 1]);
+	if (sc == (u32) n + 1) { if (l == 0) { out[0] = 0; out[1] = sc; out[2] = 1; } return; }
+	if (l == 0) rev[0] = (u32) (n - 1);
+	u64 nb = dp_chase(prev, n - 1, 1, rev, vch, [](u32 pv, u32 &rec, u64 &nj) {
+		if (pv == 0) return false;
+		rec = pv - 1; nj = (u64) pv - 1;
+		return true;
+	});
+	if (l == 0) { out[0] = nb; out[1] = sc; out[2] = 0; }
 }
 
 // fbg.cpp:827-865 (greedy, not optimal by design); sequential by construction
-__global__ void k3_greedy_dp_kernel(const u32 *__restrict__ v, u64 n, u32 *s, u32 *prev, u32 *rev, u32 *bnd, u64 *out) {
+__global__ void k3_greedy_dp_kernel(const u32 *__restrict__ v, u64 n, u32 *s, u32 *prev, u32 *rev, u64 *out) {
 	if (blockIdx.x || threadIdx.x) return;
 	const u64 INV = n + 1;
 	// size_t arithmetic of the reference, including its wrap-around on prev = n+1
@@ -204,15 +252,14 @@ __global__ void k3_greedy_dp_kernel(const u32 *__restrict__ v, u64 n, u32 *s, u3
 	u64 nb = 0, j = n - 1;
 	rev[nb++] = (u32) j;
 	while (prev[j] != 0) { rev[nb++] = prev[j] - 1; j = prev[j] - 1; }
-	for (u64 a = 0; a < nb; a++) bnd[a] = rev[nb - 1 - a];
 	out[0] = nb; out[2] = 0;
 }
 
 void k3_segment(Pipeline &p) {
 	Dev &d = p.dev;
 	const u64 n = p.n;
-	if (!p.bnd) p.bnd = dmalloc<u32>(n + 2);
-	if (!p.dp_a) { p.dp_a = dmalloc<u32>(n + 2); p.dp_b = dmalloc<u32>(n + 2); p.dp_v = dmalloc<u32>(n + 2); }
+	if (!p.bnd) p.bnd = p.dev.palloc<u32>(n + 2);
+	if (!p.dp_a) { p.dp_a = p.dev.palloc<u32>(n + 2); p.dp_b = p.dev.palloc<u32>(n + 2); p.dp_v = p.dev.palloc<u32>(n + 2); }
 	u64 mk = d.mark();
 	u32 *rev = d.alloc<u32>(n + 2);
 	u64 *out = p.scalars + 16;
@@ -227,7 +274,8 @@ void k3_segment(Pipeline &p) {
 		d.end((double) n * 8.0);
 		device_scan<OpMaxU32, false>(d, U, U, n + 1);
 		d.begin(K_DP);
-		k3_elastic_dp_kernel<<<1, 32, 0, d.stream>>>(p.f, U, n, p.dp_a, p.dp_b, rev, p.bnd, out);
+		k3_elastic_dp_kernel<<<1, 32, 0, d.stream>>>(p.f, U, n, p.dp_a, p.dp_b, rev, out);
+		k3_reverse_kernel<<<NUM_SMS, 256, 0, d.stream>>>(rev, out, p.bnd);
 		FBG_LAUNCH_CHECK();
 		d.end((double) n * 24.0);
 	} else {
@@ -244,9 +292,10 @@ void k3_segment(Pipeline &p) {
 		k3_v_from_counts_kernel<<<g, 256, 0, d.stream>>>(cnt, n, p.dp_v);
 		k3_v_sequential_kernel<<<1, 32, 0, d.stream>>>(p.f, n, nonmono, p.dp_v);
 		if (p.opt.gap_limit == 1)
-			k3_nonelastic_dp_kernel<<<1, 32, 0, d.stream>>>(p.dp_v, n, p.dp_a, p.dp_b, rev, p.bnd, out);
+			k3_nonelastic_dp_kernel<<<1, 32, 0, d.stream>>>(p.dp_v, n, p.dp_a, p.dp_b, rev, out);
 		else
-			k3_greedy_dp_kernel<<<1, 32, 0, d.stream>>>(p.dp_v, n, p.dp_a, p.dp_b, rev, p.bnd, out);
+			k3_greedy_dp_kernel<<<1, 32, 0, d.stream>>>(p.dp_v, n, p.dp_a, p.dp_b, rev, out);
+		k3_reverse_kernel<<<NUM_SMS, 256, 0, d.stream>>>(rev, out, p.bnd);
 		FBG_LAUNCH_CHECK();
 		d.end((double) n * 24.0);
 		d.note_launches(K_DP, 2);

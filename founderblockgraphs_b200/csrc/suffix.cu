@@ -14,6 +14,7 @@
 // BWT[k-1]) by direct comparison and filled with PLCP[p] = max_{q<=p,irr}(PLCP[q]+q) - p.
 #include "pipeline.cuh"
 #include "tilesort.cuh"
+#include <cstdlib>
 
 namespace fbg {
 
@@ -252,7 +253,7 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 			u32 hb_rel = hb1 - 1 - first;
 			k = ((u64) hb_rel << (32 + LOGC)) | ((u64) r2[w0 + idx] << LOGC) | (u64) (idx - first);
 		}
-		key[idx] = k;
+		key[ts_sw(idx)] = k;
 	}
 	__syncthreads();
 
@@ -268,7 +269,7 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 		u32 v = 0;
 		if (s < cnt) {
 			bool sh = s == 0;
-			if (!sh) sh = (key[s] >> LOGC) != (key[s - 1] >> LOGC);
+			if (!sh) sh = (key[ts_sw(s)] >> LOGC) != (key[ts_sw(s - 1)] >> LOGC);
 			if (sh) v = s + 1;
 		}
 		u32 inc = warp_incl_max(v);
@@ -288,11 +289,11 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 	for (int i = 0; i < ITEMS; i++) {
 		u32 s = w * WCH + i * 32 + l;
 		if (s < cnt) {
-			u64 k = key[s];
+			u64 k = key[ts_sw(s)];
 			u32 hs = (hsv[i] > wpre ? hsv[i] : wpre) - 1;
 			u32 hb = (u32) (k >> (32 + LOGC));
 			u32 irel = (u32) k & (u32) (CAP - 1);
-			bool last = (s + 1 >= cnt) || ((key[s + 1] >> LOGC) != (k >> LOGC));
+			bool last = (s + 1 >= cnt) || ((key[ts_sw(s + 1)] >> LOGC) != (k >> LOGC));
 			u32 nr = lr[g0 + hb] + (hs - hb);
 			u32 p = lp[g0 + irel];
 			R[p] = nr;
@@ -341,8 +342,8 @@ static void compact_lists(Dev &d, const u8 *cls, const u32 *lp, const u32 *lr, u
 void k1_suffix_array(Pipeline &p) {
 	Dev &d = p.dev;
 	const u64 N = p.N;
-	p.ISA = dmalloc<u32>(N + 1);
-	p.SA = dmalloc<u32>(N + 1);
+	p.ISA = p.dev.palloc<u32>(N + 1);
+	p.SA = p.dev.palloc<u32>(N + 1);
 	u64 mk = d.mark();
 
 	// alphabet: dense order-preserving codes (sentinel 0 is always present)
@@ -391,7 +392,10 @@ void k1_suffix_array(Pipeline &p) {
 	int key_bits = K * b;
 	int sc = 0;           // current S list
 	p.sa_rounds = 0;
+	const bool debug = getenv("FBG_DEBUG") != nullptr;
 	for (;;) {
+		if (debug) fprintf(stderr, "[fbg] K1 round %d: depth %llu, S list %llu (largest bucket %u), B list %llu\n", p.sa_rounds,
+		                   (unsigned long long) (p.sa_rounds ? h / 2 : 0), (unsigned long long) nS, maxb, (unsigned long long) nB);
 		FBG_CUDA(cudaMemsetAsync(p.scalars + 8, 0, 4 * sizeof(u64), d.stream));
 		// ---- S path
 		if (nS) {
@@ -505,8 +509,8 @@ __global__ void k1_nlcp_kernel(const u32 *__restrict__ SA, const u32 *__restrict
 void k1_lcp(Pipeline &p) {
 	Dev &d = p.dev;
 	const u64 N = p.N;
-	p.PLCP = dmalloc<u32>(N + 1);
-	p.NLCP = dmalloc<u32>(N + 1);
+	p.PLCP = p.dev.palloc<u32>(N + 1);
+	p.NLCP = p.dev.palloc<u32>(N + 1);
 	u64 mk = d.mark();
 	u32 *flag = d.alloc<u32>(N), *pos = d.alloc<u32>(N), *ia = d.alloc<u32>(N), *ib = d.alloc<u32>(N);
 	u32 *total = reinterpret_cast<u32 *>(p.scalars + 8);

@@ -21,11 +21,18 @@
 
 namespace fbg {
 
+// Shared-memory placement of key i: the low four index bits are XORed with bits 3..6.
+// Whatever the stride of a pass (1, 2, 4, ... keys between the lanes of a half-warp, eight
+// keys per lane), the sixteen 8-byte accesses of a half-warp then fall into sixteen
+// different bank pairs.  A GF(2)-linear bijection: ts_sw(a ^ b) == ts_sw(a) ^ ts_sw(b).
+FBG_HD uint32_t ts_sw(uint32_t i) { return i ^ ((i >> 3) & 15u); }
+
 FBG_HD void ts_cx(uint64_t &a, uint64_t &b, bool up) {
 	// ascending (up): a <= b afterwards
-	uint64_t lo = a < b ? a : b, hi = a < b ? b : a;
-	a = up ? lo : hi;
-	b = up ? hi : lo;
+	const bool sw = (a > b) == up;
+	const uint64_t t = a;
+	a = sw ? b : a;
+	b = sw ? t : b;
 }
 
 // Stages jtop, jtop/2, .., jtop >> (NST-1) of phase k for group g.  A group is
@@ -38,7 +45,7 @@ template <int NST> FBG_HD void ts_pass_group(uint64_t *key, uint32_t k, uint32_t
 	const bool up = (base & k) == 0;
 	uint64_t v[E];
 #pragma unroll
-	for (int c = 0; c < E; c++) v[c] = key[base + (uint32_t) c * low];
+	for (int c = 0; c < E; c++) v[c] = key[ts_sw(base + (uint32_t) c * low)];
 #pragma unroll
 	for (int st = NST - 1; st >= 0; st--) {
 #pragma unroll
@@ -46,7 +53,7 @@ template <int NST> FBG_HD void ts_pass_group(uint64_t *key, uint32_t k, uint32_t
 			if ((c & (1 << st)) == 0) ts_cx(v[c], v[c | (1 << st)], up);
 	}
 #pragma unroll
-	for (int c = 0; c < E; c++) key[base + (uint32_t) c * low] = v[c];
+	for (int c = 0; c < E; c++) key[ts_sw(base + (uint32_t) c * low)] = v[c];
 }
 
 // Phases k = 2, 4, 8 on the 8 consecutive keys [8g, 8g+8).
@@ -54,7 +61,7 @@ FBG_HD void ts_first_phases_group(uint64_t *key, uint32_t g) {
 	const uint32_t base = g << 3;
 	uint64_t v[8];
 #pragma unroll
-	for (int c = 0; c < 8; c++) v[c] = key[base + c];
+	for (int c = 0; c < 8; c++) v[c] = key[ts_sw(base + c)];
 #pragma unroll
 	for (int k = 2; k <= 8; k <<= 1) {
 #pragma unroll
@@ -65,7 +72,7 @@ FBG_HD void ts_first_phases_group(uint64_t *key, uint32_t g) {
 		}
 	}
 #pragma unroll
-	for (int c = 0; c < 8; c++) key[base + c] = v[c];
+	for (int c = 0; c < 8; c++) key[ts_sw(base + c)] = v[c];
 }
 
 // Schedule of one phase k >= 16: stages log2(k)-1 .. 0 in passes of <= 3.  The
@@ -103,8 +110,9 @@ template <int CAP, int THREADS> struct TsDevicePass {
 	}
 };
 
-// Sorts key[0..CAP) ascending.  CAP is a power of two >= 16; all THREADS threads of
-// the CTA call it; key[] must be visible (barrier) before the call and is visible after.
+// Sorts the tile ascending: key i lives at key[ts_sw(i)] before and after.  CAP is a power
+// of two >= 128; all THREADS threads of the CTA call it; the keys must be visible (barrier)
+// before the call and are visible after.
 template <int CAP, int THREADS> __device__ __forceinline__ void tile_bitonic_sort(uint64_t *key) {
 	TsDevicePass<CAP, THREADS> p{key};
 	ts_schedule(CAP, p);
