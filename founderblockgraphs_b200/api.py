@@ -22,7 +22,7 @@ CLI_PATH = os.path.join(_PKG, "founderblockgraph")
 
 FBG_OK, FBG_ERR_CUDA, FBG_ERR_ARG, FBG_ERR_NOSEG, FBG_ERR_UNSUPPORTED = 0, -1, -2, -3, -4
 FBG_NO_NODE = 0xFFFFFFFF
-N_KERNELS = 11
+N_KERNELS = 12
 
 _u8p = C.POINTER(C.c_uint8)
 _u32p = C.POINTER(C.c_uint32)
@@ -48,6 +48,7 @@ EXPORTS = [
     "fbg_upload_msa_device", "fbg_build_index", "fbg_compute_f", "fbg_segment", "fbg_get_boundaries", "fbg_build_graph",
     "fbg_graph_free", "fbg_run", "fbg_run_device", "fbg_get_stream", "fbg_get_stats", "fbg_reset_stats", "fbg_get_f", "fbg_get_text",
     "fbg_get_sa", "fbg_get_isa", "fbg_get_lcp", "fbg_get_dp", "fbg_radix_sort_pairs", "fbg_radix_sort_bench", "fbg_write_xgfa",
+    "fbg_dist_unique_id", "fbg_dist_init", "fbg_dist_shutdown", "fbg_plan_key_ranges", "fbg_plan_columns",
 ]
 
 _lib = None
@@ -103,8 +104,44 @@ def load_library():
     lib.fbg_radix_sort_pairs.argtypes = [C.c_void_p, _u64p, _u32p, C.c_uint64, C.c_int, C.c_int]
     lib.fbg_radix_sort_bench.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double)]
     lib.fbg_write_xgfa.argtypes = [C.c_char_p, C.c_void_p, C.c_uint64, C.c_uint64, _u64p, C.POINTER(FbgGraph), C.c_int, C.POINTER(C.c_char_p)]
+    lib.fbg_dist_unique_id.argtypes = [_u8p]
+    lib.fbg_dist_init.argtypes = [C.c_void_p, C.c_int, C.c_int, _u8p]
+    lib.fbg_dist_shutdown.argtypes = [C.c_void_p]
+    lib.fbg_plan_key_ranges.argtypes = [_u32p, C.c_uint32, C.c_int, _u32p]
+    lib.fbg_plan_columns.argtypes = [C.c_uint64, C.c_int, C.c_int, _u64p, _u64p]
     _lib = lib
     return lib
+
+
+def dist_unique_id() -> bytes:
+    """ncclGetUniqueId through the library (rank 0); ship the bytes to the other ranks."""
+    lib = load_library()
+    buf = (C.c_uint8 * 128)()
+    rc = lib.fbg_dist_unique_id(buf)
+    if rc != FBG_OK:
+        raise FbgError(rc, lib.fbg_last_error(None).decode())
+    return bytes(buf)
+
+
+def plan_key_ranges(hist: np.ndarray, world: int) -> np.ndarray:
+    """Which k-mer histogram bins each rank sorts (host plan of the sharded K1)."""
+    lib = load_library()
+    h = np.ascontiguousarray(hist, np.uint32)
+    out = np.zeros(world + 1, np.uint32)
+    rc = lib.fbg_plan_key_ranges(h.ctypes.data_as(_u32p), len(h), world, out.ctypes.data_as(_u32p))
+    if rc != FBG_OK:
+        raise FbgError(rc, "bad arguments")
+    return out
+
+
+def plan_columns(n: int, world: int, rank: int):
+    """Column range [x0, x1) of f(x) that `rank` computes in a sharded build."""
+    lib = load_library()
+    x0, x1 = C.c_uint64(), C.c_uint64()
+    rc = lib.fbg_plan_columns(n, world, rank, C.byref(x0), C.byref(x1))
+    if rc != FBG_OK:
+        raise FbgError(rc, "bad arguments")
+    return int(x0.value), int(x1.value)
 
 
 def kernel_names():
@@ -143,6 +180,14 @@ class Context:
         if rc != FBG_OK:
             raise FbgError(rc, self.lib.fbg_last_error(None).decode())
         self._graph = None
+
+    def dist_init(self, rank: int, world: int, unique_id: bytes):
+        """Joins the NCCL communicator of a sharded build (collective over all ranks)."""
+        buf = (C.c_uint8 * 128).from_buffer_copy(unique_id)
+        self._check(self.lib.fbg_dist_init(self.h, rank, world, buf))
+
+    def dist_shutdown(self):
+        self._check(self.lib.fbg_dist_shutdown(self.h))
 
     def close(self):
         if self.h:

@@ -32,7 +32,7 @@ void Pipeline::free_all() {
 
 } // namespace fbg
 
-static const char *KNAMES[K_COUNT] = {"pack", "kmer", "radix_hist", "radix_scatter", "scan", "doubling_aux", "lcp", "fcol", "dp", "graph", "tile_sort"};
+static const char *KNAMES[K_COUNT] = {"pack", "kmer", "radix_hist", "radix_scatter", "scan", "doubling_aux", "lcp", "fcol", "dp", "graph", "tile_sort", "comm"};
 
 #define FBG_TRY(ctx) try {
 #define FBG_CATCH(ctx)                                                         \
@@ -91,6 +91,7 @@ void fbg_ctx_destroy(fbg_ctx *ctx) {
 	if (!ctx) return;
 	cudaSetDevice(ctx->p.dev.device);
 	cudaStreamSynchronize(ctx->p.dev.stream);
+	if (ctx->p.dist.comm) { ctx->p.dist.api.CommDestroy(ctx->p.dist.comm); ctx->p.dist.comm = nullptr; }
 	ctx->p.free_all();
 	if (ctx->p.scalars) cudaFree(ctx->p.scalars);
 	if (ctx->p.h_scalars) cudaFreeHost(ctx->p.h_scalars);
@@ -245,6 +246,60 @@ int fbg_run(fbg_ctx *ctx, const uint8_t *rows, uint64_t m, uint64_t n, int want_
 }
 int fbg_run_device(fbg_ctx *ctx, const void *rows, uint64_t m, uint64_t n, int want_paths, uint64_t *n_blocks, uint64_t *score, fbg_graph *out) {
 	return run_common(ctx, rows, m, n, true, want_paths, n_blocks, score, out);
+}
+
+int fbg_dist_unique_id(uint8_t *out128) {
+	if (!out128) return FBG_ERR_ARG;
+	static NcclApi api;
+	if (!api.load(g_create_err)) return FBG_ERR_UNSUPPORTED;
+	NcclUniqueId id;
+	int rc = api.GetUniqueId(&id);
+	if (rc != 0) { g_create_err = std::string("ncclGetUniqueId: ") + api.GetErrorString(rc); return FBG_ERR_CUDA; }
+	std::memcpy(out128, id.internal, 128);
+	return FBG_OK;
+}
+
+int fbg_dist_init(fbg_ctx *ctx, int rank, int world, const uint8_t *id128) {
+	if (!ctx || !id128 || world < 1 || rank < 0 || rank >= world) { if (ctx) ctx->err = "bad rank / world size"; return FBG_ERR_ARG; }
+	FBG_TRY(ctx)
+	Dist &ds = ctx->p.dist;
+	if (ds.comm) { ctx->err = "context already joined a communicator"; return FBG_ERR_ARG; }
+	FBG_CUDA(cudaSetDevice(ctx->p.dev.device));
+	if (world == 1) { ds.rank = 0; ds.world = 1; return FBG_OK; }
+	if (!ds.api.load(ctx->err)) return FBG_ERR_UNSUPPORTED;
+	NcclUniqueId id;
+	std::memcpy(id.internal, id128, 128);
+	ds.check(ds.api.CommInitRank(&ds.comm, world, id, rank), "ncclCommInitRank");
+	ds.rank = rank; ds.world = world;
+	ctx->p.have_index = ctx->p.have_f = ctx->p.have_seg = false;
+	FBG_CATCH(ctx)
+	return FBG_OK;
+}
+
+int fbg_dist_shutdown(fbg_ctx *ctx) {
+	if (!ctx) return FBG_ERR_ARG;
+	Dist &ds = ctx->p.dist;
+	if (ds.comm) {
+		cudaSetDevice(ctx->p.dev.device);
+		cudaStreamSynchronize(ctx->p.dev.stream);
+		ds.api.CommDestroy(ds.comm);
+		ds.comm = nullptr;
+	}
+	ds.rank = 0; ds.world = 1;
+	ctx->p.have_index = ctx->p.have_f = ctx->p.have_seg = false;
+	return FBG_OK;
+}
+
+int fbg_plan_key_ranges(const uint32_t *hist, uint32_t nbins, int world, uint32_t *bounds) {
+	if (!hist || !bounds || world < 1 || nbins == 0) return FBG_ERR_ARG;
+	plan_key_ranges(hist, nbins, world, bounds);
+	return FBG_OK;
+}
+
+int fbg_plan_columns(uint64_t n, int world, int rank, uint64_t *x0, uint64_t *x1) {
+	if (!x0 || !x1 || world < 1 || rank < 0 || rank >= world) return FBG_ERR_ARG;
+	plan_columns(n, world, rank, x0, x1);
+	return FBG_OK;
 }
 
 void *fbg_get_stream(fbg_ctx *ctx) { return ctx ? (void *) ctx->p.dev.stream : nullptr; }

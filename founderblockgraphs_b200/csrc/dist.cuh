@@ -1,0 +1,92 @@
+// dist.cuh -- the multi-GPU side of one build: one process per GPU, every context
+// joined to an NCCL communicator over NVLink/NVSwitch.
+//
+// Sharding of ONE MSA across G GPUs:
+//   K1  suffix sorting is sharded by k-mer key range: rank r sorts the suffixes whose
+//       leading k-mer falls in its range (whole buckets, so every later refinement
+//       stays local).  Ranks are global SA indices.  The rank array R is replicated;
+//       after every doubling round the replicas are merged with an all-reduce(max):
+//       ranks only ever grow, and a rank array entry is written by its owner alone.
+//   K2  f(x) is sharded by contiguous column ranges and merged with the same all-reduce.
+//   K0, LCP, K3, K4 run replicated (O(N) streaming passes).
+// NCCL is loaded with dlopen so that the single-GPU library has no link-time dependency
+// on it; the few entry points used are declared here with NCCL's own ABI.
+#pragma once
+#include "common.cuh"
+#include <dlfcn.h>
+#include <string>
+
+namespace fbg {
+
+struct NcclUniqueId { char internal[128]; };
+
+struct NcclApi {
+	void *lib = nullptr;
+	int (*GetUniqueId)(NcclUniqueId *) = nullptr;
+	int (*CommInitRank)(void **, int, NcclUniqueId, int) = nullptr;
+	int (*CommDestroy)(void *) = nullptr;
+	int (*AllReduce)(const void *, void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+	const char *(*GetErrorString)(int) = nullptr;
+
+	bool load(std::string &err) {
+		if (lib) return true;
+		for (const char *nm : {"libnccl.so.2", "libnccl.so"}) {
+			lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+			if (lib) break;
+		}
+		if (!lib) { err = std::string("cannot load NCCL: ") + dlerror(); return false; }
+		GetUniqueId = (decltype(GetUniqueId)) dlsym(lib, "ncclGetUniqueId");
+		CommInitRank = (decltype(CommInitRank)) dlsym(lib, "ncclCommInitRank");
+		CommDestroy = (decltype(CommDestroy)) dlsym(lib, "ncclCommDestroy");
+		AllReduce = (decltype(AllReduce)) dlsym(lib, "ncclAllReduce");
+		GetErrorString = (decltype(GetErrorString)) dlsym(lib, "ncclGetErrorString");
+		if (!GetUniqueId || !CommInitRank || !CommDestroy || !AllReduce || !GetErrorString) { err = "NCCL library lacks an expected symbol"; return false; }
+		return true;
+	}
+};
+
+constexpr int NCCL_UINT32 = 3, NCCL_UINT64 = 5, NCCL_SUM = 0, NCCL_MAX = 2;
+
+struct Dist {
+	int rank = 0, world = 1;
+	void *comm = nullptr;
+	NcclApi api;
+
+	void check(int rc, const char *what) const {
+		if (rc != 0) throw cuda_error(std::string(what) + " failed: " + (api.GetErrorString ? api.GetErrorString(rc) : "NCCL error"));
+	}
+	// in-place
+	void allreduce_max_u32(u32 *buf, u64 count, cudaStream_t s) const {
+		if (world > 1 && count) check(api.AllReduce(buf, buf, count, NCCL_UINT32, NCCL_MAX, comm, s), "ncclAllReduce(max,u32)");
+	}
+	void allreduce_sum_u64(u64 *buf, u64 count, cudaStream_t s) const {
+		if (world > 1 && count) check(api.AllReduce(buf, buf, count, NCCL_UINT64, NCCL_SUM, comm, s), "ncclAllReduce(sum,u64)");
+	}
+};
+
+// ---- host-side plans (pure functions; exported through the C ABI for the CPU tests)
+
+// Key-range plan: hist[b] = number of suffixes whose k-mer falls in bin b (bins ordered like
+// the keys).  bounds[r] .. bounds[r+1] are rank r's bins; cut points are the first bin at
+// which the running count reaches r/world of the total, so equal keys never straddle ranks.
+static inline void plan_key_ranges(const u32 *hist, u32 nbins, int world, u32 *bounds) {
+	u64 total = 0;
+	for (u32 b = 0; b < nbins; b++) total += hist[b];
+	bounds[0] = 0;
+	u64 run = 0;
+	u32 b = 0;
+	for (int r = 1; r < world; r++) {
+		u64 target = total / (u64) world * (u64) r + (total % (u64) world) * (u64) r / (u64) world;
+		while (b < nbins && run < target) run += hist[b++];
+		bounds[r] = b;
+	}
+	bounds[world] = nbins;
+}
+
+// Column-range plan of K2: rank r owns [x0, x1)
+static inline void plan_columns(u64 n, int world, int rank, u64 *x0, u64 *x1) {
+	*x0 = n / (u64) world * (u64) rank + (n % (u64) world) * (u64) rank / (u64) world;
+	*x1 = rank + 1 == world ? n : n / (u64) world * (u64) (rank + 1) + (n % (u64) world) * (u64) (rank + 1) / (u64) world;
+}
+
+} // namespace fbg

@@ -146,17 +146,29 @@ void k2_compute_f(Pipeline &p) {
 	u32 threads = gc.threads;
 	a.tpg = gc.tpg; a.groups = gc.groups;
 	a.x0 = 0; a.x1 = p.n;
+	const bool sharded = p.dist.world > 1;
+	if (sharded) {
+		// contiguous column range per GPU; f >= 0 everywhere, so the slices merge by max
+		plan_columns(p.n, p.dist.world, p.dist.rank, &a.x0, &a.x1);
+		FBG_CUDA(cudaMemsetAsync(p.f, 0, p.n * sizeof(u32), d.stream));
+	}
 	a.tricks_off = p.opt.disable_tricks ? 1 : 0;
 	a.has_ignore = p.opt.n_ignore > 0 ? 1 : 0;
 	size_t smem = (size_t) a.groups * mpad * (8 + 16 + 2);
 	FBG_CUDA(cudaFuncSetAttribute(k2_fcol_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-	u64 col_groups = (p.n + a.groups - 1) / a.groups;
+	u64 col_groups = (a.x1 - a.x0 + a.groups - 1) / a.groups;
+	if (col_groups == 0) col_groups = 1;
 	u64 max_grid = (u64) NUM_SMS * 8;
 	u32 grid = (u32) (col_groups < max_grid ? col_groups : max_grid);
 	d.begin(K_FCOL);
 	k2_fcol_kernel<<<grid, threads, smem, d.stream>>>(a);
 	FBG_LAUNCH_CHECK();
-	d.end((double) p.m * p.n * 16.0);
+	d.end((double) p.m * (double) (a.x1 - a.x0) * 16.0);
+	if (sharded) {
+		d.begin(K_COMM);
+		p.dist.allreduce_max_u32(p.f, p.n, d.stream);
+		d.end((double) p.n * 8.0);
+	}
 	p.have_f = true;
 }
 

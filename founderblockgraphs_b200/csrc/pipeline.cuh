@@ -15,6 +15,7 @@
 //   bnd    [nb]  u32    inclusive block end columns (elastic: last = n)
 #pragma once
 #include "prims.cuh"
+#include "dist.cuh"
 
 namespace fbg {
 
@@ -40,6 +41,7 @@ struct Graph {
 
 struct Pipeline {
 	Dev dev;
+	Dist dist;
 	Options opt;
 	u64 m = 0, n = 0, pitch = 0, W = 0, N = 0;
 	u8 *msa = nullptr;

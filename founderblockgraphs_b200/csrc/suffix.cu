@@ -14,7 +14,9 @@
 // BWT[k-1]) by direct comparison and filled with PLCP[p] = max_{q<=p,irr}(PLCP[q]+q) - p.
 #include "pipeline.cuh"
 #include "tilesort.cuh"
+#include "dist.cuh"
 #include <cstdlib>
+#include <vector>
 
 namespace fbg {
 
@@ -34,9 +36,17 @@ constexpr int KM_THREADS = 256;
 constexpr int KM_ITEMS = 8;
 constexpr int KM_TILE = KM_THREADS * KM_ITEMS;
 
-__global__ void __launch_bounds__(KM_THREADS) k1_kmer_kernel(const u8 *__restrict__ T, u64 N, CodeTable tab, int K, int b, u64 *__restrict__ keys, u32 *__restrict__ vals) {
+// MODE 0: (key, position) of every suffix.  Modes 1-3 serve the key-range sharding of a
+// multi-GPU build (dist.cuh): 1 = histogram of the top KM_HBITS key bits, 2 = per-CTA count
+// of the keys whose bin is in [bin_lo, bin_hi), 3 = write those pairs, compacted in text order.
+constexpr int KM_HBITS = 16;
+struct KmerShard { u32 bin_lo, bin_hi; int hshift; const u64 *block_off; u32 *hist; u64 *block_cnt; };
+
+template <int MODE> __global__ void __launch_bounds__(KM_THREADS) k1_kmer_kernel(const u8 *__restrict__ T, u64 N, CodeTable tab, int K, int b, KmerShard sh,
+                                                                                 u64 *__restrict__ keys, u32 *__restrict__ vals) {
 	__shared__ u8 sc[KM_TILE + 64];
 	__shared__ u8 stab[256];
+	__shared__ u32 ssum[32];
 	stab[threadIdx.x] = tab.code[threadIdx.x];
 	__syncthreads();
 	const u64 base = (u64) blockIdx.x * KM_TILE;
@@ -49,11 +59,30 @@ __global__ void __launch_bounds__(KM_THREADS) k1_kmer_kernel(const u8 *__restric
 	u32 o = threadIdx.x * KM_ITEMS;
 	u64 key = 0;
 	for (int c = 0; c < K; c++) key = (key << b) | sc[o + c];
+	u64 kk[KM_ITEMS];
+	u32 mine = 0;
 #pragma unroll
 	for (int it = 0; it < KM_ITEMS; it++) {
 		u64 g = base + o + it;
-		if (g < N) { keys[g] = key; vals[g] = (u32) g; }
+		kk[it] = key;
+		if (MODE == 0) { if (g < N) { keys[g] = key; vals[g] = (u32) g; } }
+		else {
+			u32 bin = (u32) (key >> sh.hshift);
+			if (MODE == 1) { if (g < N) atomicAdd(&sh.hist[bin], 1u); }
+			else if (g < N && bin >= sh.bin_lo && bin < sh.bin_hi) mine |= 1u << it;
+		}
 		key = ((key << b) | sc[o + it + K]) & kmask;
+	}
+	if (MODE >= 2) {
+		u32 tot;
+		u32 ex = block_excl_scan<OpSumU32>((u32) __popc(mine), ssum, &tot);
+		if (MODE == 2) { if (threadIdx.x == 0) sh.block_cnt[blockIdx.x] = tot; }
+		else {
+			u64 q = sh.block_off[blockIdx.x] + ex;
+#pragma unroll
+			for (int it = 0; it < KM_ITEMS; it++)
+				if (mine >> it & 1u) { keys[q] = kk[it]; vals[q] = (u32) (base + o + it); q++; }
+		}
 	}
 }
 
@@ -86,7 +115,7 @@ __global__ void k1_heads_kernel(const u64 *__restrict__ keys, u64 na, int hi_shi
 
 // new rank = bucket rank + (sub-head index - bucket-head index); class by sub-bucket size
 __global__ void __launch_bounds__(256) k1_update_kernel(const u64 *__restrict__ keys, const u32 *__restrict__ vals, const u64 *__restrict__ HH, const u32 *__restrict__ HR,
-                                                        u64 na, int hi_shift, u32 *__restrict__ R, u32 *__restrict__ newr, u8 *__restrict__ cls, u32 *__restrict__ maxb) {
+                                                        u64 na, int hi_shift, u32 rank_off, u32 *__restrict__ R, u32 *__restrict__ newr, u8 *__restrict__ cls, u32 *__restrict__ maxb) {
 	__shared__ u32 smax[8];
 	u64 t = (u64) blockIdx.x * blockDim.x + threadIdx.x;
 	u32 small_size = 0;
@@ -94,7 +123,7 @@ __global__ void __launch_bounds__(256) k1_update_kernel(const u64 *__restrict__ 
 		u64 k = keys[t];
 		u64 hh = HH[t];
 		u32 hb = (u32) (hh >> 32), hs = (u32) hh;
-		u32 base = hi_shift < 64 ? (u32) (k >> hi_shift) : 0u;
+		u32 base = hi_shift < 64 ? (u32) (k >> hi_shift) : rank_off; // round 0: first global rank of this GPU's key range
 		u32 nr = base + (hs - hb);
 		u32 nh = (t + 1 < na) ? (u32) na - HR[na - 2 - t] : (u32) na; // HR scanned: 0 = no head after t
 		u32 size = nh - hs;
@@ -119,6 +148,30 @@ constexpr int CP_THREADS = 256;
 constexpr int CP_ITEMS = 16;
 constexpr int CP_TILE = CP_THREADS * CP_ITEMS;
 
+// Round 0 lays the S list out by text position instead of by rank: buckets are ordered by
+// their smallest member, so neighbouring tiles hold neighbouring MSA columns and the rank
+// look-ups R[p+h] / updates R[p] of consecutive tiles share 32-byte sectors (the S list only
+// needs every bucket contiguous, not any global order).
+//   A[p0] = size of the small bucket whose smallest member is p0 (stable sort: its head)
+__global__ void k1_bucket_size_kernel(const u64 *__restrict__ HH, const u32 *__restrict__ HR, const u32 *__restrict__ vals, const u8 *__restrict__ cls, u64 na, u32 *__restrict__ A) {
+	u64 t = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= na || cls[t] != CLS_SMALL || (u32) HH[t] != (u32) t) return;
+	u32 nh = (t + 1 < na) ? (u32) na - HR[na - 2 - t] : (u32) na;
+	A[vals[t]] = nh - (u32) t;
+}
+//   A exclusive-scanned: where each bucket starts in the S list
+__global__ void k1_ordered_write_kernel(const u64 *__restrict__ HH, const u32 *__restrict__ vals, const u32 *__restrict__ newr, const u8 *__restrict__ cls, u64 na,
+                                        const u32 *__restrict__ A, const u32 *__restrict__ R, u64 hnext, u64 N,
+                                        u32 *__restrict__ Slp, u32 *__restrict__ Slr, u32 *__restrict__ Sr2) {
+	u64 t = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= na || cls[t] != CLS_SMALL) return;
+	u32 hs = (u32) HH[t];
+	u32 q = A[vals[hs]] + ((u32) t - hs);
+	u32 p = vals[t];
+	u64 pn = (u64) p + hnext;
+	Slp[q] = p; Slr[q] = newr[t]; Sr2[q] = pn < N ? R[pn] : 0u;
+}
+
 __device__ __forceinline__ u64 cls_count16(uint4 v) {
 	// bytes equal to 1 -> low word, equal to 2 -> high word
 	u32 w[4] = {v.x, v.y, v.z, v.w};
@@ -132,12 +185,13 @@ __device__ __forceinline__ u64 cls_count16(uint4 v) {
 	return ((u64) b << 32) | s;
 }
 
-__global__ void __launch_bounds__(CP_THREADS) k1_cls_count_kernel(const u8 *__restrict__ cls, u64 na, u64 *__restrict__ partial) {
+__global__ void __launch_bounds__(CP_THREADS) k1_cls_count_kernel(const u8 *__restrict__ cls, u64 na, int skip_small, u64 *__restrict__ partial) {
 	__shared__ u64 sm[32];
 	u64 base = (u64) blockIdx.x * CP_TILE + (u64) threadIdx.x * CP_ITEMS;
 	u64 c = 0;
 	if (base + CP_ITEMS <= na) c = cls_count16(*reinterpret_cast<const uint4 *>(cls + base));
 	else for (u64 i = base; i < na; i++) { u8 v = cls[i]; c += v == CLS_SMALL ? 1ull : (v == CLS_BIG ? (1ull << 32) : 0ull); }
+	if (skip_small) c &= 0xFFFFFFFF00000000ull;
 	u64 tot;
 	block_excl_scan<OpSumU64>(c, sm, &tot);
 	if (threadIdx.x == 0) partial[blockIdx.x] = tot;
@@ -149,31 +203,45 @@ struct CompactOut {
 };
 
 // partial: exclusive-scanned per-tile (small | big << 32) counts; base: device word with
-// the offsets this call appends at (same packing), or null for 0.
+// the offsets this call appends at (same packing), or null for 0.  A warp owns 512
+// consecutive entries and walks them 32 at a time: coalesced reads, ballot/popc ranks,
+// compacted (hence nearly coalesced) writes.
 __global__ void __launch_bounds__(CP_THREADS) k1_cls_write_kernel(const u8 *__restrict__ cls, const u32 *__restrict__ lp, const u32 *__restrict__ lr, u64 na,
-                                                                  const u64 *__restrict__ partial, const u64 *__restrict__ base,
+                                                                  const u64 *__restrict__ partial, const u64 *__restrict__ base, int skip_small,
                                                                   const u32 *__restrict__ R, u64 hnext, u64 N, int nbits, CompactOut o) {
-	__shared__ u64 sm[32];
-	const u64 b0 = (u64) blockIdx.x * CP_TILE + (u64) threadIdx.x * CP_ITEMS;
+	__shared__ u64 wtot[CP_THREADS / 32];
+	const u32 w = threadIdx.x >> 5, l = threadIdx.x & 31;
+	const u64 w0 = (u64) blockIdx.x * CP_TILE + (u64) w * (32 * CP_ITEMS);
+	// pass 1: this warp's counts
+	u32 cs = 0, cb = 0;
 	u8 c[CP_ITEMS];
-	u64 cnt = 0;
 #pragma unroll
 	for (int i = 0; i < CP_ITEMS; i++) {
-		c[i] = b0 + i < na ? cls[b0 + i] : (u8) CLS_DROP;
-		cnt += c[i] == CLS_SMALL ? 1ull : (c[i] == CLS_BIG ? (1ull << 32) : 0ull);
+		u64 t = w0 + (u64) i * 32 + l;
+		u8 v = t < na ? cls[t] : (u8) CLS_DROP;
+		if (skip_small && v == CLS_SMALL) v = (u8) CLS_DROP;
+		c[i] = v;
+		cs += __popc(__ballot_sync(0xffffffffu, v == CLS_SMALL));
+		cb += __popc(__ballot_sync(0xffffffffu, v == CLS_BIG));
 	}
-	u64 tot;
-	u64 ex = block_excl_scan<OpSumU64>(cnt, sm, &tot);
-	ex += partial[blockIdx.x] + (base ? *base : 0ull);
+	if (l == 0) wtot[w] = ((u64) cb << 32) | cs;
+	__syncthreads();
+	u64 ex = partial[blockIdx.x] + (base ? *base : 0ull);
+	for (u32 ww = 0; ww < w; ww++) ex += wtot[ww];
 	u32 qs = (u32) ex, qb = (u32) (ex >> 32);
+	// pass 2
 #pragma unroll
 	for (int i = 0; i < CP_ITEMS; i++) {
-		if (c[i] == CLS_DROP) continue;
-		u32 p = lp[b0 + i], r = lr[b0 + i];
-		u64 q = (u64) p + hnext;
-		u32 r2 = q < N ? R[q] : 0u;
-		if (c[i] == CLS_SMALL) { o.Slp[qs] = p; o.Slr[qs] = r; o.Sr2[qs] = r2; qs++; }
-		else { o.Bkey[qb] = ((u64) r << nbits) | r2; o.Bval[qb] = p; qb++; }
+		u64 t = w0 + (u64) i * 32 + l;
+		u32 ms = __ballot_sync(0xffffffffu, c[i] == CLS_SMALL), mb = __ballot_sync(0xffffffffu, c[i] == CLS_BIG);
+		if (c[i] != CLS_DROP) {
+			u32 p = lp[t], r = lr[t];
+			u64 q = (u64) p + hnext;
+			u32 r2 = q < N ? R[q] : 0u;
+			if (c[i] == CLS_SMALL) { u32 d = qs + __popc(ms & lanemask_lt()); o.Slp[d] = p; o.Slr[d] = r; o.Sr2[d] = r2; }
+			else { u32 d = qb + __popc(mb & lanemask_lt()); o.Bkey[d] = ((u64) r << nbits) | r2; o.Bval[d] = p; }
+		}
+		qs += __popc(ms); qb += __popc(mb);
 	}
 }
 
@@ -182,9 +250,12 @@ __global__ void __launch_bounds__(CP_THREADS) k1_cls_write_kernel(const u8 *__re
 // [b*tile, b*tile + CAP); tile <= CAP - (largest bucket), so every owned bucket fits.
 // Key = bucket head offset | r2 | offset in the window, sorted by the shared-memory
 // bitonic network; sub-bucket heads by a max-scan; ranks, classes and R updates follow.
-template <int CAP> struct TileCfg { static constexpr int THREADS = CAP >= 8192 ? 1024 : CAP / 8; };
+template <int CAP> struct TileCfg {
+	static constexpr int THREADS = CAP >= 8192 ? 1024 : CAP / 8;
+	static constexpr int MINB = CAP >= 16384 ? 1 : CAP >= 8192 ? 2 : 6; // CTAs per SM the register budget is held to
+};
 
-template <int CAP> __global__ void __launch_bounds__(TileCfg<CAP>::THREADS)
+template <int CAP> __global__ void __launch_bounds__(TileCfg<CAP>::THREADS, TileCfg<CAP>::MINB)
 k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, const u32 *__restrict__ r2, u64 na, u32 tile,
                     u32 *__restrict__ R, u32 *__restrict__ lp_out, u32 *__restrict__ lr_out, u8 *__restrict__ cls_out, u32 *__restrict__ scal) {
 	constexpr int THREADS = TileCfg<CAP>::THREADS;
@@ -323,24 +394,32 @@ __global__ void k1_invert_kernel(const u32 *__restrict__ R, u64 N, u32 *__restri
 
 // Appends the survivors of one sorted list to the next S / B lists.  *total_out receives
 // this call's (small | big << 32) counts; base (device word, same packing) = where to append.
-static void compact_lists(Dev &d, const u8 *cls, const u32 *lp, const u32 *lr, u64 na, const u64 *base, u64 *total_out,
+static void compact_lists(Dev &d, const u8 *cls, const u32 *lp, const u32 *lr, u64 na, const u64 *base, u64 *total_out, bool skip_small,
                           const u32 *R, u64 hnext, u64 N, int nbits, CompactOut o) {
 	if (na == 0) { FBG_CUDA(cudaMemsetAsync(total_out, 0, sizeof(u64), d.stream)); return; }
 	u32 nt = div_up(na, CP_TILE);
 	u64 mk = d.mark();
 	u64 *partial = d.alloc<u64>(nt);
 	d.begin(K_DOUBLING_AUX);
-	k1_cls_count_kernel<<<nt, CP_THREADS, 0, d.stream>>>(cls, na, partial);
+	k1_cls_count_kernel<<<nt, CP_THREADS, 0, d.stream>>>(cls, na, skip_small ? 1 : 0, partial);
 	scan_partials_kernel<OpSumU64><<<1, 1024, 0, d.stream>>>(partial, nt, total_out);
-	k1_cls_write_kernel<<<nt, CP_THREADS, 0, d.stream>>>(cls, lp, lr, na, partial, base, R, hnext, N, nbits, o);
+	k1_cls_write_kernel<<<nt, CP_THREADS, 0, d.stream>>>(cls, lp, lr, na, partial, base, skip_small ? 1 : 0, R, hnext, N, nbits, o);
 	FBG_LAUNCH_CHECK();
 	d.end((double) na * (2.0 + 8.0 + 4.0 + 12.0));
 	d.note_launches(K_DOUBLING_AUX, 2);
 	d.release(mk);
 }
 
+__global__ void k1_active_total_kernel(const u64 *sc64, u64 *tot) {
+	// (small | big << 32) survivor words of the S and B compaction -> one count
+	u64 a = sc64[0], b = sc64[1];
+	*tot = (a & 0xFFFFFFFFull) + (a >> 32) + (b & 0xFFFFFFFFull) + (b >> 32);
+}
+
 void k1_suffix_array(Pipeline &p) {
 	Dev &d = p.dev;
+	const Dist &dist = p.dist;
+	const bool sharded = dist.world > 1;
 	const u64 N = p.N;
 	p.ISA = p.dev.palloc<u32>(N + 1);
 	p.SA = p.dev.palloc<u32>(N + 1);
@@ -363,38 +442,82 @@ void k1_suffix_array(Pipeline &p) {
 	while ((1 << b) < sigma) b++;
 	int K = 64 / b;
 	if (K > 32) K = 32;
+	const int key_bits0 = K * b;
+	const u32 km_grid = div_up(N, KM_TILE);
+
+	// ---- which suffixes this GPU sorts: all of them, or one k-mer key range (dist.cuh)
+	KmerShard sh;
+	sh.bin_lo = 0; sh.bin_hi = 1u << KM_HBITS; sh.hshift = key_bits0 > KM_HBITS ? key_bits0 - KM_HBITS : 0;
+	sh.block_off = nullptr; sh.hist = nullptr; sh.block_cnt = nullptr;
+	u64 nloc = N;      // suffixes sorted here
+	u32 rank_off = 0;  // global rank of the first of them
+	if (sharded) {
+		const u32 nbins = 1u << KM_HBITS;
+		u64 mk2 = d.mark();
+		u32 *hist = d.alloc<u32>(nbins);
+		FBG_CUDA(cudaMemsetAsync(hist, 0, nbins * sizeof(u32), d.stream));
+		sh.hist = hist;
+		k1_kmer_kernel<1><<<km_grid, KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, sh, nullptr, nullptr);
+		FBG_LAUNCH_CHECK();
+		std::vector<u32> hh(nbins), bounds(dist.world + 1);
+		FBG_CUDA(cudaMemcpyAsync(hh.data(), hist, nbins * sizeof(u32), cudaMemcpyDeviceToHost, d.stream));
+		FBG_CUDA(cudaStreamSynchronize(d.stream));
+		// the text is replicated, so every rank derives the same plan without talking
+		plan_key_ranges(hh.data(), nbins, dist.world, bounds.data());
+		sh.bin_lo = bounds[dist.rank]; sh.bin_hi = bounds[dist.rank + 1];
+		u64 before = 0, mine = 0;
+		for (u32 q = 0; q < sh.bin_hi; q++) { if (q < sh.bin_lo) before += hh[q]; else mine += hh[q]; }
+		nloc = mine; rank_off = (u32) before;
+		d.release(mk2);
+		d.note_launches(K_KMER, 1);
+	}
+	const u64 cap = nloc ? nloc : 1;
 
 	RadixBuffers rb;
-	rb.k[0] = d.alloc<u64>(N); rb.k[1] = d.alloc<u64>(N);
-	rb.v[0] = d.alloc<u32>(N); rb.v[1] = d.alloc<u32>(N);
+	rb.k[0] = d.alloc<u64>(cap); rb.k[1] = d.alloc<u64>(cap);
+	rb.v[0] = d.alloc<u32>(cap); rb.v[1] = d.alloc<u32>(cap);
 	rb.cur = 0;
-	u64 *HH = d.alloc<u64>(N);
-	u32 *HR = d.alloc<u32>(N), *newr = d.alloc<u32>(N);
-	u8 *clsB = d.alloc<u8>(N + 16), *clsS = d.alloc<u8>(N + 16);
+	u64 *HH = d.alloc<u64>(cap);
+	u32 *HR = d.alloc<u32>(cap), *newr = d.alloc<u32>(cap);
+	u8 *clsB = d.alloc<u8>(cap + 16), *clsS = d.alloc<u8>(cap + 16);
 	u32 *Slp[2], *Slr[2], *Sr2[2];
-	for (int q = 0; q < 2; q++) { Slp[q] = d.alloc<u32>(N); Slr[q] = d.alloc<u32>(N); Sr2[q] = d.alloc<u32>(N); }
-	u32 *lp_out = d.alloc<u32>(N), *lr_out = d.alloc<u32>(N);
+	for (int q = 0; q < 2; q++) { Slp[q] = d.alloc<u32>(cap); Slr[q] = d.alloc<u32>(cap); Sr2[q] = d.alloc<u32>(cap); }
+	u32 *lp_out = d.alloc<u32>(cap), *lr_out = d.alloc<u32>(cap);
 	u32 *sc32 = reinterpret_cast<u32 *>(p.scalars + 8);  // [0] maxb, [1] err
 	u64 *sc64 = p.scalars + 9;                          // (small | big << 32) survivor counts of the [0] S path, [1] B path
+	u64 *gtot = p.scalars + 11;                         // suffixes still tied, over all GPUs
 	u64 *h_sc = p.h_scalars + 8;                        // mirror of scalars[8..11]
 
-	k1_kmer_kernel<<<div_up(N, KM_TILE), KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, (u64 *) rb.k[0], rb.v[0]);
+	if (!sharded) {
+		k1_kmer_kernel<0><<<km_grid, KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, sh, (u64 *) rb.k[0], rb.v[0]);
+	} else {
+		u64 mk2 = d.mark();
+		u64 *bc = d.alloc<u64>(km_grid);
+		sh.block_cnt = bc; sh.block_off = bc;
+		k1_kmer_kernel<2><<<km_grid, KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, sh, nullptr, nullptr);
+		scan_partials_kernel<OpSumU64><<<1, 1024, 0, d.stream>>>(bc, km_grid, nullptr);
+		k1_kmer_kernel<3><<<km_grid, KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, sh, (u64 *) rb.k[0], rb.v[0]);
+		FBG_CUDA(cudaMemsetAsync(p.ISA, 0, N * sizeof(u32), d.stream)); // replicas are merged by max
+		FBG_CUDA(cudaStreamSynchronize(d.stream)); // bc is released below
+		d.release(mk2);
+		d.note_launches(K_KMER, 2);
+	}
 	FBG_LAUNCH_CHECK();
 	d.end((double) N * (1.0 + 8.0 + 4.0));
 	d.note_launches(K_KMER, 1);
 
 	int nbits = 1;
 	while ((1ull << nbits) < N) nbits++;
-	u64 nS = 0, nB = N;   // round 0: every suffix goes through the device-wide sort
+	u64 nS = 0, nB = nloc; // round 0: every suffix goes through the device-wide sort
 	u32 maxb = 0;
 	u64 h = (u64) K;      // depth the current ranks are exact to after the round being run
 	int hi_shift = 64;    // round 0: a single level of buckets
-	int key_bits = K * b;
+	int key_bits = key_bits0;
 	int sc = 0;           // current S list
 	p.sa_rounds = 0;
 	const bool debug = getenv("FBG_DEBUG") != nullptr;
 	for (;;) {
-		if (debug) fprintf(stderr, "[fbg] K1 round %d: depth %llu, S list %llu (largest bucket %u), B list %llu\n", p.sa_rounds,
+		if (debug) fprintf(stderr, "[fbg] rank %d K1 round %d: depth %llu, S list %llu (largest bucket %u), B list %llu\n", dist.rank, p.sa_rounds,
 		                   (unsigned long long) (p.sa_rounds ? h / 2 : 0), (unsigned long long) nS, maxb, (unsigned long long) nB);
 		FBG_CUDA(cudaMemsetAsync(p.scalars + 8, 0, 4 * sizeof(u64), d.stream));
 		// ---- S path
@@ -419,17 +542,49 @@ void k1_suffix_array(Pipeline &p) {
 			device_scan<OpMax2x32, false>(d, HH, HH, nB);
 			device_scan<OpMaxU32, false>(d, HR, HR, nB);
 			d.begin(K_DOUBLING_AUX);
-			k1_update_kernel<<<g, 256, 0, d.stream>>>(sk, sv, HH, HR, nB, hi_shift, p.ISA, newr, clsB, sc32);
+			k1_update_kernel<<<g, 256, 0, d.stream>>>(sk, sv, HH, HR, nB, hi_shift, rank_off, p.ISA, newr, clsB, sc32);
 			FBG_LAUNCH_CHECK();
 			d.end((double) nB * (8.0 + 4.0 + 8.0 + 4.0 + 4.0 + 4.0 + 1.0));
+		}
+		// ---- merge the rank replicas: every GPU raised only the ranks of its own suffixes
+		if (sharded) {
+			d.begin(K_COMM);
+			dist.allreduce_max_u32(p.ISA, N, d.stream);
+			d.end((double) N * 8.0);
 		}
 		// ---- next lists (all rank updates of this round are enqueued before these look-ups)
 		u64 hnext = h;
 		CompactOut o;
 		o.Slp = Slp[sc ^ 1]; o.Slr = Slr[sc ^ 1]; o.Sr2 = Sr2[sc ^ 1];
 		o.Bkey = (u64 *) rb.k[rb.cur ^ 1]; o.Bval = rb.v[rb.cur ^ 1];
-		compact_lists(d, clsS, lp_out, lr_out, nS, nullptr, sc64, p.ISA, hnext, N, nbits, o);
-		compact_lists(d, clsB, sv, newr, nB, sc64, sc64 + 1, p.ISA, hnext, N, nbits, o);
+		const bool ordered = p.sa_rounds == 0; // round 0: S list in text order (k1_bucket_size_kernel)
+		if (ordered) {
+			u64 mk2 = d.mark();
+			u32 *A = sharded ? d.alloc<u32>(N) : lp_out; // lp_out is free in round 0 (no S path yet) and holds N words on one GPU
+			FBG_CUDA(cudaMemsetAsync(A, 0, N * sizeof(u32), d.stream));
+			if (nB) {
+				u32 g = div_up(nB, 256);
+				d.begin(K_DOUBLING_AUX);
+				k1_bucket_size_kernel<<<g, 256, 0, d.stream>>>(HH, HR, sv, clsB, nB, A);
+				FBG_LAUNCH_CHECK();
+				d.end((double) nB * 9.0 + (double) N * 4.0);
+			}
+			device_scan<OpSumU32, true>(d, A, A, N, reinterpret_cast<u32 *>(sc64));
+			if (nB) {
+				u32 g = div_up(nB, 256);
+				d.begin(K_DOUBLING_AUX);
+				k1_ordered_write_kernel<<<g, 256, 0, d.stream>>>(HH, sv, newr, clsB, nB, A, p.ISA, hnext, N, o.Slp, o.Slr, o.Sr2);
+				FBG_LAUNCH_CHECK();
+				d.end((double) nB * (8.0 + 4.0 + 4.0 + 1.0 + 4.0 + 4.0 + 12.0));
+			}
+			if (sharded) FBG_CUDA(cudaStreamSynchronize(d.stream)); // A is released below
+			d.release(mk2);
+		} else {
+			compact_lists(d, clsS, lp_out, lr_out, nS, nullptr, sc64, false, p.ISA, hnext, N, nbits, o);
+		}
+		compact_lists(d, clsB, sv, newr, nB, sc64, sc64 + 1, ordered, p.ISA, hnext, N, nbits, o);
+		k1_active_total_kernel<<<1, 1, 0, d.stream>>>(sc64, gtot);
+		if (sharded) dist.allreduce_sum_u64(gtot, 1, d.stream);
 		FBG_CUDA(cudaMemcpyAsync(h_sc, p.scalars + 8, 4 * sizeof(u64), cudaMemcpyDeviceToHost, d.stream));
 		FBG_CUDA(cudaStreamSynchronize(d.stream));
 		p.sa_rounds++;
@@ -440,7 +595,7 @@ void k1_suffix_array(Pipeline &p) {
 		nB = h_sc[2] >> 32;
 		if (nB) rb.cur ^= 1; // the compaction wrote the next B list into the other ping-pong half
 		sc ^= 1;
-		if (nS + nB == 0) break;
+		if (h_sc[3] == 0) break; // nothing tied on any GPU
 		if (h >= N) throw cuda_error("prefix doubling did not converge");
 		hi_shift = nbits;
 		key_bits = 2 * nbits;

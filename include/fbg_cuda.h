@@ -51,7 +51,7 @@ typedef struct fbg_graph {
 
 /* Per-kernel accounting for the roofline: accumulated CUDA-event milliseconds,
  * algorithmic bytes (DESIGN.md states the per-unit figures) and launch counts. */
-#define FBG_N_KERNELS 11
+#define FBG_N_KERNELS 12
 typedef struct fbg_stats {
 	uint64_t m, n, text_len;      /* N = non-gap cells + m + 1 */
 	uint64_t gaps, to_ignore;     /* fbg.cpp:1858-1859 */
@@ -104,6 +104,21 @@ int fbg_run(fbg_ctx *ctx, const uint8_t *rows_rowmajor, uint64_t m, uint64_t n, 
 /* Same with the MSA already resident in device memory. */
 int fbg_run_device(fbg_ctx *ctx, const void *device_rows, uint64_t m, uint64_t n, int want_paths,
                    uint64_t *n_blocks, uint64_t *score, fbg_graph *out);
+
+/* ---- one MSA across the GPUs of a box (new: the reference is single-process; its only
+ * parallelism is std::thread over column ranges, fbg.cpp:2278-2289).  One process per GPU;
+ * every process uploads the same MSA and makes the same calls.  Suffix sorting is sharded by
+ * k-mer key range, f(x) by contiguous column range; rank array and f are merged by NCCL
+ * all-reduce(max) over NVLink.  Results (SA, ISA, LCP, f, segmentation, graph) are replicated
+ * on every rank and bit-identical to the single-GPU build. */
+int fbg_dist_unique_id(uint8_t *out128);   /* rank 0: ncclGetUniqueId; ship the 128 bytes to the other ranks */
+int fbg_dist_init(fbg_ctx *ctx, int rank, int world, const uint8_t *id128);   /* collective */
+int fbg_dist_shutdown(fbg_ctx *ctx);
+/* The sharding plans as pure host functions (no device needed):
+ * bounds[world+1]: rank r sorts the suffixes whose k-mer histogram bin is in [bounds[r], bounds[r+1]) */
+int fbg_plan_key_ranges(const uint32_t *hist, uint32_t nbins, int world, uint32_t *bounds);
+/* rank r computes f(x) for x in [*x0, *x1) */
+int fbg_plan_columns(uint64_t n, int world, int rank, uint64_t *x0, uint64_t *x1);
 
 /* The CUDA stream (cudaStream_t) every kernel of this context is launched on, so a caller
  * can bracket the work with its own events. */
