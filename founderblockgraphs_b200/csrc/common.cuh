@@ -90,6 +90,14 @@ template <typename T> __device__ __forceinline__ T warp_incl_max(T v) {
 	}
 	return v;
 }
+template <typename T> __device__ __forceinline__ T warp_incl_min(T v) {
+#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		T t = __shfl_up_sync(0xffffffffu, v, o);
+		if ((int) lane_id() >= o) v = t < v ? t : v;
+	}
+	return v;
+}
 template <typename T> __device__ __forceinline__ T warp_reduce_max(T v) {
 #pragma unroll
 	for (int o = 16; o > 0; o >>= 1) {

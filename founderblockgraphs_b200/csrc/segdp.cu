@@ -9,8 +9,9 @@
 // Every candidate at distance d = j-x has value >= d, so a downward scan from
 // u(j) = max{x : f[x]+1 <= j} that stops once d exceeds the best value seen is
 // exact, including the tie rules.  u(j) comes from a scatter-max + prefix-max
-// scan.  The recurrence is a chain, so one warp advances a wavefront: lanes whose
-// candidates are all final (u(j) < frontier) evaluate their column concurrently.
+// scan.  The recurrence is a chain, so one CTA advances a wavefront: columns whose
+// candidates are all final (u(j) < frontier) are evaluated concurrently, one warp each,
+// the lanes of a warp sharing the candidate scan of its column.
 //
 // Non-elastic: v[j] (fbg.cpp:552-611) = max{jp : f_notricks(jp) <= j} through a
 // counting scan when f is monotone (always, for gapless rows), else the
@@ -69,59 +70,98 @@ __global__ void k3_reverse_kernel(const u32 *__restrict__ rev, const u64 *__rest
 	for (u64 a = (u64) blockIdx.x * blockDim.x + threadIdx.x; a < nb; a += (u64) gridDim.x * blockDim.x) bnd[a] = rev[nb - 1 - a];
 }
 
-// single warp. mml/bt have n+1 entries. out[0] = nb, out[1] = mml[n]
-__global__ void __launch_bounds__(32) k3_elastic_dp_kernel(const u32 *__restrict__ f, const u32 *__restrict__ U, u64 n, u32 *mml, u32 *bt, u32 *rev, u64 *out) {
+// One CTA of DPW warps.  The DPW columns at the frontier F are examined together: column
+// F+w is "ready" when every candidate it can look at is final (u(j) < F), and the ready
+// prefix is evaluated at once, one warp per column.  Inside a warp the 32 lanes take 32
+// consecutive candidates x = u(j), u(j)-1, ...; a prefix-min over the lanes and two ballots
+// replay the reference's sequential scan (stop when the distance exceeds the best value,
+// first B candidate ends it and wins ties, largest x wins among equal A candidates).
+constexpr int DPW = 16;
+
+// mml/bt have n+1 entries. out[0] = nb, out[1] = mml[n]
+__global__ void __launch_bounds__(DPW * 32) k3_elastic_dp_kernel(const u32 *__restrict__ f, const u32 *__restrict__ U, u64 n, u32 *mml, u32 *bt, u32 *rev, u64 *out) {
 	__shared__ u32 ring[DP_RING];   // mml
 	__shared__ u32 fring[DP_RING];  // f
 	__shared__ u32 uch[DP_CH];      // U[base .. base+DP_CH)
-	const u32 l = lane_id();
+	const u32 w = threadIdx.x >> 5, l = lane_id();
 	const u32 INV = (u32) n + 1;
-	if (l == 0) { mml[0] = 0; bt[0] = 0; ring[0] = 0; }
+	if (threadIdx.x == 0) { mml[0] = 0; bt[0] = 0; ring[0] = 0; }
 	u64 base = 0, F = 1;
 	bool need_stage = true;
 	while (F <= n) {
-		if (need_stage || F + 32 > base + DP_CH) {
+		if (need_stage || F + DPW > base + DP_CH) {
 			base = need_stage ? 0 : F;
 			need_stage = false;
-			__threadfence_block();
-			__syncwarp();
-#pragma unroll 8
-			for (u32 i = l; i < DP_CH; i += 32) {
+			__syncthreads();
+			for (u32 i = threadIdx.x; i < DP_CH; i += DPW * 32) {
 				u64 x = base + i;
 				uch[i] = x <= n ? U[x] : 0u;
 				fring[x & (DP_RING - 1)] = x < n ? f[x] : 0u;
 			}
-			__syncwarp();
+			__syncthreads();
 		}
-		u64 j = F + l;
-		u32 uj = j <= n ? uch[j - base] : 0;
-		bool ready = j <= n && (uj == 0 || (u64) uj - 1 < F);
-		u32 rb = __ballot_sync(0xffffffffu, ready);
-		u32 r = rb == 0xffffffffu ? 32u : (u32) (__ffs(~rb) - 1);
-		if (l < r) {
+		u32 ujl = 0;
+		bool rdy = false;
+		if (l < DPW) {
+			u64 jj = F + l;
+			ujl = jj <= n ? uch[jj - base] : 0u;
+			rdy = jj <= n && (ujl == 0 || (u64) ujl - 1 < F);
+		}
+		const u32 rb = __ballot_sync(0xffffffffu, rdy);
+		const u32 r = (u32) (__ffs(~rb) - 1); // 1 <= r <= DPW: U[j] <= j, so column F is always ready
+		if (w < r) {
+			const u64 j = F + w;
+			const u32 uj = __shfl_sync(0xffffffffu, ujl, w);
 			u32 best = U32_MAX, bx = U32_MAX;
 			if (uj) {
-				u64 x = (u64) uj - 1;
+				u64 x0 = (u64) uj - 1;
 				for (;;) {
-					u64 dd = j - x;
-					if (dd > best) break;
-					u64 ex = (u64) ((x + DP_RING >= base + DP_CH) ? fring[x & (DP_RING - 1)] : f[x]) + 1;
-					u32 mx = (x + DP_RING > F + 31) ? ring[x & (DP_RING - 1)] : ld_vol(&mml[x]);
-					if (ex <= j && mx <= (u32) n) {
-						if (dd > mx) { best = (u32) dd; bx = (u32) x; break; }      // B candidate, ties go to B
-						else if (mx < best) { best = mx; bx = (u32) x; }            // A candidate, largest x wins ties
+					const bool inb = x0 >= l;
+					const u64 x = inb ? x0 - l : 0;
+					const u32 dd = (u32) (j - x);
+					u32 fx = 0, mx = 0;
+					if (inb) {
+						fx = (x + DP_RING >= base + DP_CH) ? fring[x & (DP_RING - 1)] : f[x];
+						mx = (x + DP_RING > F + DPW - 1) ? ring[x & (DP_RING - 1)] : ld_vol(&mml[x]);
 					}
-					if (x == 0) break;
-					x--;
+					const bool valid = inb && (u64) fx + 1 <= j && mx <= (u32) n;
+					const bool isB = valid && dd > mx;            // value j - x
+					const u32 a = (valid && !isB) ? mx : U32_MAX; // A candidates: value mml[x]
+					const u32 inc = warp_incl_min(a);
+					u32 E = __shfl_up_sync(0xffffffffu, inc, 1);  // best value before this lane's candidate
+					if (l == 0) E = U32_MAX;
+					E = E < best ? E : best;
+					const bool stopS = !inb || dd > E;            // the scan ends before this candidate
+					const bool stopB = !stopS && isB;             // ... or with it
+					const u32 ms = __ballot_sync(0xffffffffu, stopS || stopB);
+					const u32 mbits = __ballot_sync(0xffffffffu, stopB);
+					if (ms) {
+						const u32 k = (u32) (__ffs(ms) - 1);
+						if ((mbits >> k) & 1u) { best = __shfl_sync(0xffffffffu, dd, k); bx = (u32) (x0 - k); }
+						else {
+							const u32 m = __shfl_sync(0xffffffffu, E, k);
+							const u32 eq = __ballot_sync(0xffffffffu, a == m) & ((1u << k) - 1u);
+							if (m < best) { bx = (u32) (x0 - (u32) (__ffs(eq) - 1)); best = m; }
+						}
+						break;
+					}
+					const u32 tail = __shfl_sync(0xffffffffu, inc, 31);
+					const u32 eq = __ballot_sync(0xffffffffu, a == tail);
+					if (tail < best) { bx = (u32) (x0 - (u32) (__ffs(eq) - 1)); best = tail; }
+					if (x0 < 32) break; // candidate 0 was the last one
+					x0 -= 32;
 				}
 			}
-			if (bx == U32_MAX) { best = INV; bx = U32_MAX; }
-			mml[j] = best; bt[j] = bx;
-			ring[j & (DP_RING - 1)] = best;
+			if (l == 0) {
+				if (bx == U32_MAX) best = INV;
+				mml[j] = best; bt[j] = bx;
+				ring[j & (DP_RING - 1)] = best;
+			}
 		}
-		__syncwarp();
+		__syncthreads();
 		F += r;
 	}
+	if (w != 0) return;
 	// backtrack, fbg.cpp:2026-2039
 	if (l == 0) rev[0] = (u32) n;
 	u64 nb = dp_chase(bt, n, 1, rev, uch, [](u32 b, u32 &rec, u64 &nj) {
@@ -162,50 +202,69 @@ __global__ void k3_v_sequential_kernel(const u32 *__restrict__ f, u64 n, const u
 	}
 }
 
-// single warp wavefront over fbg.cpp:622-643; out[0]=nb, out[1]=s[n-1], out[2]=status
-__global__ void __launch_bounds__(32) k3_nonelastic_dp_kernel(const u32 *__restrict__ v, u64 n, u32 *s, u32 *prev, u32 *rev, u64 *out) {
+// fbg.cpp:622-643 on the same block wavefront; lanes take jp = v[j], v[j]-1, ...;
+// out[0]=nb, out[1]=s[n-1], out[2]=status
+__global__ void __launch_bounds__(DPW * 32) k3_nonelastic_dp_kernel(const u32 *__restrict__ v, u64 n, u32 *s, u32 *prev, u32 *rev, u64 *out) {
 	__shared__ u32 ring[DP_RING];
 	__shared__ u32 vch[DP_CH];
-	const u32 l = lane_id();
+	const u32 w = threadIdx.x >> 5, l = lane_id();
 	u64 F = 0, base = 0;
 	bool need_stage = true;
 	while (F < n) {
-		if (need_stage || F + 32 > base + DP_CH) {
+		if (need_stage || F + DPW > base + DP_CH) {
 			base = F;
 			need_stage = false;
-			__threadfence_block();
-			__syncwarp();
-#pragma unroll 8
-			for (u32 i = l; i < DP_CH; i += 32) vch[i] = base + i < n ? v[base + i] : 0u;
-			__syncwarp();
+			__syncthreads();
+			for (u32 i = threadIdx.x; i < DP_CH; i += DPW * 32) vch[i] = base + i < n ? v[base + i] : 0u;
+			__syncthreads();
 		}
-		u64 j = F + l;
-		u32 vj = j < n ? vch[j - base] : 0;
-		bool ready = j < n && (vj > j || vj <= F);
-		u32 rb = __ballot_sync(0xffffffffu, ready);
-		u32 r = rb == 0xffffffffu ? 32u : (u32) (__ffs(~rb) - 1);
-		if (l < r) {
+		u32 vjl = 0;
+		bool rdy = false;
+		if (l < DPW) {
+			u64 jj = F + l;
+			vjl = jj < n ? vch[jj - base] : 0u;
+			rdy = jj < n && (vjl > jj || vjl <= F);
+		}
+		const u32 rb = __ballot_sync(0xffffffffu, rdy);
+		const u32 r = (u32) (__ffs(~rb) - 1);
+		if (w < r) {
+			const u64 j = F + w;
+			const u32 vj = __shfl_sync(0xffffffffu, vjl, w);
 			u32 sj = (u32) j + 2, pj = (u32) j + 1;
 			if (vj <= j) {
-				u64 jp = vj;
+				u64 jp0 = vj;
 				for (;;) {
-					u32 sp = 0u;
-					if (jp) { u64 x = jp - 1; sp = (x + DP_RING > F + 31) ? ring[x & (DP_RING - 1)] : ld_vol(&s[x]); }
-					if (jp != 0 && sp == (u32) jp + 1) { jp--; continue; }
-					u32 len = (u32) (j - jp + 1);
-					u32 cand = sp > len ? sp : len;
-					if (sj > cand) { sj = cand; pj = (u32) jp; }
-					if (sj == len) break;
-					if (jp == 0) break;
-					jp--;
+					const bool inb = jp0 >= l;
+					const u64 jp = inb ? jp0 - l : 0;
+					u32 sp = 0;
+					if (inb && jp) { u64 x = jp - 1; sp = (x + DP_RING > F + DPW - 1) ? ring[x & (DP_RING - 1)] : ld_vol(&s[x]); }
+					const bool use = inb && !(jp != 0 && sp == (u32) jp + 1); // predecessors without a segmentation are skipped
+					const u32 len = (u32) (j - jp + 1);
+					const u32 cand = use ? (sp > len ? sp : len) : U32_MAX;
+					u32 inc = warp_incl_min(cand);
+					inc = inc < sj ? inc : sj;
+					const bool stop = use && inc == len;
+					const bool endz = inb && jp == 0;
+					const u32 ms = __ballot_sync(0xffffffffu, stop || endz);
+					if (ms) {
+						const u32 k = (u32) (__ffs(ms) - 1);
+						const u32 m = __shfl_sync(0xffffffffu, inc, k);
+						const u32 eq = __ballot_sync(0xffffffffu, cand == m) & ((2u << k) - 1u);
+						if (m < sj) { pj = (u32) (jp0 - (u32) (__ffs(eq) - 1)); sj = m; }
+						break;
+					}
+					const u32 tail = __shfl_sync(0xffffffffu, inc, 31);
+					const u32 eq = __ballot_sync(0xffffffffu, cand == tail);
+					if (tail < sj) { pj = (u32) (jp0 - (u32) (__ffs(eq) - 1)); sj = tail; }
+					jp0 -= 32; // no lane reached jp = 0, so jp0 >= 32
 				}
 			}
-			s[j] = sj; prev[j] = pj;
-			ring[j & (DP_RING - 1)] = sj;
+			if (l == 0) { s[j] = sj; prev[j] = pj; ring[j & (DP_RING - 1)] = sj; }
 		}
-		__syncwarp();
+		__syncthreads();
 		F += r;
 	}
+	if (w != 0) return;
 	__threadfence_block();
 	u32 sc = ld_vol(&s[n - 1]);
 	if (sc == (u32) n + 1) { if (l == 0) { out[0] = 0; out[1] = sc; out[2] = 1; } return; }
@@ -274,7 +333,7 @@ void k3_segment(Pipeline &p) {
 		d.end((double) n * 8.0);
 		device_scan<OpMaxU32, false>(d, U, U, n + 1);
 		d.begin(K_DP);
-		k3_elastic_dp_kernel<<<1, 32, 0, d.stream>>>(p.f, U, n, p.dp_a, p.dp_b, rev, out);
+		k3_elastic_dp_kernel<<<1, DPW * 32, 0, d.stream>>>(p.f, U, n, p.dp_a, p.dp_b, rev, out);
 		k3_reverse_kernel<<<NUM_SMS, 256, 0, d.stream>>>(rev, out, p.bnd);
 		FBG_LAUNCH_CHECK();
 		d.end((double) n * 24.0);
@@ -292,7 +351,7 @@ void k3_segment(Pipeline &p) {
 		k3_v_from_counts_kernel<<<g, 256, 0, d.stream>>>(cnt, n, p.dp_v);
 		k3_v_sequential_kernel<<<1, 32, 0, d.stream>>>(p.f, n, nonmono, p.dp_v);
 		if (p.opt.gap_limit == 1)
-			k3_nonelastic_dp_kernel<<<1, 32, 0, d.stream>>>(p.dp_v, n, p.dp_a, p.dp_b, rev, out);
+			k3_nonelastic_dp_kernel<<<1, DPW * 32, 0, d.stream>>>(p.dp_v, n, p.dp_a, p.dp_b, rev, out);
 		else
 			k3_greedy_dp_kernel<<<1, 32, 0, d.stream>>>(p.dp_v, n, p.dp_a, p.dp_b, rev, out);
 		k3_reverse_kernel<<<NUM_SMS, 256, 0, d.stream>>>(rev, out, p.bnd);
