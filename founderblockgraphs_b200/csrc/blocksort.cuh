@@ -5,6 +5,7 @@
 // __syncthreads() calls are uniform across the CTA.
 #pragma once
 #include "common.cuh"
+#include "tilesort.cuh"
 
 namespace fbg {
 
@@ -21,6 +22,25 @@ __device__ __forceinline__ void group_bitonic_sort(u64 *key, u32 mpad, u32 tg, u
 			__syncthreads();
 		}
 	}
+}
+
+// Same contract on the three-stages-per-pass network of tilesort.cuh: key i of a group
+// lives at key[ts_sw(i)] before and after (mpad is a multiple of 32, so the swizzle stays
+// inside the group's array).
+struct GroupPass {
+	u64 *key; u32 mpad, tg, tpg;
+	__device__ __forceinline__ void first() {
+		for (u32 g = tg; g < mpad / 8; g += tpg) ts_first_phases_group(key, g);
+		__syncthreads();
+	}
+	template <int NST> __device__ __forceinline__ void run(u32 k, u32 jtop) {
+		for (u32 g = tg; g < (mpad >> NST); g += tpg) ts_pass_group<NST>(key, k, jtop, g);
+		__syncthreads();
+	}
+};
+__device__ __forceinline__ void group_tile_sort(u64 *key, u32 mpad, u32 tg, u32 tpg) {
+	GroupPass p{key, mpad, tg, tpg};
+	ts_schedule(mpad, p);
 }
 
 struct GroupCfg { u32 mpad, tpg, groups, threads; };

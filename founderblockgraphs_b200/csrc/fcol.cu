@@ -62,21 +62,22 @@ __global__ void __launch_bounds__(1024) k2_fcol_kernel(FcolArgs a) {
 					A[i] = a.PLCP[p]; B[i] = a.NLCP[p];
 				}
 			}
-			key[i] = kk;
+			key[ts_sw(i)] = kk;
 		}
 		__syncthreads();
 		// 2. bitonic sort ascending by (rank, row)
-		group_bitonic_sort(key, mpad, tg, tpg);
+		group_tile_sort(key, mpad, tg, tpg);
 		// 3. run flags + initial values (sorted order)
 		for (u32 j = tg; j < mpad; j += tpg) {
-			u64 kj = key[j];
+			u64 kj = key[ts_sw(j)];
 			u32 lv = U32_MAX, rv = U32_MAX; u8 s = 1, e = 1;
 			if (kj != KEY_INVALID) {
 				u32 i = (u32) (kj & 0xFFFFFFu);
 				u64 r = kj >> 24;
 				lv = A[i]; rv = B[i];
-				s = (j == 0) || ((key[j - 1] >> 24) + 1 != r);
-				e = (j + 1 == mpad) || (key[j + 1] == KEY_INVALID) || ((key[j + 1] >> 24) != r + 1);
+				s = (j == 0) || ((key[ts_sw(j - 1)] >> 24) + 1 != r);
+				u64 kn = j + 1 < mpad ? key[ts_sw(j + 1)] : KEY_INVALID;
+				e = (kn == KEY_INVALID) || ((kn >> 24) != r + 1);
 			}
 			L[j] = lv; R[j] = rv; fl[j] = s; fr[j] = e;
 		}
@@ -100,7 +101,7 @@ __global__ void __launch_bounds__(1024) k2_fcol_kernel(FcolArgs a) {
 		// 5. fi per row, max over the column
 		u32 fmax = 0;
 		for (u32 j = tg; j < mpad; j += tpg) {
-			u64 kj = key[j];
+			u64 kj = key[ts_sw(j)];
 			if (kj == KEY_INVALID) continue;
 			u32 i = (u32) (kj & 0xFFFFFFu);
 			u32 lv = L[j], rv = R[j];
