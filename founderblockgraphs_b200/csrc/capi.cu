@@ -40,17 +40,6 @@ static const char *KNAMES[K_COUNT] = {"pack", "kmer", "radix_hist", "radix_scatt
 	catch (const fbg::cuda_error &e) { (ctx)->err = e.what(); cudaGetLastError(); return FBG_ERR_CUDA; } \
 	catch (const std::exception &e) { (ctx)->err = e.what(); return FBG_ERR_CUDA; }
 
-static u64 arena_need(const Pipeline &p) {
-	// largest scratch consumer is K1: 2 key + 2 value ping-pong buffers, head words,
-	// four u32 work arrays, the count matrix (see suffix.cu); upper bound on N is m*n+m+1
-	u64 N = p.m * p.n + p.m + 1;
-	u64 ntiles = (N + RS_TILE - 1) / RS_TILE;
-	u64 k1 = N * 76 + ntiles * RS_BINS * 12 + (1u << 20); // K1 uses 74 B/char (suffix.cu); K4 up to 64 B per (row,block) record
-	u64 W = p.W, NC = (W + 127) / 128;
-	u64 k0 = NC * p.m * 16 + (1u << 20);
-	return (k1 > k0 ? k1 : k0) + (16u << 20);
-}
-
 extern "C" {
 
 const char *fbg_kernel_name(int idx) { return (idx >= 0 && idx < K_COUNT) ? KNAMES[idx] : ""; }
@@ -123,7 +112,6 @@ static int upload_common(fbg_ctx *ctx, const void *rows, uint64_t m, uint64_t n,
 	FBG_CUDA(cudaSetDevice(ctx->p.dev.device));
 	if (device) k0_upload_device(ctx->p, (const u8 *) rows, m, n);
 	else k0_upload_host(ctx->p, (const u8 *) rows, m, n);
-	ctx->p.dev.reserve(arena_need(ctx->p));
 	FBG_CATCH(ctx)
 	return FBG_OK;
 }

@@ -189,6 +189,7 @@ void k0_pack(Pipeline &p) {
 	IgnoreSet ign;
 	for (int q = 0; q < 8; q++) ign.bits[q] = p.opt.ignore_bits[q];
 
+	d.ensure(NC * m * 16 + (1u << 20));
 	u64 mk = d.mark();
 	u32 *CS = d.alloc<u32>(NC * m), *CL = d.alloc<u32>(NC * m), *CI = d.alloc<u32>(NC * m), *CG = d.alloc<u32>(NC * m);
 	FBG_CUDA(cudaMemsetAsync(p.scalars, 0, 8 * sizeof(u64), d.stream));

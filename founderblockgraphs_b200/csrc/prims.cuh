@@ -30,6 +30,13 @@ struct Dev {
 		FBG_CUDA(cudaMalloc(&arena, bytes));
 		arena_cap = bytes;
 	}
+	// phase entry: make sure the (currently empty) scratch arena can hold `bytes`
+	void ensure(u64 bytes) {
+		if (bytes <= arena_cap) return;
+		if (arena_top) throw cuda_error("scratch arena must be empty when it grows");
+		FBG_CUDA(cudaStreamSynchronize(stream));
+		reserve(bytes);
+	}
 	template <typename T> T *alloc(u64 count) {
 		u64 off = round_up(arena_top, 256);
 		u64 need = off + count * sizeof(T);

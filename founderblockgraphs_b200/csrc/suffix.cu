@@ -423,6 +423,7 @@ void k1_suffix_array(Pipeline &p) {
 	const u64 N = p.N;
 	p.ISA = p.dev.palloc<u32>(N + 1);
 	p.SA = p.dev.palloc<u32>(N + 1);
+	d.ensure((sharded ? 1u : 0u) * (u64) (4u << KM_HBITS) + (1u << 20));
 	u64 mk = d.mark();
 
 	// alphabet: dense order-preserving codes (sentinel 0 is always present)
@@ -472,6 +473,11 @@ void k1_suffix_array(Pipeline &p) {
 		d.note_launches(K_KMER, 1);
 	}
 	const u64 cap = nloc ? nloc : 1;
+	// scratch of this phase: 74 B per suffix sorted here (sort ping-pong 24, heads 16, classes 2,
+	// S lists 24, tile outputs 8) + radix count matrices + (sharded) the N-word bucket directory
+	d.release(mk);
+	d.ensure(cap * 76 + (cap / RS_TILE + 2) * RS_BINS * 12 + (u64) km_grid * 8 + (sharded ? N * 4 + (N / SCAN_TILE + 2) * 8 : 0) + (16u << 20));
+	mk = d.mark();
 
 	RadixBuffers rb;
 	rb.k[0] = d.alloc<u64>(cap); rb.k[1] = d.alloc<u64>(cap);
@@ -666,6 +672,7 @@ void k1_lcp(Pipeline &p) {
 	const u64 N = p.N;
 	p.PLCP = p.dev.palloc<u32>(N + 1);
 	p.NLCP = p.dev.palloc<u32>(N + 1);
+	d.ensure(N * 16 + (N / SCAN_TILE + 2) * 8 + (4u << 20));
 	u64 mk = d.mark();
 	u32 *flag = d.alloc<u32>(N), *pos = d.alloc<u32>(N), *ia = d.alloc<u32>(N), *ib = d.alloc<u32>(N);
 	u32 *total = reinterpret_cast<u32 *>(p.scalars + 8);

@@ -71,9 +71,9 @@ def main():
         dist.broadcast_object_list(uid, src=0)
         same = all(np.array_equal(ref[k], got[k]) for k in ref if k != "secs") and ref["score"] == got["score"]
         ok = ok and same
-        print("[rank %d] %-20s %s  single %.1f ms, sharded x%d %.1f ms, comm %.2f ms, rounds %d" % (
+        print("[rank %d] %-20s %s  single %.1f ms, sharded x%d %.1f ms, comm %.2f ms, rounds %d, scratch arena %.2f GB" % (
             rank, name, "identical" if same else "MISMATCH", 1e3 * ref["secs"], world, 1e3 * got["secs"],
-            st["kernels"]["comm"]["ms"], st["sa_rounds"]), flush=True)
+            st["kernels"]["comm"]["ms"], st["sa_rounds"], st["arena_peak_bytes"] / 1e9), flush=True)
     flag = torch.tensor([0 if ok else 1])
     dist.all_reduce(flag)
     ctx.close()
