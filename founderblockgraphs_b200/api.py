@@ -48,7 +48,7 @@ EXPORTS = [
     "fbg_upload_msa_device", "fbg_build_index", "fbg_compute_f", "fbg_segment", "fbg_get_boundaries", "fbg_build_graph",
     "fbg_graph_free", "fbg_run", "fbg_run_device", "fbg_get_stream", "fbg_get_stats", "fbg_reset_stats", "fbg_get_f", "fbg_get_text",
     "fbg_get_sa", "fbg_get_isa", "fbg_get_lcp", "fbg_get_dp", "fbg_radix_sort_pairs", "fbg_radix_sort_bench", "fbg_write_xgfa",
-    "fbg_dist_unique_id", "fbg_dist_init", "fbg_dist_shutdown", "fbg_plan_key_ranges", "fbg_plan_columns",
+    "fbg_check_index", "fbg_dist_unique_id", "fbg_dist_init", "fbg_dist_shutdown", "fbg_plan_key_ranges", "fbg_plan_columns",
 ]
 
 _lib = None
@@ -104,6 +104,7 @@ def load_library():
     lib.fbg_radix_sort_pairs.argtypes = [C.c_void_p, _u64p, _u32p, C.c_uint64, C.c_int, C.c_int]
     lib.fbg_radix_sort_bench.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double)]
     lib.fbg_write_xgfa.argtypes = [C.c_char_p, C.c_void_p, C.c_uint64, C.c_uint64, _u64p, C.POINTER(FbgGraph), C.c_int, C.POINTER(C.c_char_p)]
+    lib.fbg_check_index.argtypes = [C.c_void_p, C.c_uint32, C.c_uint64, _u32p]
     lib.fbg_dist_unique_id.argtypes = [_u8p]
     lib.fbg_dist_init.argtypes = [C.c_void_p, C.c_int, C.c_int, _u8p]
     lib.fbg_dist_shutdown.argtypes = [C.c_void_p]
@@ -315,6 +316,12 @@ class Context:
         v = np.zeros(n, np.uint64)
         self._check(self.lib.fbg_get_dp(self.h, a.ctypes.data_as(_u64p), b.ctypes.data_as(_u64p), None if elastic else v.ctypes.data_as(_u64p)))
         return (a, b) if elastic else (a, b, v)
+
+    def check_index(self, nsamples: int = 100000, seed: int = 1) -> int:
+        """Device-side spot check of SA/ISA/LCP by direct text comparison; returns the number of bad samples."""
+        bad = C.c_uint32()
+        self._check(self.lib.fbg_check_index(self.h, nsamples, seed, C.byref(bad)))
+        return int(bad.value)
 
     def radix_sort_pairs(self, keys: np.ndarray, vals: np.ndarray, lo_bit=0, hi_bit=64):
         keys = np.ascontiguousarray(keys, np.uint64).copy()

@@ -21,6 +21,26 @@ __global__ void rs_widen_kernel(const u32 *__restrict__ c, u64 *__restrict__ o, 
 	if (i < n) o[i] = c[i];
 }
 
+// independent spot check of the index: random ranks k, direct text comparison
+__global__ void check_index_kernel(const u8 *__restrict__ T, const u32 *__restrict__ SA, const u32 *__restrict__ ISA, const u32 *__restrict__ PLCP,
+                                   u64 N, u64 seed, u32 nsamples, u32 *__restrict__ bad) {
+	u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= nsamples || N < 2) return;
+	u64 z = ((u64) i + seed) * 0x9E3779B97F4A7C15ull;
+	z ^= z >> 30; z *= 0xBF58476D1CE4E5B9ull; z ^= z >> 27; z *= 0x94D049BB133111EBull; z ^= z >> 31;
+	u64 k = 1 + z % (N - 1);
+	u64 a = SA[k - 1], b = SA[k];
+	bool ok = a < N && b < N && ISA[a] == (u32) (k - 1) && ISA[b] == (u32) k;
+	if (ok) {
+		u64 l = PLCP[b];
+		ok = a + l <= N && b + l <= N;
+		for (u64 q = 0; ok && q < l; q++) ok = T[a + q] == T[b + q];
+		// the two suffixes differ right after their common prefix, the smaller one first
+		if (ok) ok = a + l < N && b + l < N ? T[a + l] < T[b + l] : a + l == N;
+	}
+	if (!ok) atomicAdd(bad, 1u);
+}
+
 // every per-MSA array lives in the persistent arena: dropping them is resetting the bump pointer
 void Pipeline::free_all() {
 	NG = IG = RK = NIA = start = rowlen = lastcol = nullptr;
@@ -355,6 +375,21 @@ int fbg_get_dp(fbg_ctx *ctx, uint64_t *a, uint64_t *b, uint64_t *v) {
 	if (!rc && b) rc = copy_u32_as_u64(ctx, p.dp_b, cnt, b);
 	if (!rc && v && !p.opt.elastic) rc = copy_u32_as_u64(ctx, p.dp_v, p.n, v);
 	return rc;
+}
+
+int fbg_check_index(fbg_ctx *ctx, uint32_t nsamples, uint64_t seed, uint32_t *n_bad) {
+	if (!ctx || !n_bad || !ctx->p.have_index) { if (ctx) ctx->err = "index not built"; return FBG_ERR_ARG; }
+	FBG_TRY(ctx)
+	Pipeline &p = ctx->p;
+	FBG_CUDA(cudaSetDevice(p.dev.device));
+	u32 *bad = reinterpret_cast<u32 *>(p.scalars + 40);
+	FBG_CUDA(cudaMemsetAsync(bad, 0, sizeof(u64), p.dev.stream));
+	if (nsamples) check_index_kernel<<<div_up(nsamples, 128), 128, 0, p.dev.stream>>>(p.T, p.SA, p.ISA, p.PLCP, p.N, seed, nsamples, bad);
+	FBG_LAUNCH_CHECK();
+	FBG_CUDA(cudaMemcpyAsync(n_bad, bad, sizeof(u32), cudaMemcpyDeviceToHost, p.dev.stream));
+	FBG_CUDA(cudaStreamSynchronize(p.dev.stream));
+	FBG_CATCH(ctx)
+	return FBG_OK;
 }
 
 int fbg_radix_sort_pairs(fbg_ctx *ctx, uint64_t *keys, uint32_t *vals, uint64_t count, int lo_bit, int hi_bit) {

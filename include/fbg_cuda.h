@@ -135,6 +135,12 @@ int fbg_get_isa(fbg_ctx *ctx, uint64_t *out /* text_len */);
 int fbg_get_lcp(fbg_ctx *ctx, uint64_t *out /* text_len, SA order: LCP[k] */);
 int fbg_get_dp(fbg_ctx *ctx, uint64_t *a /* mml[n+1] or s[n] */, uint64_t *b /* backtrack[n+1] or prev[n] */, uint64_t *v /* n, non-elastic only, may be NULL */);
 
+/* Size-independent property check of the index for inputs whose arrays are too large to read
+ * back: nsamples pseudo-random ranks k; ISA[SA[k]] = k, the suffixes SA[k-1] and SA[k] share
+ * exactly LCP[k] characters (direct text comparison on the device) and are in order.
+ * *n_bad = samples that failed. */
+int fbg_check_index(fbg_ctx *ctx, uint32_t nsamples, uint64_t seed, uint32_t *n_bad);
+
 /* Standalone primitive, exported for the parity tests of the radix passes:
  * stable LSD sort of (key,value) pairs on bits [lo_bit,hi_bit). Host buffers. */
 int fbg_radix_sort_pairs(fbg_ctx *ctx, uint64_t *keys, uint32_t *vals, uint64_t count, int lo_bit, int hi_bit);

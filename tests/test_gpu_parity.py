@@ -278,6 +278,7 @@ def test_cfg2_full_size_properties(gpu_ctx):
     ctx.set_options(elastic=False, gap_limit=1)
     ctx.upload(msa)
     ctx.build_index()
+    assert ctx.check_index(200_000, seed=5) == 0  # device-side: order + LCP by direct comparison
     sa, isa = ctx.sa(), ctx.isa()
     N = len(sa)
     assert N == m * n + m + 1
