@@ -39,7 +39,8 @@ class FbgGraph(C.Structure):
 class FbgStats(C.Structure):
     _fields_ = [("m", C.c_uint64), ("n", C.c_uint64), ("text_len", C.c_uint64), ("gaps", C.c_uint64), ("to_ignore", C.c_uint64),
                 ("sa_rounds", C.c_uint64), ("arena_peak_bytes", C.c_uint64),
-                ("kernel_ms", C.c_double * N_KERNELS), ("kernel_bytes", C.c_double * N_KERNELS), ("kernel_launches", C.c_uint64 * N_KERNELS)]
+                ("kernel_ms", C.c_double * N_KERNELS), ("kernel_bytes", C.c_double * N_KERNELS), ("kernel_launches", C.c_uint64 * N_KERNELS),
+                ("dp_passes", C.c_int64)]
 
 
 # every symbol include/fbg_cuda.h declares (checked by tests/test_cabi.py)
@@ -48,7 +49,7 @@ EXPORTS = [
     "fbg_upload_msa_device", "fbg_build_index", "fbg_compute_f", "fbg_segment", "fbg_get_boundaries", "fbg_build_graph",
     "fbg_graph_free", "fbg_run", "fbg_run_device", "fbg_get_stream", "fbg_get_stats", "fbg_reset_stats", "fbg_get_f", "fbg_get_text",
     "fbg_get_sa", "fbg_get_isa", "fbg_get_lcp", "fbg_get_dp", "fbg_radix_sort_pairs", "fbg_radix_sort_bench", "fbg_write_xgfa",
-    "fbg_check_index", "fbg_dist_unique_id", "fbg_dist_init", "fbg_dist_shutdown", "fbg_plan_key_ranges", "fbg_plan_columns",
+    "fbg_check_index", "fbg_set_dp_chunking", "fbg_dist_unique_id", "fbg_dist_init", "fbg_dist_shutdown", "fbg_plan_key_ranges", "fbg_plan_columns",
 ]
 
 _lib = None
@@ -104,6 +105,7 @@ def load_library():
     lib.fbg_radix_sort_pairs.argtypes = [C.c_void_p, _u64p, _u32p, C.c_uint64, C.c_int, C.c_int]
     lib.fbg_radix_sort_bench.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double)]
     lib.fbg_write_xgfa.argtypes = [C.c_char_p, C.c_void_p, C.c_uint64, C.c_uint64, _u64p, C.POINTER(FbgGraph), C.c_int, C.POINTER(C.c_char_p)]
+    lib.fbg_set_dp_chunking.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64]
     lib.fbg_check_index.argtypes = [C.c_void_p, C.c_uint32, C.c_uint64, _u32p]
     lib.fbg_dist_unique_id.argtypes = [_u8p]
     lib.fbg_dist_init.argtypes = [C.c_void_p, C.c_int, C.c_int, _u8p]
@@ -283,7 +285,7 @@ class Context:
         self._check(self.lib.fbg_get_stats(self.h, C.byref(st)))
         names = kernel_names()
         return dict(m=st.m, n=st.n, text_len=st.text_len, gaps=st.gaps, to_ignore=st.to_ignore, sa_rounds=st.sa_rounds,
-                    arena_peak_bytes=st.arena_peak_bytes,
+                    arena_peak_bytes=st.arena_peak_bytes, dp_passes=int(st.dp_passes),
                     kernels={names[i]: dict(ms=st.kernel_ms[i], bytes=st.kernel_bytes[i], launches=st.kernel_launches[i]) for i in range(N_KERNELS)})
 
     def reset_stats(self):
@@ -316,6 +318,10 @@ class Context:
         v = np.zeros(n, np.uint64)
         self._check(self.lib.fbg_get_dp(self.h, a.ctypes.data_as(_u64p), b.ctypes.data_as(_u64p), None if elastic else v.ctypes.data_as(_u64p)))
         return (a, b) if elastic else (a, b, v)
+
+    def set_dp_chunking(self, chunk: int = 0, warmup: int = 0):
+        """Chunk / warm-up columns of the guess-and-verify DP (0, 0 = defaults); results never depend on it."""
+        self._check(self.lib.fbg_set_dp_chunking(self.h, chunk, warmup))
 
     def check_index(self, nsamples: int = 100000, seed: int = 1) -> int:
         """Device-side spot check of SA/ISA/LCP by direct text comparison; returns the number of bad samples."""

@@ -310,6 +310,13 @@ int fbg_plan_columns(uint64_t n, int world, int rank, uint64_t *x0, uint64_t *x1
 	return FBG_OK;
 }
 
+int fbg_set_dp_chunking(fbg_ctx *ctx, uint64_t chunk, uint64_t warmup) {
+	if (!ctx || (chunk && chunk < 16) || warmup > chunk) { if (ctx) ctx->err = "chunk must be 0 or >= 16, warm-up <= chunk"; return FBG_ERR_ARG; }
+	ctx->p.dp_chunk = chunk; ctx->p.dp_warm = warmup;
+	ctx->p.have_seg = false;
+	return FBG_OK;
+}
+
 void *fbg_get_stream(fbg_ctx *ctx) { return ctx ? (void *) ctx->p.dev.stream : nullptr; }
 
 int fbg_get_stats(fbg_ctx *ctx, fbg_stats *out) {
@@ -320,7 +327,7 @@ int fbg_get_stats(fbg_ctx *ctx, fbg_stats *out) {
 	p.dev.resolve();
 	std::memset(out, 0, sizeof *out);
 	out->m = p.m; out->n = p.n; out->text_len = p.N; out->gaps = p.gaps; out->to_ignore = p.toignore;
-	out->sa_rounds = p.sa_rounds; out->arena_peak_bytes = p.dev.arena_peak;
+	out->sa_rounds = p.sa_rounds; out->arena_peak_bytes = p.dev.arena_peak; out->dp_passes = p.dp_passes;
 	for (int k = 0; k < K_COUNT; k++) {
 		out->kernel_ms[k] = p.dev.stats[k].ms; out->kernel_bytes[k] = p.dev.stats[k].bytes; out->kernel_launches[k] = p.dev.stats[k].launches;
 	}

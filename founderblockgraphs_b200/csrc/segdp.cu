@@ -18,6 +18,8 @@
 // reference's one-directional two-pointer; s/prev DP of fbg.cpp:622-643 as the
 // same wavefront; greedy recurrence of fbg.cpp:827-846 for gap_limit != 1.
 #include "pipeline.cuh"
+#include <cstdlib>
+#include <vector>
 
 namespace fbg {
 
@@ -76,21 +78,84 @@ __global__ void k3_reverse_kernel(const u32 *__restrict__ rev, const u64 *__rest
 // consecutive candidates x = u(j), u(j)-1, ...; a prefix-min over the lanes and two ballots
 // replay the reference's sequential scan (stop when the distance exceeds the best value,
 // first B candidate ends it and wins ties, largest x wins among equal A candidates).
+//
+// The chain is broken up by guess-and-verify (k3_segment): the columns are cut into chunks,
+// every chunk runs the same wavefront from a local origin t = chunk start - warm-up (values
+// relative to a fresh start at t), the running plateau B of the chunks before is folded in
+// (guess = max(B, local)), and k3_*_verify_kernel recomputes every column from the guessed
+// values of its predecessors, fully in parallel.  A vector that reproduces itself under the
+// recurrence IS the solution (induction over j), so a pass without changes proves the guess;
+// otherwise the pass is repeated on its own output, and after a few rounds the whole-range
+// wavefront (one chunk) is run instead.  Predecessor pointers come from the final pass.
 constexpr int DPW = 16;
 
-// mml/bt have n+1 entries. out[0] = nb, out[1] = mml[n]
-__global__ void __launch_bounds__(DPW * 32) k3_elastic_dp_kernel(const u32 *__restrict__ f, const u32 *__restrict__ U, u64 n, u32 *mml, u32 *bt, u32 *rev, u64 *out) {
-	__shared__ u32 ring[DP_RING];   // mml
+// Candidate scan of column j over x = uj-1, uj-2, ..., xmin (fbg.cpp:1967-2014 in closed
+// form).  ff(x) = f[x], fm(x) = mml[x]; all 32 lanes call; result identical on every lane.
+template <class FF, class FM>
+__device__ __forceinline__ void elastic_scan(u64 j, u32 uj, u64 xmin, u32 n32, FF ff, FM fm, u32 &best, u32 &bx) {
+	const u32 l = lane_id();
+	best = U32_MAX; bx = U32_MAX;
+	if (uj == 0 || (u64) uj - 1 < xmin) return;
+	u64 x0 = (u64) uj - 1;
+	for (;;) {
+		const bool inb = x0 >= xmin + l;
+		const u64 x = inb ? x0 - l : xmin;
+		const u32 dd = (u32) (j - x);
+		u32 fx = 0, mx = 0;
+		if (inb) { fx = ff(x); mx = fm(x); }
+		const bool valid = inb && (u64) fx + 1 <= j && mx <= n32;
+		const bool isB = valid && dd > mx;            // value j - x
+		const u32 a = (valid && !isB) ? mx : U32_MAX; // A candidates: value mml[x]
+		const u32 inc = warp_incl_min(a);
+		u32 E = __shfl_up_sync(0xffffffffu, inc, 1);  // best value before this lane's candidate
+		if (l == 0) E = U32_MAX;
+		E = E < best ? E : best;
+		const bool stopS = !inb || dd > E;            // the scan ends before this candidate
+		const bool stopB = !stopS && isB;             // ... or with it
+		const u32 ms = __ballot_sync(0xffffffffu, stopS || stopB);
+		const u32 mbits = __ballot_sync(0xffffffffu, stopB);
+		if (ms) {
+			const u32 k = (u32) (__ffs(ms) - 1);
+			if ((mbits >> k) & 1u) { best = __shfl_sync(0xffffffffu, dd, k); bx = (u32) (x0 - k); }
+			else {
+				const u32 m = __shfl_sync(0xffffffffu, E, k);
+				const u32 eq = __ballot_sync(0xffffffffu, a == m) & ((1u << k) - 1u);
+				if (m < best) { bx = (u32) (x0 - (u32) (__ffs(eq) - 1)); best = m; }
+			}
+			return;
+		}
+		const u32 tail = __shfl_sync(0xffffffffu, inc, 31);
+		const u32 eq = __ballot_sync(0xffffffffu, a == tail);
+		if (tail < best) { bx = (u32) (x0 - (u32) (__ffs(eq) - 1)); best = tail; }
+		if (x0 < xmin + 32) return; // candidate xmin was the last one
+		x0 -= 32;
+	}
+}
+
+// Wavefront over the columns of chunk blockIdx.x: own range [c*C, c*C + C).  A chunk other
+// than the first starts from a window of sources [t0, t1] = [c*C - H, c*C - H + H/2], every
+// one of them a free block boundary (local value 0), no candidate before t0, and warms up
+// over the H/2 columns up to its own range: a single forced boundary would usually sit at a
+// column no good segmentation cuts at (f[t] - t can be hundreds of columns in gapped data).
+// One chunk (C > n) = the whole DP: then mml/bt are final.  bt may be null (chunked guess).
+__global__ void __launch_bounds__(DPW * 32) k3_elastic_dp_kernel(const u32 *__restrict__ f, const u32 *__restrict__ U, u64 n, u64 C, u64 H, u32 *mml, u32 *bt, u32 *fail) {
+	__shared__ u32 ring[DP_RING];   // mml (local values)
 	__shared__ u32 fring[DP_RING];  // f
 	__shared__ u32 uch[DP_CH];      // U[base .. base+DP_CH)
 	const u32 w = threadIdx.x >> 5, l = lane_id();
 	const u32 INV = (u32) n + 1;
-	if (threadIdx.x == 0) { mml[0] = 0; bt[0] = 0; ring[0] = 0; }
-	u64 base = 0, F = 1;
+	const u64 s = (u64) blockIdx.x * C;
+	const u64 e = s + C < n + 1 ? s + C : n + 1;
+	const u64 t = s > H ? s - H : 0;         // first source; nothing before it is looked at
+	const u64 t1 = s > H ? t + H / 2 : 0;    // last source
+	for (u64 x = t + threadIdx.x; x <= t1; x += DPW * 32) ring[x & (DP_RING - 1)] = 0;
+	if (threadIdx.x == 0 && s == 0) { mml[0] = 0; if (bt) bt[0] = 0; }
+	u64 base = t1, F = t1 + 1;
+	const u64 fst = t1; // f of the columns before it (the sources) is read from global memory
 	bool need_stage = true;
-	while (F <= n) {
+	while (F < e) {
 		if (need_stage || F + DPW > base + DP_CH) {
-			base = need_stage ? 0 : F;
+			base = need_stage ? t1 : F;
 			need_stage = false;
 			__syncthreads();
 			for (u32 i = threadIdx.x; i < DP_CH; i += DPW * 32) {
@@ -104,67 +169,91 @@ __global__ void __launch_bounds__(DPW * 32) k3_elastic_dp_kernel(const u32 *__re
 		bool rdy = false;
 		if (l < DPW) {
 			u64 jj = F + l;
-			ujl = jj <= n ? uch[jj - base] : 0u;
-			rdy = jj <= n && (ujl == 0 || (u64) ujl - 1 < F);
+			ujl = jj < e ? uch[jj - base] : 0u;
+			rdy = jj < e && (ujl == 0 || (u64) ujl - 1 < F);
 		}
 		const u32 rb = __ballot_sync(0xffffffffu, rdy);
 		const u32 r = (u32) (__ffs(~rb) - 1); // 1 <= r <= DPW: U[j] <= j, so column F is always ready
 		if (w < r) {
 			const u64 j = F + w;
 			const u32 uj = __shfl_sync(0xffffffffu, ujl, w);
-			u32 best = U32_MAX, bx = U32_MAX;
-			if (uj) {
-				u64 x0 = (u64) uj - 1;
-				for (;;) {
-					const bool inb = x0 >= l;
-					const u64 x = inb ? x0 - l : 0;
-					const u32 dd = (u32) (j - x);
-					u32 fx = 0, mx = 0;
-					if (inb) {
-						fx = (x + DP_RING >= base + DP_CH) ? fring[x & (DP_RING - 1)] : f[x];
-						mx = (x + DP_RING > F + DPW - 1) ? ring[x & (DP_RING - 1)] : ld_vol(&mml[x]);
-					}
-					const bool valid = inb && (u64) fx + 1 <= j && mx <= (u32) n;
-					const bool isB = valid && dd > mx;            // value j - x
-					const u32 a = (valid && !isB) ? mx : U32_MAX; // A candidates: value mml[x]
-					const u32 inc = warp_incl_min(a);
-					u32 E = __shfl_up_sync(0xffffffffu, inc, 1);  // best value before this lane's candidate
-					if (l == 0) E = U32_MAX;
-					E = E < best ? E : best;
-					const bool stopS = !inb || dd > E;            // the scan ends before this candidate
-					const bool stopB = !stopS && isB;             // ... or with it
-					const u32 ms = __ballot_sync(0xffffffffu, stopS || stopB);
-					const u32 mbits = __ballot_sync(0xffffffffu, stopB);
-					if (ms) {
-						const u32 k = (u32) (__ffs(ms) - 1);
-						if ((mbits >> k) & 1u) { best = __shfl_sync(0xffffffffu, dd, k); bx = (u32) (x0 - k); }
-						else {
-							const u32 m = __shfl_sync(0xffffffffu, E, k);
-							const u32 eq = __ballot_sync(0xffffffffu, a == m) & ((1u << k) - 1u);
-							if (m < best) { bx = (u32) (x0 - (u32) (__ffs(eq) - 1)); best = m; }
-						}
-						break;
-					}
-					const u32 tail = __shfl_sync(0xffffffffu, inc, 31);
-					const u32 eq = __ballot_sync(0xffffffffu, a == tail);
-					if (tail < best) { bx = (u32) (x0 - (u32) (__ffs(eq) - 1)); best = tail; }
-					if (x0 < 32) break; // candidate 0 was the last one
-					x0 -= 32;
-				}
-			}
+			u32 best, bx;
+			elastic_scan(j, uj, t, (u32) n,
+				[&](u64 x) { return (x >= fst && x + DP_RING >= base + DP_CH) ? fring[x & (DP_RING - 1)] : f[x]; },
+				[&](u64 x) {
+					if (x + DP_RING > F + DPW - 1) return ring[x & (DP_RING - 1)];
+					if (x >= s) return ld_vol(&mml[x]);   // older than the ring: own, already written
+					*fail = 1u;                           // warm-up value lost: the guess of this chunk is void
+					return 0u;
+				}, best, bx);
 			if (l == 0) {
 				if (bx == U32_MAX) best = INV;
-				mml[j] = best; bt[j] = bx;
 				ring[j & (DP_RING - 1)] = best;
+				if (j >= s) { mml[j] = best; if (bt) bt[j] = bx; }
 			}
 		}
 		__syncthreads();
 		F += r;
 	}
-	if (w != 0) return;
-	// backtrack, fbg.cpp:2026-2039
+}
+
+// One warp per column: (mml, bt) of column j from the values gin[] of its predecessors.
+__global__ void __launch_bounds__(256) k3_elastic_verify_kernel(const u32 *__restrict__ f, const u32 *__restrict__ U, u64 n, const u32 *__restrict__ gin,
+                                                                u32 *__restrict__ gout, u32 *__restrict__ bt, u32 *__restrict__ changes) {
+	const u64 j = (((u64) blockIdx.x * blockDim.x + threadIdx.x) >> 5) + 1;
+	if (j > n) return;
+	u32 best, bx;
+	elastic_scan(j, U[j], 0, (u32) n, [&](u64 x) { return f[x]; }, [&](u64 x) { return gin[x]; }, best, bx);
+	if (lane_id() == 0) {
+		if (bx == U32_MAX) best = (u32) n + 1;
+		gout[j] = best; bt[j] = bx;
+		u32 old = gin[j];
+		bool same = old == best || (old > (u32) n && best > (u32) n);
+		if (!same) atomicAdd(changes, 1u);
+	}
+}
+
+// per chunk c: q[c] = min of the local values in the w columns up to the next chunk's last
+// source (the plateau the next chunk starts from); then B[c] = max_{c' < c} q[c'] (B[0] = 0).
+__global__ void __launch_bounds__(1024) k3_plateau_kernel(const u32 *__restrict__ loc, u64 n_cols, u64 C, u64 H, u64 wq, u32 nchunks, u32 limit, bool nonelastic, u32 *__restrict__ B) {
+	__shared__ u32 sm[32];
+	u32 carry = 0;
+	for (u32 c0 = 0; c0 < nchunks; c0 += 1024) {
+		u32 c = c0 + threadIdx.x;
+		u32 q = 0;
+		if (c + 1 < nchunks) {
+			u64 tn = (u64) (c + 1) * C - H + H / 2; // last source of chunk c+1, inside chunk c
+			u32 mn = U32_MAX;
+			for (u64 x = tn > wq ? tn - wq : 0; x <= tn && x < n_cols; x++) {
+				if (x < (u64) c * C) continue;
+				u32 v = loc[x];
+				bool ok = nonelastic ? v != (u32) x + 2 : v <= limit;
+				if (ok && v < mn) mn = v;
+			}
+			q = mn == U32_MAX ? 0u : mn;
+		}
+		u32 tot;
+		u32 ex = block_excl_scan<OpMaxU32>(q, sm, &tot);
+		if (c < nchunks) B[c] = ex > carry ? ex : carry;
+		carry = tot > carry ? tot : carry;
+	}
+}
+
+// guess = max(B[chunk], local value); unreachable / invalid markers are kept
+__global__ void k3_apply_plateau_kernel(u32 *__restrict__ g, u64 first, u64 n_cols, u64 C, u32 limit, bool nonelastic, const u32 *__restrict__ B) {
+	u64 x = first + (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (x >= n_cols) return;
+	u32 v = g[x], b = B[x / C];
+	bool ok = nonelastic ? v != (u32) x + 2 : v <= limit;
+	if (ok && b > v) g[x] = b;
+}
+
+// backtrack, fbg.cpp:2026-2039. out[0] = nb, out[1] = mml[n]
+__global__ void __launch_bounds__(32) k3_elastic_chase_kernel(const u32 *bt, const u32 *mml, u64 n, u32 *rev, u64 *out) {
+	__shared__ u32 stage[DP_CH];
+	const u32 l = lane_id();
 	if (l == 0) rev[0] = (u32) n;
-	u64 nb = dp_chase(bt, n, 1, rev, uch, [](u32 b, u32 &rec, u64 &nj) {
+	u64 nb = dp_chase(bt, n, 1, rev, stage, [](u32 b, u32 &rec, u64 &nj) {
 		if (b == 0 || b == U32_MAX) return false;
 		rec = b - 1; nj = b;
 		return true;
@@ -202,15 +291,55 @@ __global__ void k3_v_sequential_kernel(const u32 *__restrict__ f, u64 n, const u
 	}
 }
 
-// fbg.cpp:622-643 on the same block wavefront; lanes take jp = v[j], v[j]-1, ...;
-// out[0]=nb, out[1]=s[n-1], out[2]=status
-__global__ void __launch_bounds__(DPW * 32) k3_nonelastic_dp_kernel(const u32 *__restrict__ v, u64 n, u32 *s, u32 *prev, u32 *rev, u64 *out) {
+// Candidate scan of fbg.cpp:622-643 for column j over jp = vj, vj-1, ..., jmin (jp = jmin
+// starts the segmentation: predecessor value 0).  fs(x) = s[x].
+template <class FS>
+__device__ __forceinline__ void nonelastic_scan(u64 j, u32 vj, u64 jmin, FS fs, u32 &sj, u32 &pj) {
+	const u32 l = lane_id();
+	sj = (u32) j + 2; pj = (u32) j + 1;
+	if (vj > j || vj < jmin) return;
+	u64 jp0 = vj;
+	for (;;) {
+		const bool inb = jp0 >= jmin + l;
+		const u64 jp = inb ? jp0 - l : jmin;
+		u32 sp = 0;
+		if (inb && jp > jmin) sp = fs(jp - 1);
+		const bool use = inb && !(jp > jmin && sp == (u32) jp + 1); // predecessors without a segmentation are skipped
+		const u32 len = (u32) (j - jp + 1);
+		const u32 cand = use ? (sp > len ? sp : len) : U32_MAX;
+		u32 inc = warp_incl_min(cand);
+		inc = inc < sj ? inc : sj;
+		const bool stop = use && inc == len;
+		const bool endz = inb && jp == jmin;
+		const u32 ms = __ballot_sync(0xffffffffu, stop || endz);
+		if (ms) {
+			const u32 k = (u32) (__ffs(ms) - 1);
+			const u32 m = __shfl_sync(0xffffffffu, inc, k);
+			const u32 eq = __ballot_sync(0xffffffffu, cand == m) & ((2u << k) - 1u);
+			if (m < sj) { pj = (u32) (jp0 - (u32) (__ffs(eq) - 1)); sj = m; }
+			return;
+		}
+		const u32 tail = __shfl_sync(0xffffffffu, inc, 31);
+		const u32 eq = __ballot_sync(0xffffffffu, cand == tail);
+		if (tail < sj) { pj = (u32) (jp0 - (u32) (__ffs(eq) - 1)); sj = tail; }
+		jp0 -= 32; // no lane reached jmin, so jp0 >= jmin + 32
+	}
+}
+
+// chunk wavefront of the non-elastic DP; same chunk / origin convention as the elastic one
+__global__ void __launch_bounds__(DPW * 32) k3_nonelastic_dp_kernel(const u32 *__restrict__ v, u64 n, u64 C, u64 H, u32 *s, u32 *prev, u32 *fail) {
 	__shared__ u32 ring[DP_RING];
 	__shared__ u32 vch[DP_CH];
 	const u32 w = threadIdx.x >> 5, l = lane_id();
-	u64 F = 0, base = 0;
+	const u64 cs = (u64) blockIdx.x * C;
+	const u64 e = cs + C < n ? cs + C : n;
+	// sources: prefixes ending at t0 .. t1 cost nothing (see the elastic kernel); jmin = t0 + 1
+	const u64 t0 = cs > H ? cs - H : 0, t1 = cs > H ? t0 + H / 2 : 0;
+	const u64 t = cs > H ? t0 + 1 : 0;
+	if (cs > H) for (u64 x = t0 + threadIdx.x; x <= t1; x += DPW * 32) ring[x & (DP_RING - 1)] = 0;
+	u64 F = cs > H ? t1 + 1 : 0, base = F;
 	bool need_stage = true;
-	while (F < n) {
+	while (F < e) {
 		if (need_stage || F + DPW > base + DP_CH) {
 			base = F;
 			need_stage = false;
@@ -222,54 +351,51 @@ __global__ void __launch_bounds__(DPW * 32) k3_nonelastic_dp_kernel(const u32 *_
 		bool rdy = false;
 		if (l < DPW) {
 			u64 jj = F + l;
-			vjl = jj < n ? vch[jj - base] : 0u;
-			rdy = jj < n && (vjl > jj || vjl <= F);
+			vjl = jj < e ? vch[jj - base] : 0u;
+			rdy = jj < e && (vjl > jj || vjl <= F);
 		}
 		const u32 rb = __ballot_sync(0xffffffffu, rdy);
 		const u32 r = (u32) (__ffs(~rb) - 1);
 		if (w < r) {
 			const u64 j = F + w;
 			const u32 vj = __shfl_sync(0xffffffffu, vjl, w);
-			u32 sj = (u32) j + 2, pj = (u32) j + 1;
-			if (vj <= j) {
-				u64 jp0 = vj;
-				for (;;) {
-					const bool inb = jp0 >= l;
-					const u64 jp = inb ? jp0 - l : 0;
-					u32 sp = 0;
-					if (inb && jp) { u64 x = jp - 1; sp = (x + DP_RING > F + DPW - 1) ? ring[x & (DP_RING - 1)] : ld_vol(&s[x]); }
-					const bool use = inb && !(jp != 0 && sp == (u32) jp + 1); // predecessors without a segmentation are skipped
-					const u32 len = (u32) (j - jp + 1);
-					const u32 cand = use ? (sp > len ? sp : len) : U32_MAX;
-					u32 inc = warp_incl_min(cand);
-					inc = inc < sj ? inc : sj;
-					const bool stop = use && inc == len;
-					const bool endz = inb && jp == 0;
-					const u32 ms = __ballot_sync(0xffffffffu, stop || endz);
-					if (ms) {
-						const u32 k = (u32) (__ffs(ms) - 1);
-						const u32 m = __shfl_sync(0xffffffffu, inc, k);
-						const u32 eq = __ballot_sync(0xffffffffu, cand == m) & ((2u << k) - 1u);
-						if (m < sj) { pj = (u32) (jp0 - (u32) (__ffs(eq) - 1)); sj = m; }
-						break;
-					}
-					const u32 tail = __shfl_sync(0xffffffffu, inc, 31);
-					const u32 eq = __ballot_sync(0xffffffffu, cand == tail);
-					if (tail < sj) { pj = (u32) (jp0 - (u32) (__ffs(eq) - 1)); sj = tail; }
-					jp0 -= 32; // no lane reached jp = 0, so jp0 >= 32
-				}
+			u32 sj, pj;
+			nonelastic_scan(j, vj, t, [&](u64 x) {
+				if (x + DP_RING > F + DPW - 1) return ring[x & (DP_RING - 1)];
+				if (x >= cs) return ld_vol(&s[x]);
+				*fail = 1u;
+				return 0u;
+			}, sj, pj);
+			if (l == 0) {
+				ring[j & (DP_RING - 1)] = sj;
+				if (j >= cs) { s[j] = sj; if (prev) prev[j] = pj; }
 			}
-			if (l == 0) { s[j] = sj; prev[j] = pj; ring[j & (DP_RING - 1)] = sj; }
 		}
 		__syncthreads();
 		F += r;
 	}
-	if (w != 0) return;
-	__threadfence_block();
+}
+
+__global__ void __launch_bounds__(256) k3_nonelastic_verify_kernel(const u32 *__restrict__ v, u64 n, const u32 *__restrict__ gin, u32 *__restrict__ gout, u32 *__restrict__ prev,
+                                                                   u32 *__restrict__ changes) {
+	const u64 j = ((u64) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	if (j >= n) return;
+	u32 sj, pj;
+	nonelastic_scan(j, v[j], 0, [&](u64 x) { return gin[x]; }, sj, pj);
+	if (lane_id() == 0) {
+		gout[j] = sj; prev[j] = pj;
+		if (gin[j] != sj) atomicAdd(changes, 1u);
+	}
+}
+
+// out[0]=nb, out[1]=s[n-1], out[2]=status
+__global__ void __launch_bounds__(32) k3_nonelastic_chase_kernel(const u32 *prev, const u32 *s, u64 n, u32 *rev, u64 *out) {
+	__shared__ u32 stage[DP_CH];
+	const u32 l = lane_id();
 	u32 sc = ld_vol(&s[n - 1]);
 	if (sc == (u32) n + 1) { if (l == 0) { out[0] = 0; out[1] = sc; out[2] = 1; } return; }
 	if (l == 0) rev[0] = (u32) (n - 1);
-	u64 nb = dp_chase(prev, n - 1, 1, rev, vch, [](u32 pv, u32 &rec, u64 &nj) {
+	u64 nb = dp_chase(prev, n - 1, 1, rev, stage, [](u32 pv, u32 &rec, u64 &nj) {
 		if (pv == 0) return false;
 		rec = pv - 1; nj = (u64) pv - 1;
 		return true;
@@ -314,12 +440,118 @@ __global__ void k3_greedy_dp_kernel(const u32 *__restrict__ v, u64 n, u32 *s, u3
 	out[0] = nb; out[2] = 0;
 }
 
+// sum over columns of the shortest admissible last block (j - u(j) resp. j - v[j] + 1): its mean
+// says how long a warm-up has to be before chunking is worth trying
+__global__ void __launch_bounds__(256) k3_min_block_sum_kernel(const u32 *__restrict__ UV, u64 ncols, bool elastic, u64 *__restrict__ sum) {
+	u64 j = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	u64 v = 0;
+	if (j < ncols) {
+		u32 q = UV[j];
+		if (elastic) v = q ? j - ((u64) q - 1) : 0;
+		else v = q <= j ? j - q + 1 : 0;
+	}
+	v = warp_reduce_sum(v);
+	if (lane_id() == 0 && v) atomicAdd((unsigned long long *) sum, (unsigned long long) v);
+}
+
+// Guess-and-verify driver (see the comment above DPW).  `elastic`: columns 0..n (mml), else
+// 0..n-1 (s).  Leaves values in val, pointers in ptr.
+static void dp_solve(Pipeline &p, bool elastic, const u32 *U_or_v, u32 *val, u32 *ptr) {
+	Dev &d = p.dev;
+	const u64 n = p.n;
+	const u64 ncols = elastic ? n + 1 : n;
+	const bool debug = getenv("FBG_DEBUG") != nullptr;
+	u32 *flags = reinterpret_cast<u32 *>(p.scalars + 26); // [0] warm-up lost, [1] changes of the last pass
+	u32 *h_flags = reinterpret_cast<u32 *>(p.h_scalars + 26);
+	auto whole = [&]() {
+		if (elastic) k3_elastic_dp_kernel<<<1, DPW * 32, 0, d.stream>>>(p.f, U_or_v, n, ncols + 1, 0, val, ptr, flags);
+		else k3_nonelastic_dp_kernel<<<1, DPW * 32, 0, d.stream>>>(U_or_v, n, ncols + 1, 0, val, ptr, flags);
+		FBG_LAUNCH_CHECK();
+	};
+	// The warm-up must outlast the plateau (the optimal segment length so far), which is only
+	// known afterwards; the mean shortest admissible block is a cheap indicator of it.
+	u64 C = p.dp_chunk ? p.dp_chunk : 2048, H = p.dp_chunk ? p.dp_warm : 1024;
+	if (!p.dp_chunk && ncols > C) {
+		u64 *sum = p.scalars + 28;
+		FBG_CUDA(cudaMemsetAsync(sum, 0, sizeof(u64), d.stream));
+		k3_min_block_sum_kernel<<<div_up(ncols, 256), 256, 0, d.stream>>>(U_or_v, ncols, elastic, sum);
+		FBG_LAUNCH_CHECK();
+		FBG_CUDA(cudaMemcpyAsync(p.h_scalars + 28, sum, sizeof(u64), cudaMemcpyDeviceToHost, d.stream));
+		FBG_CUDA(cudaStreamSynchronize(d.stream));
+		const u64 mean = p.h_scalars[28] / ncols + 1;
+		if (mean * 16 > 1024) { C = 8192; H = 4096; }
+		if (mean * 16 > 4096) C = ncols + 1; // blocks of hundreds of columns: few chunks would be left, run the wavefront once
+		if (debug) fprintf(stderr, "[fbg] K3 mean shortest block %llu columns -> chunk %llu, warm-up %llu\n", (unsigned long long) mean, (unsigned long long) C, (unsigned long long) H);
+		d.note_launches(K_DP, 1);
+	}
+	if (H > C) H = C;
+	if (H < 1) H = 1; // at least one source column in front of a chunk
+	u64 mk = d.mark();
+	u32 *g2 = d.alloc<u32>(ncols + 1);
+	u32 *B = d.alloc<u32>(ncols / 16 + 2);
+	bool proven = false;
+	p.dp_passes = 0;
+	std::vector<u32> dbg_guess; u64 dbgC = 0;
+	for (int attempt = 0; attempt < 1 && !proven; attempt++) {
+		const u32 nchunks = div_up(ncols, C);
+		if (nchunks <= 1) break;
+		const u64 wq = C - H / 2 < 64 ? C - H / 2 : 64;
+		FBG_CUDA(cudaMemsetAsync(flags, 0, 2 * sizeof(u32), d.stream));
+		if (elastic) k3_elastic_dp_kernel<<<nchunks, DPW * 32, 0, d.stream>>>(p.f, U_or_v, n, C, H, val, nullptr, flags);
+		else k3_nonelastic_dp_kernel<<<nchunks, DPW * 32, 0, d.stream>>>(U_or_v, n, C, H, val, nullptr, flags);
+		k3_plateau_kernel<<<1, 1024, 0, d.stream>>>(val, ncols, C, H, wq, nchunks, (u32) n, !elastic, B);
+		k3_apply_plateau_kernel<<<div_up(ncols - C, 256), 256, 0, d.stream>>>(val, C, ncols, C, (u32) n, !elastic, B);
+		FBG_LAUNCH_CHECK();
+		d.note_launches(K_DP, 3);
+		if (debug) { dbg_guess.resize(ncols); FBG_CUDA(cudaMemcpyAsync(dbg_guess.data(), val, ncols * sizeof(u32), cudaMemcpyDeviceToHost, d.stream)); FBG_CUDA(cudaStreamSynchronize(d.stream)); dbgC = C; }
+		u32 *cur = val, *nxt = g2;
+		const u32 vgrid = div_up(ncols * 32, 256);
+		for (int pass = 0; pass < 6; pass++) {
+			FBG_CUDA(cudaMemsetAsync(flags + 1, 0, sizeof(u32), d.stream));
+			if (elastic) {
+				FBG_CUDA(cudaMemsetAsync(nxt, 0, sizeof(u32), d.stream)); // mml[0] = 0
+				k3_elastic_verify_kernel<<<vgrid, 256, 0, d.stream>>>(p.f, U_or_v, n, cur, nxt, ptr, flags + 1);
+			} else {
+				k3_nonelastic_verify_kernel<<<vgrid, 256, 0, d.stream>>>(U_or_v, n, cur, nxt, ptr, flags + 1);
+			}
+			FBG_LAUNCH_CHECK();
+			FBG_CUDA(cudaMemcpyAsync(h_flags, flags, 2 * sizeof(u32), cudaMemcpyDeviceToHost, d.stream));
+			FBG_CUDA(cudaStreamSynchronize(d.stream));
+			d.note_launches(K_DP, 1);
+			p.dp_passes++;
+			if (debug) fprintf(stderr, "[fbg] K3 attempt %d (chunk %llu, warm-up %llu, %u chunks) pass %d: %u columns changed%s\n", attempt,
+			                   (unsigned long long) C, (unsigned long long) H, nchunks, pass, h_flags[1], h_flags[0] ? ", a warm-up window was lost" : "");
+			if (h_flags[0]) break; // a chunk lost its warm-up window: no guess to verify
+			u32 *tmp = cur; cur = nxt; nxt = tmp;
+			if (h_flags[1] == 0) { proven = true; break; }
+			if ((u64) h_flags[1] * 64 > ncols) break; // the guess is far off (plateau longer than the warm-up): do not iterate
+		}
+		if (proven && cur != val) FBG_CUDA(cudaMemcpyAsync(val, cur, ncols * sizeof(u32), cudaMemcpyDeviceToDevice, d.stream));
+	}
+	if (!proven) { if (p.dp_passes) p.dp_passes = -p.dp_passes; whole(); FBG_CUDA(cudaStreamSynchronize(d.stream)); }
+	if (!proven && debug && !dbg_guess.empty()) {
+		std::vector<u32> tv(ncols);
+		FBG_CUDA(cudaMemcpy(tv.data(), val, ncols * sizeof(u32), cudaMemcpyDeviceToHost));
+		int shown = 0;
+		for (u64 x = 0; x < ncols && shown < 24; x++) {
+			if (tv[x] == dbg_guess[x]) continue;
+			u64 y = x;
+			while (y < ncols && tv[y] != dbg_guess[y]) y++;
+			fprintf(stderr, "[fbg] K3 guess off in columns [%llu, %llu) (chunk %llu, offset %llu): guess %u true %u; before: true %u\n", (unsigned long long) x,
+			        (unsigned long long) y, (unsigned long long) (x / dbgC), (unsigned long long) (x % dbgC), dbg_guess[x], tv[x], x ? tv[x - 1] : 0);
+			x = y; shown++;
+		}
+	}
+	else if (elastic) FBG_CUDA(cudaMemsetAsync(ptr, 0, sizeof(u32), d.stream)); // bt[0] = 0
+	d.release(mk);
+}
+
 void k3_segment(Pipeline &p) {
 	Dev &d = p.dev;
 	const u64 n = p.n;
 	if (!p.bnd) p.bnd = p.dev.palloc<u32>(n + 2);
 	if (!p.dp_a) { p.dp_a = p.dev.palloc<u32>(n + 2); p.dp_b = p.dev.palloc<u32>(n + 2); p.dp_v = p.dev.palloc<u32>(n + 2); }
-	d.ensure((n + 2) * 8 + (n / SCAN_TILE + 2) * 8 + (1u << 20));
+	d.ensure((n + 2) * 12 + (n / 16 + 4) * 4 + (n / SCAN_TILE + 2) * 8 + (1u << 20));
 	u64 mk = d.mark();
 	u32 *rev = d.alloc<u32>(n + 2);
 	u64 *out = p.scalars + 16;
@@ -334,10 +566,12 @@ void k3_segment(Pipeline &p) {
 		d.end((double) n * 8.0);
 		device_scan<OpMaxU32, false>(d, U, U, n + 1);
 		d.begin(K_DP);
-		k3_elastic_dp_kernel<<<1, DPW * 32, 0, d.stream>>>(p.f, U, n, p.dp_a, p.dp_b, rev, out);
+		dp_solve(p, true, U, p.dp_a, p.dp_b);
+		k3_elastic_chase_kernel<<<1, 32, 0, d.stream>>>(p.dp_b, p.dp_a, n, rev, out);
 		k3_reverse_kernel<<<NUM_SMS, 256, 0, d.stream>>>(rev, out, p.bnd);
 		FBG_LAUNCH_CHECK();
 		d.end((double) n * 24.0);
+		d.note_launches(K_DP, 2);
 	} else {
 		u32 *cnt = d.alloc<u32>(n + 2);
 		u32 *nonmono = reinterpret_cast<u32 *>(p.scalars + 24);
@@ -351,14 +585,16 @@ void k3_segment(Pipeline &p) {
 		d.begin(K_DP);
 		k3_v_from_counts_kernel<<<g, 256, 0, d.stream>>>(cnt, n, p.dp_v);
 		k3_v_sequential_kernel<<<1, 32, 0, d.stream>>>(p.f, n, nonmono, p.dp_v);
-		if (p.opt.gap_limit == 1)
-			k3_nonelastic_dp_kernel<<<1, DPW * 32, 0, d.stream>>>(p.dp_v, n, p.dp_a, p.dp_b, rev, out);
-		else
+		if (p.opt.gap_limit == 1) {
+			dp_solve(p, false, p.dp_v, p.dp_a, p.dp_b);
+			k3_nonelastic_chase_kernel<<<1, 32, 0, d.stream>>>(p.dp_b, p.dp_a, n, rev, out);
+		} else {
 			k3_greedy_dp_kernel<<<1, 32, 0, d.stream>>>(p.dp_v, n, p.dp_a, p.dp_b, rev, out);
+		}
 		k3_reverse_kernel<<<NUM_SMS, 256, 0, d.stream>>>(rev, out, p.bnd);
 		FBG_LAUNCH_CHECK();
 		d.end((double) n * 24.0);
-		d.note_launches(K_DP, 2);
+		d.note_launches(K_DP, 4);
 	}
 	FBG_CUDA(cudaMemcpyAsync(p.h_scalars + 16, out, 4 * sizeof(u64), cudaMemcpyDeviceToHost, d.stream));
 	FBG_CUDA(cudaStreamSynchronize(d.stream));

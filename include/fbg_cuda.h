@@ -60,6 +60,7 @@ typedef struct fbg_stats {
 	double kernel_ms[FBG_N_KERNELS];
 	double kernel_bytes[FBG_N_KERNELS];
 	uint64_t kernel_launches[FBG_N_KERNELS];
+	int64_t dp_passes;            /* K3: verify passes of the chunked DP (0 = one chunk, < 0 = that many passes were spent and the whole-range wavefront was needed) */
 } fbg_stats;
 
 /* index -> name for the arrays above ("pack", "kmer", "radix_hist", ...) */
@@ -119,6 +120,10 @@ int fbg_dist_shutdown(fbg_ctx *ctx);
 int fbg_plan_key_ranges(const uint32_t *hist, uint32_t nbins, int world, uint32_t *bounds);
 /* rank r computes f(x) for x in [*x0, *x1) */
 int fbg_plan_columns(uint64_t n, int world, int rank, uint64_t *x0, uint64_t *x1);
+
+/* K3 tuning, for the parity tests: columns per chunk and warm-up columns of the chunked
+ * guess-and-verify DP (0, 0 = defaults 2048 / 1024).  Results never depend on it. */
+int fbg_set_dp_chunking(fbg_ctx *ctx, uint64_t chunk, uint64_t warmup);
 
 /* The CUDA stream (cudaStream_t) every kernel of this context is launched on, so a caller
  * can bracket the work with its own events. */
