@@ -314,22 +314,23 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 	u32 wpre = 0;
 	for (u32 ww = 0; ww < w; ww++) { u32 x = s_wtot[ww]; wpre = x > wpre ? x : wpre; }
 
-	// 2. keys
+	// 2. keys, compacted to slots [0, cnt); the network is sized to the keys actually present
+	u32 net = 32;
+	while (net < cnt) net <<= 1;
 #pragma unroll
 	for (int i = 0; i < ITEMS; i++) {
 		u32 idx = w * WCH + i * 32 + l;
-		u64 k = ~0ull;
 		if (idx >= first && idx < endidx) {
 			u32 hb1 = hbv[i] > wpre ? hbv[i] : wpre;
 			u32 hb_rel = hb1 - 1 - first;
-			k = ((u64) hb_rel << (32 + LOGC)) | ((u64) r2[w0 + idx] << LOGC) | (u64) (idx - first);
+			key[ts_sw(idx - first)] = ((u64) hb_rel << (32 + LOGC)) | ((u64) r2[w0 + idx] << LOGC) | (u64) (idx - first);
 		}
-		key[ts_sw(idx)] = k;
 	}
+	for (u32 slot = cnt + tid; slot < net; slot += THREADS) key[ts_sw(slot)] = ~0ull;
 	__syncthreads();
 
 	// 3. sort
-	tile_bitonic_sort<CAP, THREADS>(key);
+	tile_bitonic_sort_rt<THREADS>(key, net);
 
 	// 4. sub-bucket heads: hsv = inclusive max-scan of (sub-head ? s+1 : 0)
 	u32 hsv[ITEMS];

@@ -110,6 +110,24 @@ template <int CAP, int THREADS> struct TsDevicePass {
 	}
 };
 
+// Same network on the first `net` keys only (net = power of two, 32 <= net <= tile capacity,
+// uniform over the CTA): a tile that turned out half empty pays for the smaller network.
+template <int THREADS> struct TsDevicePassRt {
+	uint64_t *key; uint32_t net;
+	__device__ __forceinline__ void first() {
+		for (uint32_t g = threadIdx.x; g < net / 8; g += THREADS) ts_first_phases_group(key, g);
+		__syncthreads();
+	}
+	template <int NST> __device__ __forceinline__ void run(uint32_t k, uint32_t jtop) {
+		for (uint32_t g = threadIdx.x; g < (net >> NST); g += THREADS) ts_pass_group<NST>(key, k, jtop, g);
+		__syncthreads();
+	}
+};
+template <int THREADS> __device__ __forceinline__ void tile_bitonic_sort_rt(uint64_t *key, uint32_t net) {
+	TsDevicePassRt<THREADS> p{key, net};
+	ts_schedule(net, p);
+}
+
 // Sorts the tile ascending: key i lives at key[ts_sw(i)] before and after.  CAP is a power
 // of two >= 128; all THREADS threads of the CTA call it; the keys must be visible (barrier)
 // before the call and are visible after.
