@@ -45,7 +45,7 @@ __global__ void check_index_kernel(const u8 *__restrict__ T, const u32 *__restri
 void Pipeline::free_all() {
 	NG = IG = RK = NIA = start = rowlen = lastcol = nullptr;
 	T = nullptr; msa = nullptr;
-	col = ISA = SA = PLCP = NLCP = f = bnd = dp_a = dp_b = dp_v = nullptr;
+	col = ISA = SA = PLCP = f = bnd = dp_a = dp_b = dp_v = nullptr;
 	dev.pers_top = 0;
 	have_msa = have_index = have_f = have_seg = false;
 }

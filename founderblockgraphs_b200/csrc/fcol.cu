@@ -5,14 +5,15 @@
 // row suffixes; here one thread group owns one column and works on flat arrays:
 //
 //   p_i(x) = start_i + rank_i(x)                     (RK table + NG bitmap popcount)
-//   k_i    = ISA[p_i],  a_i = LCP[k_i] = PLCP[p_i],  b_i = LCP[k_i+1] = NLCP[p_i]
+//   k_i    = ISA[p_i],  a_i = LCP[k_i] = PLCP[p_i],  b_i = LCP[k_i+1] (the next row's a inside a
+//            run of consecutive ranks, PLCP[SA[k_i+1]] at a run's end)
 //   sort the active rows by k_i (bitonic network in shared memory)
 //   maximal runs of consecutive ranks = the reference's coloured leaf runs
 //   (fbg.cpp:1633-1641); segmented prefix-min of a / suffix-min of b over a run
 //   give  g = 1 + max(min LCP[a..k], min LCP[k+1..b+1])  = depth(parent(w)) + 1
 //   (fbg.cpp:1644-1656); then fi per fbg.cpp:1657-1670 and f[x] = max(x, max fi).
 //
-// All ISA/PLCP/NLCP reads of one row advance by one text position per column, so
+// All ISA/PLCP reads of one row advance by one text position per column, so
 // consecutive columns of a CTA re-use the same sectors.
 #include "pipeline.cuh"
 #include "blocksort.cuh"
@@ -22,9 +23,9 @@ namespace fbg {
 constexpr u64 KEY_INVALID = ~0ull;
 
 struct FcolArgs {
-	const u32 *NG, *IG, *RK, *NIA, *start, *rowlen, *lastcol, *col, *ISA, *PLCP, *NLCP;
+	const u32 *NG, *IG, *RK, *NIA, *start, *rowlen, *lastcol, *col, *ISA, *SA, *PLCP;
 	u32 *f;
-	u64 m, n;
+	u64 m, n, N;
 	u32 mpad;      // power of two >= m
 	u32 tpg;       // threads per column group
 	u32 groups;    // column groups per CTA
@@ -32,16 +33,16 @@ struct FcolArgs {
 	int tricks_off, has_ignore;
 };
 
-// dynamic smem per group: key u64[mpad] | A u32[mpad] | B u32[mpad] | L u32[mpad] | R u32[mpad] | fl u8[mpad] | fr u8[mpad]
+// dynamic smem per group: key u64[mpad] | A u32[mpad] | L u32[mpad] | R u32[mpad] | fl u8[mpad] | fr u8[mpad]
 __global__ void __launch_bounds__(1024) k2_fcol_kernel(FcolArgs a) {
 	extern __shared__ __align__(16) unsigned char k2_raw[];
 	const u32 mpad = a.mpad, tpg = a.tpg;
 	const u32 grp = threadIdx.x / tpg, tg = threadIdx.x % tpg;
-	const u64 per_group = (u64) mpad * (8 + 4 * 4 + 2);
+	const u64 per_group = (u64) mpad * (8 + 3 * 4 + 2);
 	unsigned char *basep = k2_raw + (u64) grp * per_group;
 	u64 *key = reinterpret_cast<u64 *>(basep);
 	u32 *A = reinterpret_cast<u32 *>(basep + (u64) mpad * 8);
-	u32 *B = A + mpad, *L = B + mpad, *R = L + mpad;
+	u32 *L = A + mpad, *R = L + mpad;
 	u8 *fl = reinterpret_cast<u8 *>(R + mpad), *fr = fl + mpad;
 	__shared__ u32 red[32];
 	const u64 m = a.m;
@@ -59,7 +60,7 @@ __global__ void __launch_bounds__(1024) k2_fcol_kernel(FcolArgs a) {
 				if (a.tricks_off || rk > 0) {
 					u64 p = (u64) a.start[i] + rk;
 					kk = ((u64) a.ISA[p] << 24) | i;
-					A[i] = a.PLCP[p]; B[i] = a.NLCP[p];
+					A[i] = a.PLCP[p];
 				}
 			}
 			key[ts_sw(i)] = kk;
@@ -74,10 +75,14 @@ __global__ void __launch_bounds__(1024) k2_fcol_kernel(FcolArgs a) {
 			if (kj != KEY_INVALID) {
 				u32 i = (u32) (kj & 0xFFFFFFu);
 				u64 r = kj >> 24;
-				lv = A[i]; rv = B[i];
+				lv = A[i];
 				s = (j == 0) || ((key[ts_sw(j - 1)] >> 24) + 1 != r);
 				u64 kn = j + 1 < mpad ? key[ts_sw(j + 1)] : KEY_INVALID;
 				e = (kn == KEY_INVALID) || ((kn >> 24) != r + 1);
+				// LCP[r+1]: inside a run it is the next element's own LCP value; only a run's
+				// last element has to look the foreign neighbour up (SA, then PLCP)
+				if (!e) rv = A[(u32) (kn & 0xFFFFFFu)];
+				else rv = r + 1 < a.N ? a.PLCP[a.SA[r + 1]] : 0u;
 			}
 			L[j] = lv; R[j] = rv; fl[j] = s; fr[j] = e;
 		}
@@ -141,8 +146,8 @@ void k2_compute_f(Pipeline &p) {
 	if (mpad > 8192) throw cuda_error("more than 8192 rows per column group is not supported by the shared-memory f(x) kernel yet");
 	FcolArgs a;
 	a.NG = p.NG; a.IG = p.IG; a.RK = p.RK; a.NIA = p.NIA; a.start = p.start; a.rowlen = p.rowlen; a.lastcol = p.lastcol;
-	a.col = p.col; a.ISA = p.ISA; a.PLCP = p.PLCP; a.NLCP = p.NLCP; a.f = p.f;
-	a.m = p.m; a.n = p.n; a.mpad = mpad;
+	a.col = p.col; a.ISA = p.ISA; a.SA = p.SA; a.PLCP = p.PLCP; a.f = p.f;
+	a.m = p.m; a.n = p.n; a.N = p.N; a.mpad = mpad;
 	// the Hillis-Steele phase keeps <= 8 elements per thread in registers
 	u32 threads = gc.threads;
 	a.tpg = gc.tpg; a.groups = gc.groups;
@@ -155,7 +160,7 @@ void k2_compute_f(Pipeline &p) {
 	}
 	a.tricks_off = p.opt.disable_tricks ? 1 : 0;
 	a.has_ignore = p.opt.n_ignore > 0 ? 1 : 0;
-	size_t smem = (size_t) a.groups * mpad * (8 + 16 + 2);
+	size_t smem = (size_t) a.groups * mpad * (8 + 12 + 2);
 	FBG_CUDA(cudaFuncSetAttribute(k2_fcol_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
 	u64 col_groups = (a.x1 - a.x0 + a.groups - 1) / a.groups;
 	if (col_groups == 0) col_groups = 1;
@@ -164,7 +169,7 @@ void k2_compute_f(Pipeline &p) {
 	d.begin(K_FCOL);
 	k2_fcol_kernel<<<grid, threads, smem, d.stream>>>(a);
 	FBG_LAUNCH_CHECK();
-	d.end((double) p.m * (double) (a.x1 - a.x0) * 16.0);
+	d.end((double) p.m * (double) (a.x1 - a.x0) * 12.0);
 	if (sharded) {
 		d.begin(K_COMM);
 		p.dist.allreduce_max_u32(p.f, p.n, d.stream);

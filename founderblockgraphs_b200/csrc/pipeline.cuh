@@ -9,8 +9,8 @@
 //   T      [N]   u8     gap-stripped rows, '#' after each, final 0 sentinel
 //   col    [N]   u32    text position -> MSA column ('#': n)
 //   ISA    [N]   u32    suffix rank of every text position
+//   SA     [N]   u32    suffix array (LCP construction; LCP[k+1] at run ends in K2)
 //   PLCP   [N]   u32    LCP[ISA[p]]      (text order)
-//   NLCP   [N]   u32    LCP[ISA[p]+1]    (text order; 0 at the last rank)
 //   f      [n]   u32    minimal right extension
 //   bnd    [nb]  u32    inclusive block end columns (elastic: last = n)
 #pragma once
@@ -48,7 +48,7 @@ struct Pipeline {
 	u32 *NG = nullptr, *IG = nullptr, *RK = nullptr, *NIA = nullptr;
 	u32 *start = nullptr, *rowlen = nullptr, *lastcol = nullptr;
 	u8 *T = nullptr;
-	u32 *col = nullptr, *ISA = nullptr, *SA = nullptr, *PLCP = nullptr, *NLCP = nullptr;
+	u32 *col = nullptr, *ISA = nullptr, *SA = nullptr, *PLCP = nullptr;
 	u32 *f = nullptr, *bnd = nullptr;
 	u32 *dp_a = nullptr, *dp_b = nullptr; // mml/backtrack or s/prev (+ v)
 	u32 *dp_v = nullptr;
@@ -79,7 +79,7 @@ void k4_graph(Pipeline &p, Graph &g, bool want_node_of);
 // bytes of the persistent arena one m x n MSA can need (N <= m*n + m + 1)
 static inline u64 persistent_need(u64 m, u64 n) {
 	u64 pitch = round_up(n, 32), W = pitch / 32, N = m * n + m + 1;
-	return m * pitch + 16 * W * m + 12 * (m + 1) + (N + 64) + 5 * 4 * (N + 1) + 6 * 4 * (n + 2) + 64 * 256;
+	return m * pitch + 16 * W * m + 12 * (m + 1) + (N + 64) + 4 * 4 * (N + 1) + 6 * 4 * (n + 2) + 64 * 256;
 }
 
 } // namespace fbg

@@ -661,18 +661,10 @@ __global__ void k1_plcp_kernel(u32 *__restrict__ M, u64 N) {
 	if (p < N) M[p] = M[p] - (u32) p;
 }
 
-// NLCP[SA[k]] = PLCP[SA[k+1]]  (0 for the last rank)
-__global__ void k1_nlcp_kernel(const u32 *__restrict__ SA, const u32 *__restrict__ PLCP, u64 N, u32 *__restrict__ NLCP) {
-	u64 k = (u64) blockIdx.x * blockDim.x + threadIdx.x;
-	if (k >= N) return;
-	NLCP[SA[k]] = (k + 1 < N) ? PLCP[SA[k + 1]] : 0u;
-}
-
 void k1_lcp(Pipeline &p) {
 	Dev &d = p.dev;
 	const u64 N = p.N;
 	p.PLCP = p.dev.palloc<u32>(N + 1);
-	p.NLCP = p.dev.palloc<u32>(N + 1);
 	d.ensure(N * 16 + (N / SCAN_TILE + 2) * 8 + (4u << 20));
 	u64 mk = d.mark();
 	u32 *flag = d.alloc<u32>(N), *pos = d.alloc<u32>(N), *ia = d.alloc<u32>(N), *ib = d.alloc<u32>(N);
@@ -700,10 +692,8 @@ void k1_lcp(Pipeline &p) {
 	device_scan<OpMaxU32, false>(d, p.PLCP, p.PLCP, N);
 	d.begin(K_LCP);
 	k1_plcp_kernel<<<g, 256, 0, d.stream>>>(p.PLCP, N);
-	k1_nlcp_kernel<<<g, 256, 0, d.stream>>>(p.SA, p.PLCP, N, p.NLCP);
 	FBG_LAUNCH_CHECK();
-	d.end((double) N * (8.0 + 4.0 + 4.0 + 4.0 + 4.0));
-	d.note_launches(K_LCP, 1);
+	d.end((double) N * 8.0);
 	d.release(mk);
 }
 
