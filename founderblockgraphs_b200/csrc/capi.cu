@@ -16,11 +16,6 @@ static std::string g_create_err;
 
 namespace fbg {
 
-__global__ void rs_widen_kernel(const u32 *__restrict__ c, u64 *__restrict__ o, u64 n) {
-	u64 i = (u64) blockIdx.x * blockDim.x + threadIdx.x;
-	if (i < n) o[i] = c[i];
-}
-
 // independent spot check of the index: random ranks k, direct text comparison
 __global__ void check_index_kernel(const u8 *__restrict__ T, const u32 *__restrict__ SA, const u32 *__restrict__ ISA, const u32 *__restrict__ PLCP,
                                    u64 N, u64 seed, u32 nsamples, u32 *__restrict__ bad) {

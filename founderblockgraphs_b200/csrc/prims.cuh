@@ -226,26 +226,29 @@ template <class Op, bool EXCL> void device_scan(Dev &d, const typename Op::T *in
 // -------------------------------------------------------------- radix sort
 // LSD radix sort of (key, u32 value) pairs, digits of <= 8 bits.
 // Per pass: (1) per-tile digit histogram staged in shared memory,
-//           (2) exclusive scan of the digit-major [bins x tiles] count matrix,
-//           (3) stable scatter: warp-level __match_any ranking, per-warp digit
-//               counters in shared memory, tile-local reorder in shared memory so
-//               the global writes of one digit are contiguous.
-constexpr int RS_THREADS = 256;
+//           (2) one CTA per digit: exclusive scan of that digit's counts over the tiles
+//               + the digit total (rs_binscan),
+//           (3) stable scatter: every CTA scans the 256 digit totals itself, ranks by
+//               warp-level __match_any, per-warp digit counters in shared memory, tile-local
+//               reorder in shared memory so the global writes of one digit are contiguous.
+constexpr int RS_THREADS = 512;          // scatter
 constexpr int RS_WARPS = RS_THREADS / 32;
-constexpr int RS_ITEMS = 16;
+constexpr int RS_ITEMS = 8;
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS; // 4096 keys per CTA
 constexpr int RS_BINS = 256;
+constexpr int RS_HTHREADS = 256;         // histogram: one thread per bin
+constexpr int RS_HITEMS = RS_TILE / RS_HTHREADS;
 
 template <typename K> __device__ __forceinline__ u32 rs_digit(K k, int shift, u32 mask) { return (u32) (k >> shift) & mask; }
 
-template <typename K> __global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const K *__restrict__ keys, u64 n, int shift, u32 mask, u32 ntiles, u32 *__restrict__ counts) {
+template <typename K> __global__ void __launch_bounds__(RS_HTHREADS) rs_hist_kernel(const K *__restrict__ keys, u64 n, int shift, u32 mask, u32 ntiles, u32 *__restrict__ counts) {
 	__shared__ u32 h[RS_BINS];
 	h[threadIdx.x] = 0;
 	__syncthreads();
 	u64 base = (u64) blockIdx.x * RS_TILE;
 #pragma unroll 4
-	for (int r = 0; r < RS_ITEMS; r++) {
-		u64 i = base + (u64) r * RS_THREADS + threadIdx.x;
+	for (int r = 0; r < RS_HITEMS; r++) {
+		u64 i = base + (u64) r * RS_HTHREADS + threadIdx.x;
 		bool ok = i < n;
 		u32 dg = ok ? rs_digit(keys[i], shift, mask) : 0xFFFFFFFFu;
 		// warp-aggregated shared-memory atomics
@@ -256,6 +259,22 @@ template <typename K> __global__ void __launch_bounds__(RS_THREADS) rs_hist_kern
 	counts[(u64) threadIdx.x * ntiles + blockIdx.x] = h[threadIdx.x];
 }
 
+// CTA d: counts[d][0..ntiles) -> exclusive prefix over the tiles (in place), totals[d] = sum
+static __global__ void __launch_bounds__(1024) rs_binscan_kernel(u32 *__restrict__ counts, u32 ntiles, u64 *__restrict__ totals) {
+	__shared__ u32 sm[32];
+	u32 *row = counts + (u64) blockIdx.x * ntiles;
+	u32 carry = 0;
+	for (u32 base = 0; base < ntiles; base += 1024) {
+		u32 i = base + threadIdx.x;
+		u32 v = i < ntiles ? row[i] : 0u;
+		u32 tot;
+		u32 ex = block_excl_scan<OpSumU32>(v, sm, &tot);
+		if (i < ntiles) row[i] = carry + ex;
+		carry += tot;
+	}
+	if (threadIdx.x == 0) totals[blockIdx.x] = carry;
+}
+
 template <typename K> struct RsSmem {
 	K keys[RS_TILE];
 	u32 vals[RS_TILE];
@@ -263,11 +282,13 @@ template <typename K> struct RsSmem {
 	u32 digit_base[RS_BINS];
 	u32 gbase_lo[RS_BINS];
 	u32 gbase_hi[RS_BINS];
-	u32 scan_sm[32];
+	u64 scan_sm[32];
+	u32 scan_sm32[32];
 };
 
-template <typename K, bool HAS_VAL> __global__ void __launch_bounds__(RS_THREADS)
-rs_scatter_kernel(const K *__restrict__ kin, const u32 *__restrict__ vin, K *__restrict__ kout, u32 *__restrict__ vout, u64 n, int shift, u32 mask, u32 ntiles, const u64 *__restrict__ offsets) {
+template <typename K, bool HAS_VAL> __global__ void __launch_bounds__(RS_THREADS, 2)
+rs_scatter_kernel(const K *__restrict__ kin, const u32 *__restrict__ vin, K *__restrict__ kout, u32 *__restrict__ vout, u64 n, int shift, u32 mask, u32 ntiles,
+                  const u32 *__restrict__ tile_off, const u64 *__restrict__ totals) {
 	extern __shared__ __align__(16) unsigned char rs_raw[];
 	RsSmem<K> &S = *reinterpret_cast<RsSmem<K> *>(rs_raw);
 	const u32 tid = threadIdx.x, w = tid >> 5, l = tid & 31;
@@ -275,7 +296,7 @@ rs_scatter_kernel(const K *__restrict__ kin, const u32 *__restrict__ vin, K *__r
 	__syncthreads();
 	const u64 tbase = (u64) blockIdx.x * RS_TILE;
 	const u32 tcount = (u32) (n - tbase < (u64) RS_TILE ? n - tbase : (u64) RS_TILE);
-	// warp-striped: warp w owns tile items [w*512, (w+1)*512), round r covers 32 consecutive keys
+	// warp-striped: warp w owns tile items [w*256, (w+1)*256), round r covers 32 consecutive keys
 	K key[RS_ITEMS];
 	u32 val[RS_ITEMS];
 	u32 rank[RS_ITEMS];
@@ -297,18 +318,27 @@ rs_scatter_kernel(const K *__restrict__ kin, const u32 *__restrict__ vin, K *__r
 		rank[r] = prev + __popc(peers & lanemask_lt());
 	}
 	__syncthreads();
-	// thread d: exclusive prefix over warps for digit d, digit totals, digit bases
+	// thread d < 256: exclusive prefix over warps for digit d, digit totals in the tile, digit
+	// bases in the tile and in the output (sum of the totals of the smaller digits + the tiles before)
 	{
 		u32 run = 0;
+		u64 gtot = 0;
+		if (tid < RS_BINS) {
 #pragma unroll
-		for (int ww = 0; ww < RS_WARPS; ww++) { u32 c = S.warp_cnt[ww][tid]; S.warp_cnt[ww][tid] = run; run += c; }
+			for (int ww = 0; ww < RS_WARPS; ww++) { u32 c = S.warp_cnt[ww][tid]; S.warp_cnt[ww][tid] = run; run += c; }
+			gtot = totals[tid];
+		}
 		u32 tot;
-		u32 ex = block_excl_scan<OpSumU32>(run, S.scan_sm, &tot);
-		S.digit_base[tid] = ex;
-		// padded keys (all ones) fall in the last bin after every real key, so the
-		// global base of a digit only depends on the scanned real counts
-		u64 g = offsets[(u64) tid * ntiles + blockIdx.x] - ex;
-		S.gbase_lo[tid] = (u32) g; S.gbase_hi[tid] = (u32) (g >> 32);
+		u32 ex = block_excl_scan<OpSumU32>(run, S.scan_sm32, &tot);
+		u64 gt;
+		u64 gex = block_excl_scan<OpSumU64>(gtot, S.scan_sm, &gt);
+		if (tid < RS_BINS) {
+			S.digit_base[tid] = ex;
+			// padded keys (all ones) fall in the last bin after every real key, so the
+			// global base of a digit only depends on the scanned real counts
+			u64 g = gex + tile_off[(u64) tid * ntiles + blockIdx.x] - ex;
+			S.gbase_lo[tid] = (u32) g; S.gbase_hi[tid] = (u32) (g >> 32);
+		}
 	}
 	__syncthreads();
 #pragma unroll
@@ -328,9 +358,6 @@ rs_scatter_kernel(const K *__restrict__ kin, const u32 *__restrict__ vin, K *__r
 	}
 }
 
-// The count matrix is scanned as u64 so totals beyond 2^32 keys stay exact.
-__global__ void rs_widen_kernel(const u32 *__restrict__ c, u64 *__restrict__ o, u64 n);
-
 struct RadixBuffers {
 	void *k[2]; u32 *v[2]; // ping-pong
 	int cur = 0;
@@ -344,7 +371,7 @@ template <typename K, bool HAS_VAL> int radix_sort(Dev &d, RadixBuffers &rb, u64
 	u32 ntiles = div_up(n, RS_TILE);
 	u64 mk = d.mark();
 	u32 *counts = d.alloc<u32>((u64) RS_BINS * ntiles);
-	u64 *offsets = d.alloc<u64>((u64) RS_BINS * ntiles);
+	u64 *totals = d.alloc<u64>(RS_BINS);
 	size_t smem = sizeof(RsSmem<K>);
 	FBG_CUDA(cudaFuncSetAttribute(rs_scatter_kernel<K, HAS_VAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
 	int bit = lo_bit;
@@ -354,14 +381,13 @@ template <typename K, bool HAS_VAL> int radix_sort(Dev &d, RadixBuffers &rb, u64
 		const K *kin = (const K *) rb.k[rb.cur];
 		K *kout = (K *) rb.k[rb.cur ^ 1];
 		d.begin(K_RADIX_HIST);
-		rs_hist_kernel<K><<<ntiles, RS_THREADS, 0, d.stream>>>(kin, n, bit, mask, ntiles, counts);
-		rs_widen_kernel<<<div_up((u64) RS_BINS * ntiles, 256), 256, 0, d.stream>>>(counts, offsets, (u64) RS_BINS * ntiles);
+		rs_hist_kernel<K><<<ntiles, RS_HTHREADS, 0, d.stream>>>(kin, n, bit, mask, ntiles, counts);
+		rs_binscan_kernel<<<RS_BINS, 1024, 0, d.stream>>>(counts, ntiles, totals);
 		FBG_LAUNCH_CHECK();
-		d.end((double) n * sizeof(K));
+		d.end((double) n * sizeof(K) + (double) RS_BINS * ntiles * 12.0);
 		d.note_launches(K_RADIX_HIST, 1);
-		device_scan<OpSumU64, true>(d, offsets, offsets, (u64) RS_BINS * ntiles);
 		d.begin(K_RADIX_SCATTER);
-		rs_scatter_kernel<K, HAS_VAL><<<ntiles, RS_THREADS, smem, d.stream>>>(kin, rb.v[rb.cur], kout, rb.v[rb.cur ^ 1], n, bit, mask, ntiles, offsets);
+		rs_scatter_kernel<K, HAS_VAL><<<ntiles, RS_THREADS, smem, d.stream>>>(kin, rb.v[rb.cur], kout, rb.v[rb.cur ^ 1], n, bit, mask, ntiles, counts, totals);
 		FBG_LAUNCH_CHECK();
 		d.end((double) n * (sizeof(K) + (HAS_VAL ? 4 : 0)) * 2.0);
 		rb.cur ^= 1;

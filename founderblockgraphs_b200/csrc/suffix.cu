@@ -115,7 +115,7 @@ __global__ void k1_heads_kernel(const u64 *__restrict__ keys, u64 na, int hi_shi
 
 // new rank = bucket rank + (sub-head index - bucket-head index); class by sub-bucket size
 __global__ void __launch_bounds__(256) k1_update_kernel(const u64 *__restrict__ keys, const u32 *__restrict__ vals, const u64 *__restrict__ HH, const u32 *__restrict__ HR,
-                                                        u64 na, int hi_shift, u32 rank_off, u32 *__restrict__ R, u32 *__restrict__ newr, u8 *__restrict__ cls, u32 *__restrict__ maxb) {
+                                                        u64 na, int hi_shift, u32 rank_off, u32 *__restrict__ R, u32 *__restrict__ SA, u32 *__restrict__ newr, u8 *__restrict__ cls, u32 *__restrict__ maxb) {
 	__shared__ u32 smax[8];
 	u64 t = (u64) blockIdx.x * blockDim.x + threadIdx.x;
 	u32 small_size = 0;
@@ -128,7 +128,9 @@ __global__ void __launch_bounds__(256) k1_update_kernel(const u64 *__restrict__ 
 		u32 nh = (t + 1 < na) ? (u32) na - HR[na - 2 - t] : (u32) na; // HR scanned: 0 = no head after t
 		u32 size = nh - hs;
 		u32 c = size == 1 ? CLS_DROP : (size <= BSMALL ? CLS_SMALL : CLS_BIG);
-		R[vals[t]] = nr;
+		const u32 pv = vals[t];
+		R[pv] = nr;
+		if (c == CLS_DROP) SA[nr] = pv; // a suffix alone in its bucket has its final rank: the SA entry is written as it leaves
 		newr[t] = nr;
 		cls[t] = (u8) c;
 		if (c == CLS_SMALL && hs == (u32) t) small_size = size;
@@ -257,7 +259,7 @@ template <int CAP> struct TileCfg {
 
 template <int CAP> __global__ void __launch_bounds__(TileCfg<CAP>::THREADS, TileCfg<CAP>::MINB)
 k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, const u32 *__restrict__ r2, u64 na, u32 tile,
-                    u32 *__restrict__ R, u32 *__restrict__ lp_out, u32 *__restrict__ lr_out, u8 *__restrict__ cls_out, u32 *__restrict__ scal) {
+                    u32 *__restrict__ R, u32 *__restrict__ SA, u32 *__restrict__ lp_out, u32 *__restrict__ lr_out, u8 *__restrict__ cls_out, u32 *__restrict__ scal) {
 	constexpr int THREADS = TileCfg<CAP>::THREADS;
 	constexpr int ITEMS = CAP / THREADS;
 	constexpr int NW = THREADS / 32;
@@ -368,10 +370,12 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 			bool last = (s + 1 >= cnt) || ((key[ts_sw(s + 1)] >> LOGC) != (k >> LOGC));
 			u32 nr = lr[g0 + hb] + (hs - hb);
 			u32 p = lp[g0 + irel];
+			const bool single = hs == s && last;
 			R[p] = nr;
+			if (single) SA[nr] = p;
 			lp_out[g0 + s] = p;
 			lr_out[g0 + s] = nr;
-			cls_out[g0 + s] = (u8) ((hs == s && last) ? CLS_DROP : CLS_SMALL);
+			cls_out[g0 + s] = (u8) (single ? CLS_DROP : CLS_SMALL);
 			if (last && s != hs) { u32 sz = s - hs + 1; mx = sz > mx ? sz : mx; }
 		}
 	}
@@ -380,11 +384,11 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 }
 
 template <int CAP> static void launch_tile_sort(Dev &d, const u32 *lp, const u32 *lr, const u32 *r2, u64 na, u32 maxb,
-                                                u32 *R, u32 *lp_out, u32 *lr_out, u8 *cls_out, u32 *scal) {
+                                                u32 *R, u32 *SA, u32 *lp_out, u32 *lr_out, u8 *cls_out, u32 *scal) {
 	u32 tile = (u32) CAP - maxb;
 	size_t smem = (size_t) CAP * 8;
 	FBG_CUDA(cudaFuncSetAttribute(k1_tile_sort_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-	k1_tile_sort_kernel<CAP><<<div_up(na, tile), TileCfg<CAP>::THREADS, smem, d.stream>>>(lp, lr, r2, na, tile, R, lp_out, lr_out, cls_out, scal);
+	k1_tile_sort_kernel<CAP><<<div_up(na, tile), TileCfg<CAP>::THREADS, smem, d.stream>>>(lp, lr, r2, na, tile, R, SA, lp_out, lr_out, cls_out, scal);
 	FBG_LAUNCH_CHECK();
 }
 
@@ -530,9 +534,9 @@ void k1_suffix_array(Pipeline &p) {
 		// ---- S path
 		if (nS) {
 			d.begin(K_TILE_SORT);
-			if (2 * maxb <= 2048) launch_tile_sort<2048>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, lp_out, lr_out, clsS, sc32);
-			else if (2 * maxb <= 8192) launch_tile_sort<8192>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, lp_out, lr_out, clsS, sc32);
-			else launch_tile_sort<16384>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, lp_out, lr_out, clsS, sc32);
+			if (2 * maxb <= 2048) launch_tile_sort<2048>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
+			else if (2 * maxb <= 8192) launch_tile_sort<8192>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
+			else launch_tile_sort<16384>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
 			d.end((double) nS * (12.0 + 4.0 + 9.0));
 		}
 		// ---- B path
@@ -549,7 +553,7 @@ void k1_suffix_array(Pipeline &p) {
 			device_scan<OpMax2x32, false>(d, HH, HH, nB);
 			device_scan<OpMaxU32, false>(d, HR, HR, nB);
 			d.begin(K_DOUBLING_AUX);
-			k1_update_kernel<<<g, 256, 0, d.stream>>>(sk, sv, HH, HR, nB, hi_shift, rank_off, p.ISA, newr, clsB, sc32);
+			k1_update_kernel<<<g, 256, 0, d.stream>>>(sk, sv, HH, HR, nB, hi_shift, rank_off, p.ISA, p.SA, newr, clsB, sc32);
 			FBG_LAUNCH_CHECK();
 			d.end((double) nB * (8.0 + 4.0 + 8.0 + 4.0 + 4.0 + 4.0 + 1.0));
 		}
@@ -608,10 +612,13 @@ void k1_suffix_array(Pipeline &p) {
 		key_bits = 2 * nbits;
 		h *= 2;
 	}
-	d.begin(K_DOUBLING_AUX);
-	k1_invert_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(p.ISA, N, p.SA);
-	FBG_LAUNCH_CHECK();
-	d.end((double) N * 8.0);
+	if (sharded) {
+		// every GPU wrote the SA entries of its own suffixes only; the merged rank array gives the rest
+		d.begin(K_DOUBLING_AUX);
+		k1_invert_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(p.ISA, N, p.SA);
+		FBG_LAUNCH_CHECK();
+		d.end((double) N * 8.0);
+	}
 	d.release(mk);
 }
 
