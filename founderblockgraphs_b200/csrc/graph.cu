@@ -218,7 +218,7 @@ void k4_graph(Pipeline &p, Graph &g, bool want_node_of) {
 	if (R >= 0xFFFFFFF0ull) throw cuda_error("more than 2^32 (row,block) records");
 	GroupCfg gc = group_cfg(m);
 	if (gc.mpad > 8192) throw cuda_error("more than 8192 rows is not supported by the shared-memory dedup kernel yet");
-	d.ensure(R * 64 + (nb + 1) * 12 + (R / SCAN_TILE + 2) * 8 + (4u << 20));
+	d.ensure(R * 64 + (nb + 1) * 12 + (R / SCAN_TILE + 2) * 24 + (4u << 20));
 	u64 mk = d.mark();
 	u64 *H1 = d.alloc<u64>(R), *H2 = d.alloc<u64>(R);
 	u32 *LEN = d.alloc<u32>(R), *POS = d.alloc<u32>(R), *REP = d.alloc<u32>(R), *HEAD = d.alloc<u32>(R), *NIDX = d.alloc<u32>(R);

@@ -206,20 +206,102 @@ template <class Op, bool EXCL> __global__ void __launch_bounds__(SCAN_THREADS) s
 	}
 }
 
+// Single-pass scan with decoupled look-back: tiles take tickets in launch order, publish
+// their aggregate, and warp 0 walks back over the predecessors (32 at a time) until it meets
+// a tile whose inclusive prefix is already known.  Traffic: one read + one write of the data.
+// Every operator used here is commutative, so the walk may combine in any order.
+// state per tile: flag (0 nothing, 1 aggregate, 2 inclusive prefix), agg, incl.
+template <class Op> __device__ __forceinline__ typename Op::T warp_reduce_op(typename Op::T v) {
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) v = Op::f(v, __shfl_xor_sync(0xffffffffu, v, o));
+	return v;
+}
+
+template <class Op, bool EXCL> __global__ void __launch_bounds__(SCAN_THREADS)
+scan_lookback_kernel(const typename Op::T *in, typename Op::T *out, u64 n, u32 *flag, typename Op::T *agg, typename Op::T *incl, u32 *ticket, typename Op::T *total_out) {
+	typedef typename Op::T T;
+	__shared__ T sm[32];
+	__shared__ T s_prefix;
+	__shared__ u32 s_tile;
+	if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+	__syncthreads();
+	const u32 tile = s_tile;
+	const u32 ntiles = gridDim.x;
+	// warp-striped: warp w owns 32*SCAN_ITEMS consecutive elements, lane l takes element i*32+l
+	// of round i (coalesced); v[i] = scan value inside the warp's chunk (exclusive if EXCL)
+	const u32 wi = threadIdx.x >> 5, li = threadIdx.x & 31;
+	const u64 base = (u64) tile * SCAN_TILE + (u64) wi * (32 * SCAN_ITEMS) + li;
+	T v[SCAN_ITEMS];
+	T carry = Op::id();
+#pragma unroll
+	for (int i = 0; i < SCAN_ITEMS; i++) {
+		const u64 idx = base + (u64) i * 32;
+		T x = idx < n ? in[idx] : Op::id();
+		T inc = Op::f(carry, warp_incl_scan<Op>(x));
+		if (EXCL) {
+			T ex = __shfl_up_sync(0xffffffffu, inc, 1);
+			v[i] = li == 0 ? carry : ex;
+		} else v[i] = inc;
+		carry = __shfl_sync(0xffffffffu, inc, 31);
+	}
+	// carry = total of the warp's chunk (same on every lane); scan the warp totals
+	if (li == 0) sm[wi] = carry;
+	__syncthreads();
+	T pre = Op::id(), tot = Op::id();
+	for (u32 ww = 0; ww < SCAN_THREADS / 32; ww++) { T t = sm[ww]; if (ww < wi) pre = Op::f(pre, t); tot = Op::f(tot, t); }
+	if (threadIdx.x < 32) {
+		const u32 l = threadIdx.x;
+		T run = Op::id();
+		if (tile == 0) {
+			if (l == 0) { incl[0] = tot; __threadfence(); *reinterpret_cast<volatile u32 *>(&flag[0]) = 2u; }
+		} else {
+			if (l == 0) { agg[tile] = tot; __threadfence(); *reinterpret_cast<volatile u32 *>(&flag[tile]) = 1u; }
+			i64 tb = (i64) tile - 1;
+			for (;;) {
+				i64 t = tb - (i64) l;
+				u32 f = 2u;
+				T c = Op::id();
+				if (t >= 0) {
+					do { f = *reinterpret_cast<volatile u32 *>(&flag[t]); } while (f == 0u);
+					__threadfence();
+					c = f == 2u ? *reinterpret_cast<volatile T *>(&incl[t]) : *reinterpret_cast<volatile T *>(&agg[t]);
+				}
+				const u32 m2 = __ballot_sync(0xffffffffu, f == 2u);
+				const u32 first = (u32) (__ffs(m2) - 1); // m2 != 0 at the latest when the walk passes tile 0
+				if (m2 && l > first) c = Op::id();
+				run = Op::f(run, warp_reduce_op<Op>(c));
+				if (m2) break;
+				tb -= 32;
+			}
+			if (l == 0) { incl[tile] = Op::f(run, tot); __threadfence(); *reinterpret_cast<volatile u32 *>(&flag[tile]) = 2u; }
+		}
+		if (l == 0) {
+			s_prefix = run;
+			if (tile == ntiles - 1 && total_out) *total_out = Op::f(run, tot);
+		}
+	}
+	__syncthreads();
+	pre = Op::f(s_prefix, pre);
+#pragma unroll
+	for (int i = 0; i < SCAN_ITEMS; i++) {
+		const u64 idx = base + (u64) i * 32;
+		if (idx < n) out[idx] = Op::f(pre, v[i]);
+	}
+}
+
 // Device-wide scan. in/out may alias. total_out: optional device scalar receiving the grand total.
 template <class Op, bool EXCL> void device_scan(Dev &d, const typename Op::T *in, typename Op::T *out, u64 n, typename Op::T *total_out = nullptr) {
 	typedef typename Op::T T;
 	if (n == 0) { if (total_out) FBG_CUDA(cudaMemsetAsync(total_out, 0, sizeof(T), d.stream)); return; }
 	u32 nt = div_up(n, SCAN_TILE);
 	u64 mk = d.mark();
-	T *partial = d.alloc<T>(nt);
+	u32 *flag = d.alloc<u32>((u64) nt + 1); // [nt] = ticket counter
+	T *agg = d.alloc<T>(nt), *incl = d.alloc<T>(nt);
 	d.begin(K_SCAN);
-	scan_reduce_kernel<Op><<<nt, SCAN_THREADS, 0, d.stream>>>(in, n, partial);
-	scan_partials_kernel<Op><<<1, 1024, 0, d.stream>>>(partial, nt, total_out);
-	scan_apply_kernel<Op, EXCL><<<nt, SCAN_THREADS, 0, d.stream>>>(in, out, n, partial);
+	FBG_CUDA(cudaMemsetAsync(flag, 0, ((u64) nt + 1) * sizeof(u32), d.stream));
+	scan_lookback_kernel<Op, EXCL><<<nt, SCAN_THREADS, 0, d.stream>>>(in, out, n, flag, agg, incl, flag + nt, total_out);
 	FBG_LAUNCH_CHECK();
-	d.end((double) n * sizeof(T) * 3.0);
-	d.note_launches(K_SCAN, 2);
+	d.end((double) n * sizeof(T) * 2.0);
 	d.release(mk);
 }
 

@@ -551,7 +551,7 @@ void k3_segment(Pipeline &p) {
 	const u64 n = p.n;
 	if (!p.bnd) p.bnd = p.dev.palloc<u32>(n + 2);
 	if (!p.dp_a) { p.dp_a = p.dev.palloc<u32>(n + 2); p.dp_b = p.dev.palloc<u32>(n + 2); p.dp_v = p.dev.palloc<u32>(n + 2); }
-	d.ensure((n + 2) * 12 + (n / 16 + 4) * 4 + (n / SCAN_TILE + 2) * 8 + (1u << 20));
+	d.ensure((n + 2) * 12 + (n / 16 + 4) * 4 + (n / SCAN_TILE + 2) * 24 + (1u << 20));
 	u64 mk = d.mark();
 	u32 *rev = d.alloc<u32>(n + 2);
 	u64 *out = p.scalars + 16;

@@ -481,7 +481,7 @@ void k1_suffix_array(Pipeline &p) {
 	// scratch of this phase: 74 B per suffix sorted here (sort ping-pong 24, heads 16, classes 2,
 	// S lists 24, tile outputs 8) + radix count matrices + (sharded) the N-word bucket directory
 	d.release(mk);
-	d.ensure(cap * 76 + (cap / RS_TILE + 2) * RS_BINS * 12 + (u64) km_grid * 8 + (sharded ? N * 4 + (N / SCAN_TILE + 2) * 8 : 0) + (16u << 20));
+	d.ensure(cap * 76 + (cap / RS_TILE + 2) * RS_BINS * 12 + (u64) km_grid * 8 + (sharded ? N * 4 + (N / SCAN_TILE + 2) * 24 : 0) + (16u << 20));
 	mk = d.mark();
 
 	RadixBuffers rb;
@@ -672,7 +672,7 @@ void k1_lcp(Pipeline &p) {
 	Dev &d = p.dev;
 	const u64 N = p.N;
 	p.PLCP = p.dev.palloc<u32>(N + 1);
-	d.ensure(N * 16 + (N / SCAN_TILE + 2) * 8 + (4u << 20));
+	d.ensure(N * 16 + (N / SCAN_TILE + 2) * 24 + (4u << 20));
 	u64 mk = d.mark();
 	u32 *flag = d.alloc<u32>(N), *pos = d.alloc<u32>(N), *ia = d.alloc<u32>(N), *ib = d.alloc<u32>(N);
 	u32 *total = reinterpret_cast<u32 *>(p.scalars + 8);
