@@ -204,12 +204,19 @@ __global__ void k4_edge_gather_kernel(u64 m, u64 nb, const u64 *__restrict__ PAI
 	es[o] = (u32) (pr >> 32); ed[o] = (u32) pr;
 }
 
-template <typename T> static void d2h(std::vector<T> &dst, const u32 *src, u64 count, cudaStream_t s) {
-	std::vector<u32> tmp(count);
-	if (count) FBG_CUDA(cudaMemcpyAsync(tmp.data(), src, count * sizeof(u32), cudaMemcpyDeviceToHost, s));
-	FBG_CUDA(cudaStreamSynchronize(s));
+__global__ void k4_widen_kernel(const u32 *__restrict__ src, u64 *__restrict__ dst, u64 count) {
+	u64 i = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < count) dst[i] = src[i];
+}
+
+// the C ABI hands out 64-bit arrays: widen on the device, one copy into the final vector
+static void d2h(std::vector<u64> &dst, const u32 *src, u64 count, u64 *wide, cudaStream_t s) {
 	dst.resize(count);
-	for (u64 i = 0; i < count; i++) dst[i] = tmp[i];
+	if (count) {
+		k4_widen_kernel<<<div_up(count, 256), 256, 0, s>>>(src, wide, count);
+		FBG_CUDA(cudaMemcpyAsync(dst.data(), wide, count * sizeof(u64), cudaMemcpyDeviceToHost, s));
+	}
+	FBG_CUDA(cudaStreamSynchronize(s));
 }
 
 void k4_graph(Pipeline &p, Graph &g, bool want_node_of) {
@@ -218,7 +225,7 @@ void k4_graph(Pipeline &p, Graph &g, bool want_node_of) {
 	if (R >= 0xFFFFFFF0ull) throw cuda_error("more than 2^32 (row,block) records");
 	GroupCfg gc = group_cfg(m);
 	if (gc.mpad > 8192) throw cuda_error("more than 8192 rows is not supported by the shared-memory dedup kernel yet");
-	d.ensure(R * 64 + (nb + 1) * 12 + (R / SCAN_TILE + 2) * 24 + (4u << 20));
+	d.ensure(R * 72 + (nb + 1) * 12 + (R / SCAN_TILE + 2) * 24 + (4u << 20));
 	u64 mk = d.mark();
 	u64 *H1 = d.alloc<u64>(R), *H2 = d.alloc<u64>(R);
 	u32 *LEN = d.alloc<u32>(R), *POS = d.alloc<u32>(R), *REP = d.alloc<u32>(R), *HEAD = d.alloc<u32>(R), *NIDX = d.alloc<u32>(R);
@@ -226,6 +233,7 @@ void k4_graph(Pipeline &p, Graph &g, bool want_node_of) {
 	u32 *heights = d.alloc<u32>(nb + 1), *EC = d.alloc<u32>(nb + 1), *EOFF = d.alloc<u32>(nb + 1);
 	u64 *PAIRS = d.alloc<u64>(R);
 	u32 *es = d.alloc<u32>(R), *ed = d.alloc<u32>(R);
+	u64 *wide = d.alloc<u64>(R > nb ? R : nb + 1);
 	u32 *bad = reinterpret_cast<u32 *>(p.scalars + 32);
 	u32 *tot_nodes = reinterpret_cast<u32 *>(p.scalars + 33);
 	u32 *tot_edges = reinterpret_cast<u32 *>(p.scalars + 34);
@@ -273,11 +281,11 @@ void k4_graph(Pipeline &p, Graph &g, bool want_node_of) {
 	FBG_CUDA(cudaStreamSynchronize(d.stream));
 	u64 nn = *reinterpret_cast<u32 *>(p.h_scalars + 33), ne = *reinterpret_cast<u32 *>(p.h_scalars + 34);
 	g.label_total = p.h_scalars[35];
-	d2h(g.heights, heights, nb, d.stream);
-	d2h(g.node_block, node_block, nn, d.stream);
-	d2h(g.node_row, node_row, nn, d.stream);
-	d2h(g.edge_src, es, ne, d.stream);
-	d2h(g.edge_dst, ed, ne, d.stream);
+	d2h(g.heights, heights, nb, wide, d.stream);
+	d2h(g.node_block, node_block, nn, wide, d.stream);
+	d2h(g.node_row, node_row, nn, wide, d.stream);
+	d2h(g.edge_src, es, ne, wide, d.stream);
+	d2h(g.edge_dst, ed, ne, wide, d.stream);
 	g.node_of.clear();
 	if (want_node_of) {
 		g.node_of.resize(R);

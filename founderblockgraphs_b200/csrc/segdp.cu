@@ -50,7 +50,13 @@ template <class STEP> __device__ __forceinline__ u64 dp_chase(const u32 *link, u
 	for (;;) {
 		u64 cb = j + 1 >= DP_CH ? j + 1 - DP_CH : 0;
 		__syncwarp();
-		for (u32 i = l; i < DP_CH && cb + i <= j; i += 32) stage[i] = __ldcg(&link[cb + i]);
+		for (u32 i0 = 0; i0 < DP_CH && cb + i0 <= j; i0 += 256) { // eight independent loads in flight per lane
+			u32 tmp[8];
+#pragma unroll
+			for (int q = 0; q < 8; q++) { u32 i = i0 + q * 32 + l; tmp[q] = cb + i <= j ? __ldcg(&link[cb + i]) : 0u; }
+#pragma unroll
+			for (int q = 0; q < 8; q++) stage[i0 + q * 32 + l] = tmp[q];
+		}
 		__syncwarp();
 		bool done = false;
 		for (;;) {

@@ -392,11 +392,6 @@ template <int CAP> static void launch_tile_sort(Dev &d, const u32 *lp, const u32
 	FBG_LAUNCH_CHECK();
 }
 
-__global__ void k1_invert_kernel(const u32 *__restrict__ R, u64 N, u32 *__restrict__ SA) {
-	u64 p = (u64) blockIdx.x * blockDim.x + threadIdx.x;
-	if (p < N) SA[R[p]] = (u32) p;
-}
-
 // Appends the survivors of one sorted list to the next S / B lists.  *total_out receives
 // this call's (small | big << 32) counts; base (device word, same packing) = where to append.
 static void compact_lists(Dev &d, const u8 *cls, const u32 *lp, const u32 *lr, u64 na, const u64 *base, u64 *total_out, bool skip_small,
@@ -509,6 +504,7 @@ void k1_suffix_array(Pipeline &p) {
 		scan_partials_kernel<OpSumU64><<<1, 1024, 0, d.stream>>>(bc, km_grid, nullptr);
 		k1_kmer_kernel<3><<<km_grid, KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, sh, (u64 *) rb.k[0], rb.v[0]);
 		FBG_CUDA(cudaMemsetAsync(p.ISA, 0, N * sizeof(u32), d.stream)); // replicas are merged by max
+		FBG_CUDA(cudaMemsetAsync(p.SA, 0, N * sizeof(u32), d.stream));
 		FBG_CUDA(cudaStreamSynchronize(d.stream)); // bc is released below
 		d.release(mk2);
 		d.note_launches(K_KMER, 2);
@@ -613,10 +609,9 @@ void k1_suffix_array(Pipeline &p) {
 		h *= 2;
 	}
 	if (sharded) {
-		// every GPU wrote the SA entries of its own suffixes only; the merged rank array gives the rest
-		d.begin(K_DOUBLING_AUX);
-		k1_invert_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(p.ISA, N, p.SA);
-		FBG_LAUNCH_CHECK();
+		// every GPU wrote the SA entries of its own suffixes only (the rest is still 0): merge like the ranks
+		d.begin(K_COMM);
+		dist.allreduce_max_u32(p.SA, N, d.stream);
 		d.end((double) N * 8.0);
 	}
 	d.release(mk);
