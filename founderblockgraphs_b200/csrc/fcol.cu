@@ -28,24 +28,56 @@ struct FcolArgs {
 	u64 m, n, N;
 	u32 mpad;      // power of two >= m
 	u32 tpg;       // threads per column group
+	u32 E;         // sorted slots per thread (mpad / tpg)
 	u32 groups;    // column groups per CTA
 	u64 x0, x1;    // column range [x0, x1)
 	int tricks_off, has_ignore;
 };
 
-// dynamic smem per group: key u64[mpad] | A u32[mpad] | L u32[mpad] | R u32[mpad] | fl u8[mpad] | fr u8[mpad]
+// One column group = tpg threads over mpad = tpg * E sorted slots (E <= 8 consecutive slots
+// per thread, held in registers after the sort).
+struct FcolCfg { u32 mpad, tpg, groups, threads, E; };
+static inline FcolCfg fcol_cfg(u64 m) {
+	FcolCfg c;
+	c.mpad = 32;
+	while (c.mpad < m) c.mpad <<= 1;
+	c.tpg = c.mpad / 8;
+	if (c.tpg < 32) c.tpg = 32;
+	c.E = c.mpad / c.tpg;
+	c.threads = c.tpg < 256 ? 256 : c.tpg;
+	c.groups = c.threads / c.tpg;
+	return c;
+}
+
+// Inclusive segmented min over the lanes of a warp, towards higher lanes (UP) or lower
+// lanes (!UP): a lane whose flag is set starts a new segment.
+template <bool UP> __device__ __forceinline__ void warp_seg_min(u32 &v, bool &fl) {
+	const u32 lane = lane_id();
+#pragma unroll
+	for (int d = 1; d < 32; d <<= 1) {
+		u32 ov = UP ? __shfl_up_sync(0xFFFFFFFFu, v, d) : __shfl_down_sync(0xFFFFFFFFu, v, d);
+		int of = UP ? __shfl_up_sync(0xFFFFFFFFu, (int) fl, d) : __shfl_down_sync(0xFFFFFFFFu, (int) fl, d);
+		const bool in = UP ? lane >= (u32) d : lane + (u32) d < 32u;
+		if (in && !fl) { v = ov < v ? ov : v; fl = of != 0; }
+	}
+}
+
+// dynamic smem per group: key u64[mpad] | A u32[mpad] (PLCP of row i) | RKS u32[mpad] (rank of row i)
 __global__ void __launch_bounds__(1024) k2_fcol_kernel(FcolArgs a) {
 	extern __shared__ __align__(16) unsigned char k2_raw[];
-	const u32 mpad = a.mpad, tpg = a.tpg;
+	const u32 mpad = a.mpad, tpg = a.tpg, E = a.E;
 	const u32 grp = threadIdx.x / tpg, tg = threadIdx.x % tpg;
-	const u64 per_group = (u64) mpad * (8 + 3 * 4 + 2);
+	const u64 per_group = (u64) mpad * 16;
 	unsigned char *basep = k2_raw + (u64) grp * per_group;
 	u64 *key = reinterpret_cast<u64 *>(basep);
 	u32 *A = reinterpret_cast<u32 *>(basep + (u64) mpad * 8);
-	u32 *L = A + mpad, *R = L + mpad;
-	u8 *fl = reinterpret_cast<u8 *>(R + mpad), *fr = fl + mpad;
+	u32 *RKS = A + mpad;
 	__shared__ u32 red[32];
+	__shared__ u32 wl[32], wr[32];      // per warp: segmented aggregate (value), towards the right / the left
+	__shared__ u32 wfl[32], wfr[32];    // per warp: a run start / a run end inside the warp
 	const u64 m = a.m;
+	const u32 wid = threadIdx.x >> 5, lane = lane_id();
+	const u32 w_first = (grp * tpg) >> 5, w_last = w_first + (tpg >> 5) - 1;
 
 	for (u64 xb = a.x0 + (u64) blockIdx.x * a.groups; xb < a.x1; xb += (u64) gridDim.x * a.groups) {
 		const u64 x = xb + grp;
@@ -61,6 +93,7 @@ __global__ void __launch_bounds__(1024) k2_fcol_kernel(FcolArgs a) {
 					u64 p = (u64) a.start[i] + rk;
 					kk = ((u64) a.ISA[p] << 24) | i;
 					A[i] = a.PLCP[p];
+					RKS[i] = rk;
 				}
 			}
 			key[ts_sw(i)] = kk;
@@ -68,70 +101,98 @@ __global__ void __launch_bounds__(1024) k2_fcol_kernel(FcolArgs a) {
 		__syncthreads();
 		// 2. bitonic sort ascending by (rank, row)
 		group_tile_sort(key, mpad, tg, tpg);
-		// 3. run flags + initial values (sorted order)
-		for (u32 j = tg; j < mpad; j += tpg) {
-			u64 kj = key[ts_sw(j)];
-			u32 lv = U32_MAX, rv = U32_MAX; u8 s = 1, e = 1;
-			if (kj != KEY_INVALID) {
-				u32 i = (u32) (kj & 0xFFFFFFu);
-				u64 r = kj >> 24;
-				lv = A[i];
-				s = (j == 0) || ((key[ts_sw(j - 1)] >> 24) + 1 != r);
-				u64 kn = j + 1 < mpad ? key[ts_sw(j + 1)] : KEY_INVALID;
-				e = (kn == KEY_INVALID) || ((kn >> 24) != r + 1);
-				// LCP[r+1]: inside a run it is the next element's own LCP value; only a run's
-				// last element has to look the foreign neighbour up (SA, then PLCP)
-				if (!e) rv = A[(u32) (kn & 0xFFFFFFu)];
-				else rv = r + 1 < a.N ? a.PLCP[a.SA[r + 1]] : 0u;
+		// 3. the thread's E consecutive sorted slots: run flags, LCP[k] and LCP[k+1]
+		const u32 j0 = tg * E;
+		u32 row[8], lv[8], rv[8];
+		u32 smask = 0, emask = 0, vmask = 0;
+		u64 kprev = j0 ? key[ts_sw(j0 - 1)] : KEY_INVALID;
+		u64 kcur = key[ts_sw(j0)];
+#pragma unroll
+		for (u32 c = 0; c < 8; c++) {
+			if (c < E) {
+				const u32 j = j0 + c;
+				const u64 kn = j + 1 < mpad ? key[ts_sw(j + 1)] : KEY_INVALID;
+				lv[c] = U32_MAX; rv[c] = U32_MAX; row[c] = 0;
+				bool s = true, e = true;
+				if (kcur != KEY_INVALID) {
+					const u32 i = (u32) (kcur & 0xFFFFFFu);
+					const u64 r = kcur >> 24;
+					row[c] = i;
+					vmask |= 1u << c;
+					lv[c] = A[i];
+					s = (j == 0) || ((kprev >> 24) + 1 != r);
+					e = (kn == KEY_INVALID) || ((kn >> 24) != r + 1);
+					// LCP[r+1]: inside a run it is the next element's own LCP value; only a run's
+					// last element has to look the foreign neighbour up (SA, then PLCP)
+					if (!e) rv[c] = A[(u32) (kn & 0xFFFFFFu)];
+					else rv[c] = r + 1 < a.N ? a.PLCP[a.SA[r + 1]] : 0u;
+				}
+				smask |= (u32) s << c; emask |= (u32) e << c;
+				kprev = kcur; kcur = kn;
 			}
-			L[j] = lv; R[j] = rv; fl[j] = s; fr[j] = e;
 		}
+		// 4. segmented prefix-min of lv (run starts) and suffix-min of rv (run ends):
+		//    inside the thread, across the warp by shuffles, across the group's warps through
+		//    the per-warp aggregates
+		u32 runl = U32_MAX, runr = U32_MAX;
+#pragma unroll
+		for (u32 c = 0; c < 8; c++)
+			if (c < E) { runl = ((smask >> c) & 1u) ? lv[c] : (lv[c] < runl ? lv[c] : runl); lv[c] = runl; }
+#pragma unroll
+		for (int c = 7; c >= 0; c--)
+			if ((u32) c < E) { runr = ((emask >> c) & 1u) ? rv[c] : (rv[c] < runr ? rv[c] : runr); rv[c] = runr; }
+		u32 sl = runl, sr = runr;
+		bool fl = smask != 0, fr = emask != 0;
+		warp_seg_min<true>(sl, fl);
+		warp_seg_min<false>(sr, fr);
+		if (lane == 31) { wl[wid] = sl; wfl[wid] = fl; }
+		if (lane == 0) { wr[wid] = sr; wfr[wid] = fr; }
+		// what the neighbouring lanes carry into this thread
+		u32 pl = __shfl_up_sync(0xFFFFFFFFu, sl, 1), pr = __shfl_down_sync(0xFFFFFFFFu, sr, 1);
+		int pfl = __shfl_up_sync(0xFFFFFFFFu, (int) fl, 1), pfr = __shfl_down_sync(0xFFFFFFFFu, (int) fr, 1);
 		__syncthreads();
-		// 4. segmented prefix-min (L, run starts) and suffix-min (R, run ends), Hillis-Steele
-		for (u32 o = 1; o < mpad; o <<= 1) {
-			// read phase into registers (each thread owns the same j's in both phases)
-			u32 nl[8], nr[8]; u8 nfl[8], nfr[8];
-			u32 c = 0;
-			for (u32 j = tg; j < mpad; j += tpg, c++) {
-				u32 lv = L[j], rv = R[j]; u8 s = fl[j], e = fr[j];
-				if (!s && j >= o) { u32 q = L[j - o]; lv = q < lv ? q : lv; s = fl[j - o]; }
-				if (!e && j + o < mpad) { u32 q = R[j + o]; rv = q < rv ? q : rv; e = fr[j + o]; }
-				nl[c] = lv; nr[c] = rv; nfl[c] = s; nfr[c] = e;
-			}
-			__syncthreads();
-			c = 0;
-			for (u32 j = tg; j < mpad; j += tpg, c++) { L[j] = nl[c]; R[j] = nr[c]; fl[j] = nfl[c]; fr[j] = nfr[c]; }
-			__syncthreads();
-		}
+		u32 cl = U32_MAX, cr = U32_MAX;      // carry from the warps before / after this one
+		for (u32 w = wid; w > w_first; w--) { u32 q = wl[w - 1]; cl = q < cl ? q : cl; if (wfl[w - 1]) break; }
+		for (u32 w = wid; w < w_last; w++) { u32 q = wr[w + 1]; cr = q < cr ? q : cr; if (wfr[w + 1]) break; }
+		if (lane > 0) cl = pfl ? pl : (pl < cl ? pl : cl);
+		if (lane < 31) cr = pfr ? pr : (pr < cr ? pr : cr);
 		// 5. fi per row, max over the column
 		u32 fmax = 0;
-		for (u32 j = tg; j < mpad; j += tpg) {
-			u64 kj = key[ts_sw(j)];
-			if (kj == KEY_INVALID) continue;
-			u32 i = (u32) (kj & 0xFFFFFFu);
-			u32 lv = L[j], rv = R[j];
-			u64 g = (u64) (lv > rv ? lv : rv) + 1;                      // fbg.cpp:1656
-			u32 ng = a.NG[t * m + i];
-			u64 rk = (u64) a.RK[t * m + i] + __popc(ng & below);
-			u64 gg = rk + g;                                            // fbg.cpp:1657
-			u32 fi;
-			if (gg > a.rowlen[i]) fi = a.tricks_off ? (u32) a.n : a.lastcol[i]; // 1659-1665
-			else fi = a.col[(u64) a.start[i] + gg - 1];                 // 1666
-			if (a.has_ignore) {                                         // 1669-1670
-				u32 ig = a.IG[t * m + i] >> dx;
-				u32 ni = ig ? (u32) x + (__ffs(ig) - 1) : a.NIA[t * m + i];
-				if (ni < fi) fi = ni;
+		bool openl = true;
+		u32 closed_r = 0;                    // slots at or after which a run end lies inside the thread
+#pragma unroll
+		for (int c = 7; c >= 0; c--)
+			if ((u32) c < E) { if ((emask >> c) & 1u) closed_r |= (2u << c) - 1u; }
+#pragma unroll
+		for (u32 c = 0; c < 8; c++) {
+			if (c < E) {
+				if ((smask >> c) & 1u) openl = false;
+				if ((vmask >> c) & 1u) {
+					u32 l = lv[c], r = rv[c];
+					if (openl) l = cl < l ? cl : l;
+					if (!((closed_r >> c) & 1u)) r = cr < r ? cr : r;
+					const u32 i = row[c];
+					u64 g = (u64) (l > r ? l : r) + 1;                         // fbg.cpp:1656
+					u64 gg = (u64) RKS[i] + g;                                  // fbg.cpp:1657
+					u32 fi;
+					if (gg > a.rowlen[i]) fi = a.tricks_off ? (u32) a.n : a.lastcol[i]; // 1659-1665
+					else fi = a.col[(u64) a.start[i] + gg - 1];                 // 1666
+					if (a.has_ignore) {                                         // 1669-1670
+						u32 ig = a.IG[t * m + i] >> dx;
+						u32 ni = ig ? (u32) x + (__ffs(ig) - 1) : a.NIA[t * m + i];
+						if (ni < fi) fi = ni;
+					}
+					fmax = fi > fmax ? fi : fmax;
+				}
 			}
-			fmax = fi > fmax ? fi : fmax;
 		}
 		// group reduction (groups are warp multiples)
 		fmax = warp_reduce_max(fmax);
-		if (lane_id() == 0) red[threadIdx.x >> 5] = fmax;
+		if (lane == 0) red[wid] = fmax;
 		__syncthreads();
 		if (tg == 0 && live) {
 			u32 v = 0;
-			u32 w0 = threadIdx.x >> 5, nw = tpg >> 5;
-			for (u32 w = 0; w < nw; w++) v = red[w0 + w] > v ? red[w0 + w] : v;
+			for (u32 w = w_first; w <= w_last; w++) v = red[w] > v ? red[w] : v;
 			a.f[x] = v > (u32) x ? v : (u32) x;                         // 1618,1681
 		}
 		__syncthreads();
@@ -141,16 +202,15 @@ __global__ void __launch_bounds__(1024) k2_fcol_kernel(FcolArgs a) {
 void k2_compute_f(Pipeline &p) {
 	Dev &d = p.dev;
 	if (!p.f) p.f = p.dev.palloc<u32>(p.n + 1);
-	GroupCfg gc = group_cfg(p.m);
+	FcolCfg gc = fcol_cfg(p.m);
 	u32 mpad = gc.mpad;
 	if (mpad > 8192) throw cuda_error("more than 8192 rows per column group is not supported by the shared-memory f(x) kernel yet");
 	FcolArgs a;
 	a.NG = p.NG; a.IG = p.IG; a.RK = p.RK; a.NIA = p.NIA; a.start = p.start; a.rowlen = p.rowlen; a.lastcol = p.lastcol;
 	a.col = p.col; a.ISA = p.ISA; a.SA = p.SA; a.PLCP = p.PLCP; a.f = p.f;
 	a.m = p.m; a.n = p.n; a.N = p.N; a.mpad = mpad;
-	// the Hillis-Steele phase keeps <= 8 elements per thread in registers
 	u32 threads = gc.threads;
-	a.tpg = gc.tpg; a.groups = gc.groups;
+	a.tpg = gc.tpg; a.groups = gc.groups; a.E = gc.E;
 	a.x0 = 0; a.x1 = p.n;
 	const bool sharded = p.dist.world > 1;
 	if (sharded) {
@@ -160,7 +220,7 @@ void k2_compute_f(Pipeline &p) {
 	}
 	a.tricks_off = p.opt.disable_tricks ? 1 : 0;
 	a.has_ignore = p.opt.n_ignore > 0 ? 1 : 0;
-	size_t smem = (size_t) a.groups * mpad * (8 + 12 + 2);
+	size_t smem = (size_t) a.groups * mpad * 16;
 	FBG_CUDA(cudaFuncSetAttribute(k2_fcol_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
 	u64 col_groups = (a.x1 - a.x0 + a.groups - 1) / a.groups;
 	if (col_groups == 0) col_groups = 1;
