@@ -42,13 +42,27 @@ constexpr int KM_TILE = KM_THREADS * KM_ITEMS;
 constexpr int KM_HBITS = 16;
 struct KmerShard { u32 bin_lo, bin_hi; int hshift; const u64 *block_off; u32 *hist; u64 *block_cnt; };
 
+// MODE 4: round 0 without a sort of all suffixes (k1_round0_dict below).  The rows of an MSA
+// repeat each other, so the text holds few distinct k-mers (2-8 % of N on the bench
+// inputs): every position enters its k-mer into an open-addressing table and leaves with
+// (slot, arrival number inside the k-mer's bucket).
+constexpr u64 KD_EMPTY = ~0ull;
+constexpr u32 KD_MAX_PROBES = 4096;
+struct KmerDict { u64 *key; u32 *cnt, *first; u32 mask; u32 *slot_of, *ord_of; u32 *overflow; };
+__device__ __forceinline__ u32 kd_hash(u64 k) {
+	k ^= k >> 33; k *= 0xff51afd7ed558ccdull; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ull; k ^= k >> 33;
+	return (u32) k;
+}
+
 template <int MODE> __global__ void __launch_bounds__(KM_THREADS) k1_kmer_kernel(const u8 *__restrict__ T, u64 N, CodeTable tab, int K, int b, KmerShard sh,
-                                                                                 u64 *__restrict__ keys, u32 *__restrict__ vals) {
+                                                                                 u64 *__restrict__ keys, u32 *__restrict__ vals, KmerDict dk) {
 	__shared__ u8 sc[KM_TILE + 64];
 	__shared__ u8 stab[256];
 	__shared__ u32 ssum[32];
 	stab[threadIdx.x] = tab.code[threadIdx.x];
+	if (MODE == 4 && threadIdx.x == 0) ssum[0] = *reinterpret_cast<volatile u32 *>(dk.overflow);
 	__syncthreads();
+	if (MODE == 4 && ssum[0]) return; // the table overflowed: the caller falls back to the sort
 	const u64 base = (u64) blockIdx.x * KM_TILE;
 	for (u32 i = threadIdx.x; i < KM_TILE + 64; i += KM_THREADS) {
 		u64 g = base + i;
@@ -66,14 +80,31 @@ template <int MODE> __global__ void __launch_bounds__(KM_THREADS) k1_kmer_kernel
 		u64 g = base + o + it;
 		kk[it] = key;
 		if (MODE == 0) { if (g < N) { keys[g] = key; vals[g] = (u32) g; } }
-		else {
+		else if (MODE == 4) {
+			if (g < N) {
+				u32 s = kd_hash(key) & dk.mask, probes = 0;
+				for (;;) {
+					// a stale EMPTY only costs the CAS, and a slot that holds a key never changes
+					u64 cur = __ldcg(dk.key + s);
+					if (cur == key) break;
+					if (cur == KD_EMPTY) {
+						u64 prev = atomicCAS(reinterpret_cast<unsigned long long *>(dk.key + s), (unsigned long long) KD_EMPTY, (unsigned long long) key);
+						if (prev == KD_EMPTY) { dk.first[s] = (u32) g; break; }
+						if (prev == key) break;
+					}
+					s = (s + 1) & dk.mask;
+					if (++probes > KD_MAX_PROBES) { *dk.overflow = 1u; s = U32_MAX; break; }
+				}
+				if (s != U32_MAX) { dk.ord_of[g] = atomicAdd(dk.cnt + s, 1u); dk.slot_of[g] = s; }
+			}
+		} else {
 			u32 bin = (u32) (key >> sh.hshift);
 			if (MODE == 1) { if (g < N) atomicAdd(&sh.hist[bin], 1u); }
 			else if (g < N && bin >= sh.bin_lo && bin < sh.bin_hi) mine |= 1u << it;
 		}
 		key = ((key << b) | sc[o + it + K]) & kmask;
 	}
-	if (MODE >= 2) {
+	if (MODE == 2 || MODE == 3) {
 		u32 tot;
 		u32 ex = block_excl_scan<OpSumU32>((u32) __popc(mine), ssum, &tot);
 		if (MODE == 2) { if (threadIdx.x == 0) sh.block_cnt[blockIdx.x] = tot; }
@@ -250,11 +281,21 @@ __global__ void __launch_bounds__(CP_THREADS) k1_cls_write_kernel(const u8 *__re
 // ---- bucket-local sort of the S list
 // CTA b owns the buckets whose head lies in [b*tile, (b+1)*tile) and loads the window
 // [b*tile, b*tile + CAP); tile <= CAP - (largest bucket), so every owned bucket fits.
-// Key = bucket head offset | r2 | offset in the window, sorted by the shared-memory
-// bitonic network; sub-bucket heads by a max-scan; ranks, classes and R updates follow.
+//
+// The rows of an MSA are near copies of each other, so most of a bucket (the rows that agree
+// at a column over h characters) lands in ONE bucket again h characters further on: nearly
+// all of its r2 values are equal.  Every bucket therefore takes the r2 of its middle element
+// as a pivot; elements equal to the pivot keep their relative order and leave at once
+// (new rank = bucket rank + number of smaller elements), and only the others -- the
+// "minority" -- go through the shared-memory sorting network, whose size follows their
+// number.  Any pivot is correct; a bad one only sends more keys through the network.
+//   key = bucket head | greater-than-pivot | r2 | window index of the element
+// Shared memory: key u64[CAP] (first an r2 copy for the pivot look-ups), PXI u32[CAP+1]
+// (inclusive prefix counts, minority | smaller << 16), bend u16[CAP] (bucket end by head).
 template <int CAP> struct TileCfg {
 	static constexpr int THREADS = CAP >= 8192 ? 1024 : CAP / 8;
-	static constexpr int MINB = CAP >= 16384 ? 1 : CAP >= 8192 ? 2 : 6; // CTAs per SM the register budget is held to
+	static constexpr int MINB = CAP >= 8192 ? 1 : CAP >= 4096 ? 3 : 5; // CTAs per SM the register budget is held to
+	static constexpr size_t SMEM = (size_t) CAP * 8 + ((size_t) CAP + 4) * 4 + (size_t) CAP * 2;
 };
 
 template <int CAP> __global__ void __launch_bounds__(TileCfg<CAP>::THREADS, TileCfg<CAP>::MINB)
@@ -268,6 +309,9 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 	static_assert(LOGC > 0, "unsupported tile capacity");
 	extern __shared__ __align__(16) unsigned char k1_raw[];
 	u64 *key = reinterpret_cast<u64 *>(k1_raw);
+	u32 *r2s = reinterpret_cast<u32 *>(k1_raw);                       // until the keys are written
+	u32 *PXI = reinterpret_cast<u32 *>(k1_raw + (size_t) CAP * 8);
+	unsigned short *bend = reinterpret_cast<unsigned short *>(k1_raw + (size_t) CAP * 8 + ((size_t) CAP + 4) * 4);
 	__shared__ u32 s_first, s_end, s_wtot[32];
 	const u32 tid = threadIdx.x, w = tid >> 5, l = tid & 31;
 	const u64 w0 = (u64) blockIdx.x * tile;
@@ -276,8 +320,8 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 	if (tid == 0) { s_first = U32_MAX; s_end = U32_MAX; }
 	__syncthreads();
 
-	// 1. bucket heads in the window; hbv = inclusive max-scan of (head ? idx+1 : 0)
-	u32 hbv[ITEMS];
+	// 1. bucket heads in the window; st = inclusive max-scan of (head ? idx+1 : 0)
+	u32 st[ITEMS];
 	u32 carry = 0, fmin = U32_MAX, emin = U32_MAX;
 #pragma unroll
 	for (int i = 0; i < ITEMS; i++) {
@@ -286,6 +330,7 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 		if (idx < wlen) {
 			u64 t = w0 + idx;
 			bool head = (t == 0) || (lr[t - 1] != lr[t]);
+			r2s[idx] = r2[t];
 			if (head) {
 				v = idx + 1;
 				if (idx < tlen) fmin = idx < fmin ? idx : fmin;
@@ -294,7 +339,7 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 		}
 		u32 inc = warp_incl_max(v);
 		inc = inc > carry ? inc : carry;
-		hbv[i] = inc;
+		st[i] = inc;
 		carry = __shfl_sync(0xffffffffu, inc, 31);
 	}
 	if (l == 31) s_wtot[w] = carry;
@@ -312,71 +357,148 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 		if (w0 + wlen == na) endidx = wlen;
 		else { if (tid == 0) scal[1] = 1u; return; } // a bucket larger than CAP - tile: host contract broken
 	}
-	const u32 cnt = endidx - first;
 	u32 wpre = 0;
 	for (u32 ww = 0; ww < w; ww++) { u32 x = s_wtot[ww]; wpre = x > wpre ? x : wpre; }
 
-	// 2. keys, compacted to slots [0, cnt); the network is sized to the keys actually present
-	u32 net = 32;
-	while (net < cnt) net <<= 1;
+	// 2. st = window index of the element's bucket head; the last element of a bucket posts its end
 #pragma unroll
 	for (int i = 0; i < ITEMS; i++) {
 		u32 idx = w * WCH + i * 32 + l;
 		if (idx >= first && idx < endidx) {
-			u32 hb1 = hbv[i] > wpre ? hbv[i] : wpre;
-			u32 hb_rel = hb1 - 1 - first;
-			key[ts_sw(idx - first)] = ((u64) hb_rel << (32 + LOGC)) | ((u64) r2[w0 + idx] << LOGC) | (u64) (idx - first);
+			u32 hb = (st[i] > wpre ? st[i] : wpre) - 1;
+			st[i] = hb;
+			u64 t = w0 + idx;
+			if (idx + 1 == endidx || lr[t + 1] != lr[t]) bend[hb] = (unsigned short) (idx + 1);
 		}
 	}
-	for (u32 slot = cnt + tid; slot < net; slot += THREADS) key[ts_sw(slot)] = ~0ull;
 	__syncthreads();
 
-	// 3. sort
-	tile_bitonic_sort_rt<THREADS>(key, net);
-
-	// 4. sub-bucket heads: hsv = inclusive max-scan of (sub-head ? s+1 : 0)
-	u32 hsv[ITEMS];
-	carry = 0;
+	// 3. pivot of the bucket, minority / smaller flags, their prefix counts over the window
+	u32 mmask = 0, gmask = 0, run = 0;
 #pragma unroll
 	for (int i = 0; i < ITEMS; i++) {
-		u32 s = w * WCH + i * 32 + l;
-		u32 v = 0;
-		if (s < cnt) {
-			bool sh = s == 0;
-			if (!sh) sh = (key[ts_sw(s)] >> LOGC) != (key[ts_sw(s - 1)] >> LOGC);
-			if (sh) v = s + 1;
+		u32 idx = w * WCH + i * 32 + l;
+		bool mn = false, ls = false;
+		if (idx >= first && idx < endidx) {
+			u32 hb = st[i];
+			u32 pv = r2s[hb + (((u32) bend[hb] - hb) >> 1)];
+			u32 rr = r2s[idx];
+			mn = rr != pv; ls = rr < pv;
 		}
-		u32 inc = warp_incl_max(v);
-		inc = inc > carry ? inc : carry;
-		hsv[i] = inc;
-		carry = __shfl_sync(0xffffffffu, inc, 31);
+		u32 bm = __ballot_sync(0xffffffffu, mn), bl = __ballot_sync(0xffffffffu, ls);
+		u32 lt = lanemask_lt();
+		PXI[idx + 1] = run + (u32) __popc(bm & lt) + (mn ? 1u : 0u) + (((u32) __popc(bl & lt) + (ls ? 1u : 0u)) << 16); // inside the warp, for now
+		run += (u32) __popc(bm) + ((u32) __popc(bl) << 16);
+		mmask |= (mn ? 1u : 0u) << i;
+		gmask |= ((mn && !ls) ? 1u : 0u) << i;
+	}
+	if (l == 0) s_wtot[w] = run;
+	if (tid == 0) PXI[0] = 0;
+	__syncthreads();
+	u32 ppre = 0, ptot = 0;
+	for (u32 ww = 0; ww < NW; ww++) { u32 x = s_wtot[ww]; if (ww < w) ppre += x; ptot += x; }
+	const u32 nmin = ptot & 0xFFFFu;
+	if (ppre) {
+#pragma unroll
+		for (int i = 0; i < ITEMS; i++) PXI[w * WCH + i * 32 + l + 1] += ppre;
+	}
+	__syncthreads();
+
+	// 4. elements equal to their pivot leave; the minority writes its keys (r2s is dead: its
+	//    last read lies before the two barriers above)
+	u32 mx = 0;
+#pragma unroll
+	for (int i = 0; i < ITEMS; i++) {
+		u32 idx = w * WCH + i * 32 + l;
+		if (idx >= first && idx < endidx) {
+			const u32 hb = st[i];
+			const u32 x = PXI[idx];
+			const u64 t = w0 + idx;
+			if ((mmask >> i) & 1u) {
+				key[ts_sw(x & 0xFFFFu)] = ((u64) hb << (33 + LOGC)) | ((u64) ((gmask >> i) & 1u) << (32 + LOGC)) | ((u64) r2[t] << LOGC) | (u64) idx;
+			} else {
+				const u32 end = bend[hb];
+				const u32 xh = PXI[hb], xe = PXI[end];
+				const u32 nless = (xe >> 16) - (xh >> 16);
+				const u32 neq = (end - hb) - ((xe & 0xFFFFu) - (xh & 0xFFFFu));
+				const u32 out = hb + nless + (idx - hb) - ((x & 0xFFFFu) - (xh & 0xFFFFu));
+				const u32 p = lp[t];
+				const u32 nr = lr[t] + nless;
+				const bool single = neq == 1;
+				if (nless) R[p] = nr;           // otherwise the rank is the one the suffix already has
+				if (single) SA[nr] = p;
+				lp_out[w0 + out] = p;
+				lr_out[w0 + out] = nr;
+				cls_out[w0 + out] = (u8) (single ? CLS_DROP : CLS_SMALL);
+				if (!single) mx = neq > mx ? neq : mx;
+			}
+		}
+	}
+	if (nmin == 0) {
+		mx = warp_reduce_max(mx);
+		if (l == 0 && mx) atomicMax(&scal[0], mx);
+		return;
+	}
+	u32 net = 32;
+	while (net < nmin) net <<= 1;
+	for (u32 slot = nmin + tid; slot < net; slot += THREADS) key[ts_sw(slot)] = ~0ull;
+	__syncthreads();
+
+	// 5. sort the minority
+	tile_bitonic_sort_rt<THREADS>(key, net);
+
+	// 6. sub-bucket heads among them: st = inclusive max-scan of (sub-head ? s+1 : 0)
+	carry = 0;
+	if (w * WCH < nmin) {
+#pragma unroll
+		for (int i = 0; i < ITEMS; i++) {
+			u32 s = w * WCH + i * 32 + l;
+			u32 v = 0;
+			if (s < nmin) {
+				bool sh = s == 0;
+				if (!sh) sh = (key[ts_sw(s)] >> LOGC) != (key[ts_sw(s - 1)] >> LOGC);
+				if (sh) v = s + 1;
+			}
+			u32 inc = warp_incl_max(v);
+			inc = inc > carry ? inc : carry;
+			st[i] = inc;
+			carry = __shfl_sync(0xffffffffu, inc, 31);
+		}
 	}
 	if (l == 31) s_wtot[w] = carry;
 	__syncthreads();
 	wpre = 0;
 	for (u32 ww = 0; ww < w; ww++) { u32 x = s_wtot[ww]; wpre = x > wpre ? x : wpre; }
 
-	// 5. ranks, classes, outputs
-	const u64 g0 = w0 + first;
-	u32 mx = 0;
+	// 7. ranks, classes, outputs of the minority: smaller ones in front of the bucket's equal
+	//    elements, greater ones behind them
+	if (w * WCH < nmin) {
 #pragma unroll
-	for (int i = 0; i < ITEMS; i++) {
-		u32 s = w * WCH + i * 32 + l;
-		if (s < cnt) {
-			u64 k = key[ts_sw(s)];
-			u32 hs = (hsv[i] > wpre ? hsv[i] : wpre) - 1;
-			u32 hb = (u32) (k >> (32 + LOGC));
-			u32 irel = (u32) k & (u32) (CAP - 1);
-			bool last = (s + 1 >= cnt) || ((key[ts_sw(s + 1)] >> LOGC) != (k >> LOGC));
-			u32 nr = lr[g0 + hb] + (hs - hb);
-			u32 p = lp[g0 + irel];
-			const bool single = hs == s && last;
-			R[p] = nr;
-			if (single) SA[nr] = p;
-			lp_out[g0 + s] = p;
-			lr_out[g0 + s] = nr;
-			cls_out[g0 + s] = (u8) (single ? CLS_DROP : CLS_SMALL);
-			if (last && s != hs) { u32 sz = s - hs + 1; mx = sz > mx ? sz : mx; }
+		for (int i = 0; i < ITEMS; i++) {
+			u32 s = w * WCH + i * 32 + l;
+			if (s < nmin) {
+				const u64 k = key[ts_sw(s)];
+				const u32 hs = (st[i] > wpre ? st[i] : wpre) - 1;
+				const u32 hb = (u32) (k >> (33 + LOGC));
+				const u32 e = (u32) k & (u32) (CAP - 1);
+				const bool last = (s + 1 >= nmin) || ((key[ts_sw(s + 1)] >> LOGC) != (k >> LOGC));
+				const u32 end = bend[hb];
+				const u32 xh = PXI[hb], xe = PXI[end];
+				const u32 pmh = xh & 0xFFFFu;
+				const u32 neq = (end - hb) - ((xe & 0xFFFFu) - pmh);
+				const u32 off = ((k >> (32 + LOGC)) & 1ull) ? neq : 0u;
+				const u32 out = hb + (s - pmh) + off;
+				const u32 hrel = (hs - pmh) + off;     // sub-bucket head, relative to the bucket head
+				const u32 nr = lr[w0 + hb] + hrel;
+				const u32 p = lp[w0 + e];
+				const bool single = hs == s && last;
+				if (hrel) R[p] = nr;
+				if (single) SA[nr] = p;
+				lp_out[w0 + out] = p;
+				lr_out[w0 + out] = nr;
+				cls_out[w0 + out] = (u8) (single ? CLS_DROP : CLS_SMALL);
+				if (last && s != hs) { u32 sz = s - hs + 1; mx = sz > mx ? sz : mx; }
+			}
 		}
 	}
 	mx = warp_reduce_max(mx);
@@ -386,7 +508,7 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 template <int CAP> static void launch_tile_sort(Dev &d, const u32 *lp, const u32 *lr, const u32 *r2, u64 na, u32 maxb,
                                                 u32 *R, u32 *SA, u32 *lp_out, u32 *lr_out, u8 *cls_out, u32 *scal) {
 	u32 tile = (u32) CAP - maxb;
-	size_t smem = (size_t) CAP * 8;
+	const size_t smem = TileCfg<CAP>::SMEM;
 	FBG_CUDA(cudaFuncSetAttribute(k1_tile_sort_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
 	k1_tile_sort_kernel<CAP><<<div_up(na, tile), TileCfg<CAP>::THREADS, smem, d.stream>>>(lp, lr, r2, na, tile, R, SA, lp_out, lr_out, cls_out, scal);
 	FBG_LAUNCH_CHECK();
@@ -416,6 +538,144 @@ __global__ void k1_active_total_kernel(const u64 *sc64, u64 *tot) {
 	*tot = (a & 0xFFFFFFFFull) + (a >> 32) + (b & 0xFFFFFFFFull) + (b >> 32);
 }
 
+// ---- round 0 through the k-mer dictionary (single GPU)
+__global__ void k1_dict_flag_kernel(const u64 *__restrict__ key, u32 cap, u32 *__restrict__ flag) {
+	u32 s = blockIdx.x * blockDim.x + threadIdx.x;
+	if (s < cap) flag[s] = key[s] != KD_EMPTY ? 1u : 0u;
+}
+__global__ void k1_dict_list_kernel(const u64 *__restrict__ key, const u32 *__restrict__ pos, u32 cap, u64 *__restrict__ lk, u32 *__restrict__ lv) {
+	u32 s = blockIdx.x * blockDim.x + threadIdx.x;
+	if (s >= cap) return;
+	u64 k = key[s];
+	if (k != KD_EMPTY) { u32 q = pos[s]; lk[q] = k; lv[q] = s; }
+}
+// bucket sizes in k-mer order: all of them (their exclusive scan = the ranks) and the big ones (B list offsets)
+__global__ void k1_dict_counts_kernel(const u32 *__restrict__ lv, const u32 *__restrict__ cnt, u32 nd, u32 *__restrict__ call, u32 *__restrict__ cbig) {
+	u32 t = blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= nd) return;
+	u32 c = cnt[lv[t]];
+	call[t] = c; cbig[t] = c > BSMALL ? c : 0u;
+}
+// info[slot] = (rank, start of the bucket in its list, size, first arrival); A = directory of the small buckets by text position
+__global__ void k1_dict_assign_kernel(const u32 *__restrict__ lv, const u32 *__restrict__ cnt, const u32 *__restrict__ first, const u32 *__restrict__ rk, const u32 *__restrict__ bs,
+                                      u32 nd, u32 rank_off, uint4 *__restrict__ info, u32 *__restrict__ A, u32 *__restrict__ maxb) {
+	u32 t = blockIdx.x * blockDim.x + threadIdx.x;
+	u32 small = 0;
+	if (t < nd) {
+		u32 s = lv[t], c = cnt[s], f = first[s], start = 0;
+		if (c > BSMALL) start = bs[t];
+		else if (c > 1) { A[f] = c; small = c; }
+		info[s] = make_uint4(rank_off + rk[t], start, c, f);
+	}
+	small = warp_reduce_max(small);
+	if (lane_id() == 0 && small) atomicMax(maxb, small);
+}
+__global__ void k1_dict_fold_kernel(const u32 *__restrict__ lv, u32 nd, uint4 *__restrict__ info, const u32 *__restrict__ A) {
+	u32 t = blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= nd) return;
+	u32 s = lv[t];
+	uint4 v = info[s];
+	if (v.z > 1 && v.z <= BSMALL) { v.y = A[v.w]; info[s] = v; }
+}
+// what the sort-based round 0 leaves behind: ranks, SA entries of the suffixes alone in their
+// bucket, the S and B lists of the next round with R[p+h] looked up (through the table: no
+// rank has to be visible yet)
+__global__ void __launch_bounds__(256) k1_dict_emit_kernel(const u32 *__restrict__ slot_of, const u32 *__restrict__ ord_of, const uint4 *__restrict__ info, u64 N, u64 hnext, int nbits,
+                                                           u32 *__restrict__ R, u32 *__restrict__ SA, CompactOut o) {
+	u64 p = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (p >= N) return;
+	const uint4 v = __ldg(info + slot_of[p]);
+	R[p] = v.x;
+	if (v.z == 1) { SA[v.x] = (u32) p; return; }
+	const u64 pn = p + hnext;
+	const u32 r2 = pn < N ? __ldg(info + slot_of[pn]).x : 0u;
+	const u32 q = v.y + ord_of[p];
+	if (v.z <= BSMALL) { o.Slp[q] = (u32) p; o.Slr[q] = v.x; o.Sr2[q] = r2; }
+	else { o.Bkey[q] = ((u64) v.x << nbits) | r2; o.Bval[q] = (u32) p; }
+}
+
+static u32 dict_capacity(u64 N) {
+	u32 cap = 1u << 16;
+	while ((u64) cap * 8 < N && cap < (1u << 30)) cap <<= 1;
+	return cap;
+}
+static u64 dict_scratch_bytes(u64 N) {
+	u64 cap = dict_capacity(N);
+	return cap * (8 + 4 + 4 + 16 + 4) + (cap / 2) * (16 + 8 + 8) + (cap / SCAN_TILE + 2) * 24 + (1u << 16);
+}
+
+// Returns false (nothing written that matters) when the text has too many distinct k-mers for
+// the table: the caller then sorts all suffixes as before.
+static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int key_bits0, u32 km_grid, u32 *slot_of, u32 *ord_of, u32 *A,
+                           u64 hnext, int nbits, CompactOut o, u64 *nS, u64 *nB, u32 *maxb) {
+	Dev &d = p.dev;
+	const u64 N = p.N;
+	const u32 cap = dict_capacity(N), ndmax = cap / 2;
+	u64 mk = d.mark();
+	KmerDict dk;
+	dk.key = d.alloc<u64>(cap); dk.cnt = d.alloc<u32>(cap); dk.first = d.alloc<u32>(cap);
+	dk.mask = cap - 1; dk.slot_of = slot_of; dk.ord_of = ord_of;
+	u32 *sc = reinterpret_cast<u32 *>(p.scalars + 48); // [0] distinct, [1] overflow, [2] nS, [3] nB, [4] maxb
+	u32 *h_sc = reinterpret_cast<u32 *>(p.h_scalars + 48);
+	dk.overflow = sc + 1;
+	uint4 *info = d.alloc<uint4>(cap);
+	u32 *pos = d.alloc<u32>(cap);
+	RadixBuffers lb;
+	lb.k[0] = d.alloc<u64>(ndmax); lb.k[1] = d.alloc<u64>(ndmax);
+	lb.v[0] = d.alloc<u32>(ndmax); lb.v[1] = d.alloc<u32>(ndmax);
+	lb.cur = 0;
+	u32 *call = d.alloc<u32>(ndmax), *cbig = d.alloc<u32>(ndmax);
+	FBG_CUDA(cudaMemsetAsync(p.scalars + 48, 0, 4 * sizeof(u64), d.stream));
+	d.begin(K_KMER);
+	FBG_CUDA(cudaMemsetAsync(dk.key, 0xFF, (u64) cap * sizeof(u64), d.stream));
+	FBG_CUDA(cudaMemsetAsync(dk.cnt, 0, (u64) cap * sizeof(u32), d.stream));
+	KmerShard sh;
+	sh.bin_lo = 0; sh.bin_hi = 0; sh.hshift = 0; sh.block_off = nullptr; sh.hist = nullptr; sh.block_cnt = nullptr;
+	k1_kmer_kernel<4><<<km_grid, KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, sh, nullptr, nullptr, dk);
+	FBG_LAUNCH_CHECK();
+	d.end((double) N * (1.0 + 8.0 + 8.0));
+	const u32 gc = div_up(cap, 256);
+	d.begin(K_DOUBLING_AUX);
+	k1_dict_flag_kernel<<<gc, 256, 0, d.stream>>>(dk.key, cap, pos);
+	FBG_LAUNCH_CHECK();
+	d.end((double) cap * 12.0);
+	device_scan<OpSumU32, true>(d, pos, pos, cap, sc);
+	FBG_CUDA(cudaMemcpyAsync(h_sc, sc, 2 * sizeof(u32), cudaMemcpyDeviceToHost, d.stream));
+	FBG_CUDA(cudaStreamSynchronize(d.stream));
+	const u32 nd = h_sc[0];
+	if (h_sc[1] || nd > ndmax) { d.release(mk); return false; }
+	d.begin(K_DOUBLING_AUX);
+	k1_dict_list_kernel<<<gc, 256, 0, d.stream>>>(dk.key, pos, cap, (u64 *) lb.k[0], lb.v[0]);
+	FBG_LAUNCH_CHECK();
+	d.end((double) cap * 12.0 + (double) nd * 12.0);
+	const int cur = radix_sort<u64, true>(d, lb, nd, 0, key_bits0);
+	const u32 *lv = lb.v[cur];
+	const u32 gn = div_up(nd, 256);
+	d.begin(K_DOUBLING_AUX);
+	k1_dict_counts_kernel<<<gn, 256, 0, d.stream>>>(lv, dk.cnt, nd, call, cbig);
+	FBG_LAUNCH_CHECK();
+	d.end((double) nd * 16.0);
+	device_scan<OpSumU32, true>(d, call, call, nd);
+	device_scan<OpSumU32, true>(d, cbig, cbig, nd, sc + 3);
+	d.begin(K_DOUBLING_AUX);
+	FBG_CUDA(cudaMemsetAsync(A, 0, N * sizeof(u32), d.stream));
+	k1_dict_assign_kernel<<<gn, 256, 0, d.stream>>>(lv, dk.cnt, dk.first, call, cbig, nd, 0u, info, A, sc + 4);
+	FBG_LAUNCH_CHECK();
+	d.end((double) nd * 40.0 + (double) N * 4.0);
+	device_scan<OpSumU32, true>(d, A, A, N, sc + 2);
+	d.begin(K_DOUBLING_AUX);
+	k1_dict_fold_kernel<<<gn, 256, 0, d.stream>>>(lv, nd, info, A);
+	k1_dict_emit_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, N, hnext, nbits, p.ISA, p.SA, o);
+	FBG_LAUNCH_CHECK();
+	d.end((double) N * (8.0 + 4.0 + 4.0 + 12.0) + (double) nd * 24.0);
+	d.note_launches(K_DOUBLING_AUX, 1);
+	FBG_CUDA(cudaMemcpyAsync(h_sc, sc, 5 * sizeof(u32), cudaMemcpyDeviceToHost, d.stream));
+	FBG_CUDA(cudaStreamSynchronize(d.stream));
+	*nS = h_sc[2]; *nB = h_sc[3]; *maxb = h_sc[4];
+	d.release(mk);
+	return true;
+}
+
 void k1_suffix_array(Pipeline &p) {
 	Dev &d = p.dev;
 	const Dist &dist = p.dist;
@@ -432,6 +692,7 @@ void k1_suffix_array(Pipeline &p) {
 	d.begin(K_KMER);
 	k1_presence_kernel<<<NUM_SMS * 4, 256, 0, d.stream>>>(p.T, N, present);
 	FBG_LAUNCH_CHECK();
+	d.end((double) N);
 	u32 hpres[256];
 	FBG_CUDA(cudaMemcpyAsync(hpres, present, sizeof hpres, cudaMemcpyDeviceToHost, d.stream));
 	FBG_CUDA(cudaStreamSynchronize(d.stream));
@@ -458,8 +719,10 @@ void k1_suffix_array(Pipeline &p) {
 		u32 *hist = d.alloc<u32>(nbins);
 		FBG_CUDA(cudaMemsetAsync(hist, 0, nbins * sizeof(u32), d.stream));
 		sh.hist = hist;
-		k1_kmer_kernel<1><<<km_grid, KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, sh, nullptr, nullptr);
+		d.begin(K_KMER);
+		k1_kmer_kernel<1><<<km_grid, KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, sh, nullptr, nullptr, KmerDict());
 		FBG_LAUNCH_CHECK();
+		d.end((double) N);
 		std::vector<u32> hh(nbins), bounds(dist.world + 1);
 		FBG_CUDA(cudaMemcpyAsync(hh.data(), hist, nbins * sizeof(u32), cudaMemcpyDeviceToHost, d.stream));
 		FBG_CUDA(cudaStreamSynchronize(d.stream));
@@ -470,13 +733,12 @@ void k1_suffix_array(Pipeline &p) {
 		for (u32 q = 0; q < sh.bin_hi; q++) { if (q < sh.bin_lo) before += hh[q]; else mine += hh[q]; }
 		nloc = mine; rank_off = (u32) before;
 		d.release(mk2);
-		d.note_launches(K_KMER, 1);
 	}
 	const u64 cap = nloc ? nloc : 1;
 	// scratch of this phase: 74 B per suffix sorted here (sort ping-pong 24, heads 16, classes 2,
 	// S lists 24, tile outputs 8) + radix count matrices + (sharded) the N-word bucket directory
 	d.release(mk);
-	d.ensure(cap * 76 + (cap / RS_TILE + 2) * RS_BINS * 12 + (u64) km_grid * 8 + (sharded ? N * 4 + (N / SCAN_TILE + 2) * 24 : 0) + (16u << 20));
+	d.ensure(cap * 76 + (cap / RS_TILE + 2) * RS_BINS * 12 + (u64) km_grid * 8 + (sharded ? N * 4 + (N / SCAN_TILE + 2) * 24 : dict_scratch_bytes(N)) + (16u << 20));
 	mk = d.mark();
 
 	RadixBuffers rb;
@@ -494,15 +756,30 @@ void k1_suffix_array(Pipeline &p) {
 	u64 *gtot = p.scalars + 11;                         // suffixes still tied, over all GPUs
 	u64 *h_sc = p.h_scalars + 8;                        // mirror of scalars[8..11]
 
-	if (!sharded) {
-		k1_kmer_kernel<0><<<km_grid, KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, sh, (u64 *) rb.k[0], rb.v[0]);
+	int nbits = 1;
+	while ((1ull << nbits) < N) nbits++;
+	u64 nS = 0, nB = nloc; // round 0: every suffix goes through the device-wide sort ...
+	u32 maxb = 0;
+	int sc = 0;           // current S list
+	// ... unless the k-mer dictionary takes it: no sort, ranks written in text order
+	bool by_dict = false;
+	if (!sharded && key_bits0 < 64 && !getenv("FBG_NO_KMER_DICT")) {
+		CompactOut o;
+		o.Slp = Slp[1]; o.Slr = Slr[1]; o.Sr2 = Sr2[1];
+		o.Bkey = (u64 *) rb.k[1]; o.Bval = rb.v[1];
+		by_dict = k1_round0_dict(p, tab, K, b, key_bits0, km_grid, HR, newr, lp_out, (u64) K, nbits, o, &nS, &nB, &maxb);
+	}
+	if (!by_dict) d.begin(K_KMER);
+	if (by_dict) {
+	} else if (!sharded) {
+		k1_kmer_kernel<0><<<km_grid, KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, sh, (u64 *) rb.k[0], rb.v[0], KmerDict());
 	} else {
 		u64 mk2 = d.mark();
 		u64 *bc = d.alloc<u64>(km_grid);
 		sh.block_cnt = bc; sh.block_off = bc;
-		k1_kmer_kernel<2><<<km_grid, KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, sh, nullptr, nullptr);
+		k1_kmer_kernel<2><<<km_grid, KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, sh, nullptr, nullptr, KmerDict());
 		scan_partials_kernel<OpSumU64><<<1, 1024, 0, d.stream>>>(bc, km_grid, nullptr);
-		k1_kmer_kernel<3><<<km_grid, KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, sh, (u64 *) rb.k[0], rb.v[0]);
+		k1_kmer_kernel<3><<<km_grid, KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, sh, (u64 *) rb.k[0], rb.v[0], KmerDict());
 		FBG_CUDA(cudaMemsetAsync(p.ISA, 0, N * sizeof(u32), d.stream)); // replicas are merged by max
 		FBG_CUDA(cudaMemsetAsync(p.SA, 0, N * sizeof(u32), d.stream));
 		FBG_CUDA(cudaStreamSynchronize(d.stream)); // bc is released below
@@ -510,28 +787,35 @@ void k1_suffix_array(Pipeline &p) {
 		d.note_launches(K_KMER, 2);
 	}
 	FBG_LAUNCH_CHECK();
-	d.end((double) N * (1.0 + 8.0 + 4.0));
-	d.note_launches(K_KMER, 1);
+	if (!by_dict) d.end((double) N * (1.0 + 8.0 + 4.0));
 
-	int nbits = 1;
-	while ((1ull << nbits) < N) nbits++;
-	u64 nS = 0, nB = nloc; // round 0: every suffix goes through the device-wide sort
-	u32 maxb = 0;
 	u64 h = (u64) K;      // depth the current ranks are exact to after the round being run
 	int hi_shift = 64;    // round 0: a single level of buckets
 	int key_bits = key_bits0;
-	int sc = 0;           // current S list
 	p.sa_rounds = 0;
 	const bool debug = getenv("FBG_DEBUG") != nullptr;
+	const u32 tile_ratio = getenv("FBG_TILE_RATIO") ? (u32) atoi(getenv("FBG_TILE_RATIO")) : 2u;
+	if (debug) fprintf(stderr, "[fbg] rank %d K1 round 0 %s\n", dist.rank, by_dict ? "through the k-mer dictionary" : "by sorting all suffixes");
+	if (by_dict) {
+		// the state a sorted round 0 ends in
+		p.sa_rounds = 1;
+		if (nB) rb.cur ^= 1;
+		sc ^= 1;
+		hi_shift = nbits;
+		key_bits = 2 * nbits;
+		h *= 2;
+	}
 	for (;;) {
+		if (by_dict && nS + nB == 0) break; // every k-mer was unique
 		if (debug) fprintf(stderr, "[fbg] rank %d K1 round %d: depth %llu, S list %llu (largest bucket %u), B list %llu\n", dist.rank, p.sa_rounds,
 		                   (unsigned long long) (p.sa_rounds ? h / 2 : 0), (unsigned long long) nS, maxb, (unsigned long long) nB);
 		FBG_CUDA(cudaMemsetAsync(p.scalars + 8, 0, 4 * sizeof(u64), d.stream));
 		// ---- S path
 		if (nS) {
 			d.begin(K_TILE_SORT);
-			if (2 * maxb <= 2048) launch_tile_sort<2048>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
-			else if (2 * maxb <= 8192) launch_tile_sort<8192>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
+			if (tile_ratio * maxb <= 2048) launch_tile_sort<2048>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
+			else if (tile_ratio * maxb <= 4096) launch_tile_sort<4096>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
+			else if (tile_ratio * maxb <= 8192) launch_tile_sort<8192>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
 			else launch_tile_sort<16384>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
 			d.end((double) nS * (12.0 + 4.0 + 9.0));
 		}
