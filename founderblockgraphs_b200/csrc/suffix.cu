@@ -294,9 +294,30 @@ __global__ void __launch_bounds__(CP_THREADS) k1_cls_write_kernel(const u8 *__re
 // (inclusive prefix counts, minority | smaller << 16), bend u16[CAP] (bucket end by head).
 template <int CAP> struct TileCfg {
 	static constexpr int THREADS = CAP >= 8192 ? 1024 : CAP / 8;
-	static constexpr int MINB = CAP >= 8192 ? 1 : CAP >= 4096 ? 3 : 5; // CTAs per SM the register budget is held to
-	static constexpr size_t SMEM = (size_t) CAP * 8 + ((size_t) CAP + 4) * 4 + (size_t) CAP * 2;
+	static constexpr int MINB = CAP >= 8192 ? 1 : CAP >= 4096 ? 2 : 5; // CTAs per SM the register budget is held to
+	// windows up to 8192 slots also stage lr and lp in shared memory (one burst of asynchronous
+	// copies at the start, every later access at shared-memory latency)
+	static constexpr bool STAGE = CAP <= 8192;
+	static constexpr size_t SMEM = (size_t) CAP * 8 + ((size_t) CAP + 4) * 4 + (size_t) CAP * 2 + (STAGE ? ((size_t) CAP + 4) * 4 + (size_t) CAP * 4 : 0);
 };
+
+__device__ __forceinline__ void cp_async4(void *smem_dst, const void *gsrc) {
+	const u32 d = (u32) __cvta_generic_to_shared(smem_dst);
+	asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+	asm volatile("cp.async.commit_group;" ::: "memory");
+	asm volatile("cp.async.wait_group 0;" ::: "memory");
+}
+
+// inclusive "index + 1 of the last flagged element at or before me" over a 32-element chunk
+// whose lane 0 holds element `base`; carry = the value flowing in from the chunks before
+__device__ __forceinline__ u32 ts_last_flag(u32 fm, u32 base, u32 &carry) {
+	const u32 m = fm & (lanemask_lt() | (1u << lane_id()));
+	const u32 inc = m ? base + (32u - (u32) __clz(m)) : carry;
+	if (fm) carry = base + (32u - (u32) __clz(fm));
+	return inc;
+}
 
 template <int CAP> __global__ void __launch_bounds__(TileCfg<CAP>::THREADS, TileCfg<CAP>::MINB)
 k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, const u32 *__restrict__ r2, u64 na, u32 tile,
@@ -309,43 +330,84 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 	static_assert(LOGC > 0, "unsupported tile capacity");
 	extern __shared__ __align__(16) unsigned char k1_raw[];
 	u64 *key = reinterpret_cast<u64 *>(k1_raw);
-	u32 *r2s = reinterpret_cast<u32 *>(k1_raw);                       // until the keys are written
+	u32 *r2s = reinterpret_cast<u32 *>(k1_raw);                                              // until the keys are written
+	unsigned short *hbs = reinterpret_cast<unsigned short *>(k1_raw + (size_t) CAP * 4);     // until step 3 has read it
 	u32 *PXI = reinterpret_cast<u32 *>(k1_raw + (size_t) CAP * 8);
 	unsigned short *bend = reinterpret_cast<unsigned short *>(k1_raw + (size_t) CAP * 8 + ((size_t) CAP + 4) * 4);
+	constexpr bool STAGE = TileCfg<CAP>::STAGE;
+	u32 *lrs = reinterpret_cast<u32 *>(k1_raw + (size_t) CAP * 8 + ((size_t) CAP + 4) * 4 + (size_t) CAP * 2); // lrs[idx + 1] = lr of window element idx
+	u32 *lps = lrs + CAP + 4;
 	__shared__ u32 s_first, s_end, s_wtot[32];
 	const u32 tid = threadIdx.x, w = tid >> 5, l = tid & 31;
 	const u64 w0 = (u64) blockIdx.x * tile;
 	const u32 wlen = (u32) (na - w0 < (u64) CAP ? na - w0 : (u64) CAP);
 	const u32 tlen = tile < wlen ? tile : wlen;
 	if (tid == 0) { s_first = U32_MAX; s_end = U32_MAX; }
-	__syncthreads();
-
-	// 1. bucket heads in the window; st = inclusive max-scan of (head ? idx+1 : 0)
-	u32 st[ITEMS];
-	u32 carry = 0, fmin = U32_MAX, emin = U32_MAX;
-#pragma unroll
-	for (int i = 0; i < ITEMS; i++) {
-		u32 idx = w * WCH + i * 32 + l;
-		u32 v = 0;
-		if (idx < wlen) {
-			u64 t = w0 + idx;
-			bool head = (t == 0) || (lr[t - 1] != lr[t]);
-			r2s[idx] = r2[t];
-			if (head) {
-				v = idx + 1;
-				if (idx < tlen) fmin = idx < fmin ? idx : fmin;
-				else emin = idx < emin ? idx : emin;
+	// The kernel alternates between short bursts of loads and long stretches of shared-memory
+	// work, which leaves too few bytes in flight to cover DRAM latency: every CTA therefore
+	// pulls the window of the CTA that will run about one wave later into L2.
+	{
+		constexpr u32 LINES = CAP / 32; // 128-byte lines per array and window
+		const u64 pb = ((u64) blockIdx.x + (u64) NUM_SMS * (TileCfg<CAP>::MINB + 1)) * tile;
+		for (u32 q = tid; q < 3 * LINES; q += THREADS) {
+			const u32 arr = q / LINES;
+			const u64 e = pb + (u64) (q % LINES) * 32;
+			if (e < na) {
+				const u32 *a = (arr == 0 ? lr : arr == 1 ? r2 : lp) + e;
+				asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
 			}
 		}
-		u32 inc = warp_incl_max(v);
-		inc = inc > carry ? inc : carry;
-		st[i] = inc;
-		carry = __shfl_sync(0xffffffffu, inc, 31);
 	}
-	if (l == 31) s_wtot[w] = carry;
-	fmin = ~warp_reduce_max(~fmin);
-	emin = ~warp_reduce_max(~emin);
+	if (STAGE) {
+#pragma unroll
+		for (int i = 0; i < ITEMS; i++) {
+			const u32 idx = i * THREADS + tid;
+			if (idx < wlen) { cp_async4(lrs + idx + 1, lr + w0 + idx); cp_async4(r2s + idx, r2 + w0 + idx); cp_async4(lps + idx, lp + w0 + idx); }
+		}
+		if (tid == 0 && w0 > 0) cp_async4(lrs, lr + w0 - 1);
+		cp_async_wait_all();
+	}
+	__syncthreads();
+
+	// 1. bucket heads in the window (warp w scans [w*WCH, (w+1)*WCH)); st = index + 1 of the
+	//    last head at or before the element, as far as this warp can see.  All loads first:
+	//    the scan below is one dependent chain.
+	u32 st[ITEMS];
+#pragma unroll
+	for (int i = 0; i < ITEMS; i++) {
+		const u32 idx = w * WCH + i * 32 + l;
+		st[i] = idx < wlen ? (STAGE ? lrs[idx + 1] : lr[w0 + idx]) : 0u;
+	}
+	if (!STAGE) {
+#pragma unroll
+		for (int i = 0; i < ITEMS; i++) {
+			const u32 idx = w * WCH + i * 32 + l;
+			if (idx < wlen) r2s[idx] = r2[w0 + idx];
+		}
+	}
+	u32 hmask = 0;
+	u32 carry = 0, fmin = U32_MAX, emin = U32_MAX;
+	u32 pl = 0;
+	if (l == 0 && w * WCH < wlen && w0 + w * WCH > 0) pl = STAGE ? lrs[w * WCH] : lr[w0 + w * WCH - 1];
+#pragma unroll
+	for (int i = 0; i < ITEMS; i++) {
+		const u32 base = w * WCH + i * 32;
+		const u32 idx = base + l;
+		const u32 v = st[i];
+		u32 pv = __shfl_up_sync(0xffffffffu, v, 1);
+		if (l == 0) pv = pl;
+		pl = __shfl_sync(0xffffffffu, v, 31);
+		const bool head = idx < wlen && (w0 + idx == 0 || pv != v);
+		const u32 hm = __ballot_sync(0xffffffffu, head);
+		hmask |= (head ? 1u : 0u) << i;
+		st[i] = ts_last_flag(hm, base, carry);
+		// first head inside the tile, first head behind it (warp-uniform)
+		const u32 inl = tlen > base ? (tlen - base >= 32 ? 0xffffffffu : (1u << (tlen - base)) - 1u) : 0u;
+		if ((hm & inl) && fmin == U32_MAX) fmin = base + (u32) __ffs(hm & inl) - 1;
+		if ((hm & ~inl) && emin == U32_MAX) emin = base + (u32) __ffs(hm & ~inl) - 1;
+	}
 	if (l == 0) {
+		s_wtot[w] = carry;
 		if (fmin != U32_MAX) atomicMin(&s_first, fmin);
 		if (emin != U32_MAX) atomicMin(&s_end, emin);
 	}
@@ -357,86 +419,118 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 		if (w0 + wlen == na) endidx = wlen;
 		else { if (tid == 0) scal[1] = 1u; return; } // a bucket larger than CAP - tile: host contract broken
 	}
+	const u32 cnt = endidx - first;
 	u32 wpre = 0;
 	for (u32 ww = 0; ww < w; ww++) { u32 x = s_wtot[ww]; wpre = x > wpre ? x : wpre; }
 
-	// 2. st = window index of the element's bucket head; the last element of a bucket posts its end
+	// 2. every owned element posts its bucket head; the last element of a bucket posts the end
 #pragma unroll
 	for (int i = 0; i < ITEMS; i++) {
-		u32 idx = w * WCH + i * 32 + l;
+		const u32 idx = w * WCH + i * 32 + l;
+		const u32 hm = __ballot_sync(0xffffffffu, (hmask >> i) & 1u);
+		const u32 hn = i + 1 < ITEMS ? __ballot_sync(0xffffffffu, (hmask >> (i + 1 < ITEMS ? i + 1 : i)) & 1u) : 0u;
 		if (idx >= first && idx < endidx) {
-			u32 hb = (st[i] > wpre ? st[i] : wpre) - 1;
-			st[i] = hb;
-			u64 t = w0 + idx;
-			if (idx + 1 == endidx || lr[t + 1] != lr[t]) bend[hb] = (unsigned short) (idx + 1);
+			const u32 hb = (st[i] > wpre ? st[i] : wpre) - 1;
+			hbs[idx] = (unsigned short) hb;
+			bool last;
+			if (idx + 1 == endidx) last = true;
+			else if (l < 31) last = (hm >> (l + 1)) & 1u;
+			else if (i + 1 < ITEMS) last = hn & 1u;
+			else last = STAGE ? lrs[idx + 2] != lrs[idx + 1] : lr[w0 + idx + 1] != lr[w0 + idx];
+			if (last) bend[hb] = (unsigned short) (idx + 1);
 		}
 	}
 	__syncthreads();
 
-	// 3. pivot of the bucket, minority / smaller flags, their prefix counts over the window
+	// From here on the cnt owned elements are dealt out evenly: warp w takes
+	// [first + w*per, first + (w+1)*per), per a multiple of 32.
+	const u32 per = ((cnt + NW * 32 - 1) / (NW * 32)) * 32;
+	const u32 wb = first + w * per;
+
+	// 3. pivot of the bucket, minority / smaller flags, their prefix counts over the owned range
 	u32 mmask = 0, gmask = 0, run = 0;
 #pragma unroll
 	for (int i = 0; i < ITEMS; i++) {
-		u32 idx = w * WCH + i * 32 + l;
-		bool mn = false, ls = false;
-		if (idx >= first && idx < endidx) {
-			u32 hb = st[i];
-			u32 pv = r2s[hb + (((u32) bend[hb] - hb) >> 1)];
-			u32 rr = r2s[idx];
-			mn = rr != pv; ls = rr < pv;
+		if ((u32) i * 32 < per) {
+			const u32 idx = wb + i * 32 + l;
+			bool mn = false, ls = false;
+			if (idx < endidx) {
+				const u32 hb = hbs[idx];
+				st[i] = hb;
+				const u32 pv = r2s[hb + (((u32) bend[hb] - hb) >> 1)];
+				const u32 rr = r2s[idx];
+				mn = rr != pv; ls = rr < pv;
+			}
+			const u32 bm = __ballot_sync(0xffffffffu, mn), bl = __ballot_sync(0xffffffffu, ls);
+			const u32 lt = lanemask_lt();
+			if (idx < endidx) PXI[idx + 1] = run + (u32) __popc(bm & lt) + (mn ? 1u : 0u) + (((u32) __popc(bl & lt) + (ls ? 1u : 0u)) << 16); // inside the warp, for now
+			run += (u32) __popc(bm) + ((u32) __popc(bl) << 16);
+			mmask |= (mn ? 1u : 0u) << i;
+			gmask |= ((mn && !ls) ? 1u : 0u) << i;
 		}
-		u32 bm = __ballot_sync(0xffffffffu, mn), bl = __ballot_sync(0xffffffffu, ls);
-		u32 lt = lanemask_lt();
-		PXI[idx + 1] = run + (u32) __popc(bm & lt) + (mn ? 1u : 0u) + (((u32) __popc(bl & lt) + (ls ? 1u : 0u)) << 16); // inside the warp, for now
-		run += (u32) __popc(bm) + ((u32) __popc(bl) << 16);
-		mmask |= (mn ? 1u : 0u) << i;
-		gmask |= ((mn && !ls) ? 1u : 0u) << i;
 	}
 	if (l == 0) s_wtot[w] = run;
-	if (tid == 0) PXI[0] = 0;
+	if (tid == 0) PXI[first] = 0;
 	__syncthreads();
 	u32 ppre = 0, ptot = 0;
 	for (u32 ww = 0; ww < NW; ww++) { u32 x = s_wtot[ww]; if (ww < w) ppre += x; ptot += x; }
 	const u32 nmin = ptot & 0xFFFFu;
 	if (ppre) {
 #pragma unroll
-		for (int i = 0; i < ITEMS; i++) PXI[w * WCH + i * 32 + l + 1] += ppre;
+		for (int i = 0; i < ITEMS; i++)
+			if ((u32) i * 32 < per && wb + i * 32 + l < endidx) PXI[wb + i * 32 + l + 1] += ppre;
 	}
 	__syncthreads();
 
-	// 4. elements equal to their pivot leave; the minority writes its keys (r2s is dead: its
-	//    last read lies before the two barriers above)
+	// 4. elements equal to their pivot leave; the minority writes its keys (r2s and hbs are
+	//    dead: their last reads lie before the two barriers above)
 	u32 mx = 0;
+	constexpr int P4C = ITEMS < 8 ? ITEMS : 8; // global loads of a chunk of items go out together
 #pragma unroll
-	for (int i = 0; i < ITEMS; i++) {
-		u32 idx = w * WCH + i * 32 + l;
-		if (idx >= first && idx < endidx) {
-			const u32 hb = st[i];
-			const u32 x = PXI[idx];
-			const u64 t = w0 + idx;
-			if ((mmask >> i) & 1u) {
-				key[ts_sw(x & 0xFFFFu)] = ((u64) hb << (33 + LOGC)) | ((u64) ((gmask >> i) & 1u) << (32 + LOGC)) | ((u64) r2[t] << LOGC) | (u64) idx;
-			} else {
-				const u32 end = bend[hb];
-				const u32 xh = PXI[hb], xe = PXI[end];
-				const u32 nless = (xe >> 16) - (xh >> 16);
-				const u32 neq = (end - hb) - ((xe & 0xFFFFu) - (xh & 0xFFFFu));
-				const u32 out = hb + nless + (idx - hb) - ((x & 0xFFFFu) - (xh & 0xFFFFu));
-				const u32 p = lp[t];
-				const u32 nr = lr[t] + nless;
-				const bool single = neq == 1;
-				if (nless) R[p] = nr;           // otherwise the rank is the one the suffix already has
-				if (single) SA[nr] = p;
-				lp_out[w0 + out] = p;
-				lr_out[w0 + out] = nr;
-				cls_out[w0 + out] = (u8) (single ? CLS_DROP : CLS_SMALL);
-				if (!single) mx = neq > mx ? neq : mx;
+	for (int i0 = 0; i0 < ITEMS; i0 += P4C) {
+		u32 pv4[P4C], rv4[P4C];
+#pragma unroll
+		for (int c = 0; c < P4C; c++) {
+			const int i = i0 + c;
+			const u32 idx = wb + i * 32 + l;
+			pv4[c] = 0; rv4[c] = 0;
+			if ((u32) i * 32 < per && idx < endidx) {
+				if ((mmask >> i) & 1u) rv4[c] = r2[w0 + idx];
+				else if (STAGE) { pv4[c] = lps[idx]; rv4[c] = lrs[idx + 1]; }
+				else { pv4[c] = lp[w0 + idx]; rv4[c] = lr[w0 + idx]; }
+			}
+		}
+#pragma unroll
+		for (int c = 0; c < P4C; c++) {
+			const int i = i0 + c;
+			const u32 idx = wb + i * 32 + l;
+			if ((u32) i * 32 < per && idx < endidx) {
+				const u32 hb = st[i];
+				const u32 x = PXI[idx];
+				if ((mmask >> i) & 1u) {
+					key[ts_sw(x & 0xFFFFu)] = ((u64) hb << (33 + LOGC)) | ((u64) ((gmask >> i) & 1u) << (32 + LOGC)) | ((u64) rv4[c] << LOGC) | (u64) idx;
+				} else {
+					const u32 end = bend[hb];
+					const u32 xh = PXI[hb], xe = PXI[end];
+					const u32 nless = (xe >> 16) - (xh >> 16);
+					const u32 neq = (end - hb) - ((xe & 0xFFFFu) - (xh & 0xFFFFu));
+					const u32 out = hb + nless + (idx - hb) - ((x & 0xFFFFu) - (xh & 0xFFFFu));
+					const u32 p = pv4[c];
+					const u32 nr = rv4[c] + nless;
+					const bool single = neq == 1;
+					if (nless) R[p] = nr;           // otherwise the rank is the one the suffix already has
+					if (single) SA[nr] = p;
+					lp_out[w0 + out] = p;
+					lr_out[w0 + out] = nr;
+					cls_out[w0 + out] = (u8) (single ? CLS_DROP : CLS_SMALL);
+					if (!single) mx = neq > mx ? neq : mx;
+				}
 			}
 		}
 	}
 	if (nmin == 0) {
 		mx = warp_reduce_max(mx);
-		if (l == 0 && mx) atomicMax(&scal[0], mx);
+		if (l == 0 && mx > *reinterpret_cast<volatile u32 *>(scal)) atomicMax(&scal[0], mx);
 		return;
 	}
 	u32 net = 32;
@@ -447,62 +541,56 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 	// 5. sort the minority
 	tile_bitonic_sort_rt<THREADS>(key, net);
 
-	// 6. sub-bucket heads among them: st = inclusive max-scan of (sub-head ? s+1 : 0)
+	// 6. sub-bucket heads among them (dealt out like the owned range): st = index + 1 of the
+	//    last sub-head at or before the element
+	const u32 per2 = ((nmin + NW * 32 - 1) / (NW * 32)) * 32;
+	const u32 sb = w * per2;
 	carry = 0;
-	if (w * WCH < nmin) {
 #pragma unroll
-		for (int i = 0; i < ITEMS; i++) {
-			u32 s = w * WCH + i * 32 + l;
-			u32 v = 0;
-			if (s < nmin) {
-				bool sh = s == 0;
-				if (!sh) sh = (key[ts_sw(s)] >> LOGC) != (key[ts_sw(s - 1)] >> LOGC);
-				if (sh) v = s + 1;
-			}
-			u32 inc = warp_incl_max(v);
-			inc = inc > carry ? inc : carry;
-			st[i] = inc;
-			carry = __shfl_sync(0xffffffffu, inc, 31);
+	for (int i = 0; i < ITEMS; i++) {
+		if ((u32) i * 32 < per2) {
+			const u32 s = sb + i * 32 + l;
+			bool sh = false;
+			if (s < nmin) sh = s == 0 || (key[ts_sw(s)] >> LOGC) != (key[ts_sw(s - 1)] >> LOGC);
+			st[i] = ts_last_flag(__ballot_sync(0xffffffffu, sh), sb + i * 32, carry);
 		}
 	}
-	if (l == 31) s_wtot[w] = carry;
+	if (l == 0) s_wtot[w] = carry;
 	__syncthreads();
 	wpre = 0;
 	for (u32 ww = 0; ww < w; ww++) { u32 x = s_wtot[ww]; wpre = x > wpre ? x : wpre; }
 
 	// 7. ranks, classes, outputs of the minority: smaller ones in front of the bucket's equal
 	//    elements, greater ones behind them
-	if (w * WCH < nmin) {
 #pragma unroll
-		for (int i = 0; i < ITEMS; i++) {
-			u32 s = w * WCH + i * 32 + l;
-			if (s < nmin) {
-				const u64 k = key[ts_sw(s)];
-				const u32 hs = (st[i] > wpre ? st[i] : wpre) - 1;
-				const u32 hb = (u32) (k >> (33 + LOGC));
-				const u32 e = (u32) k & (u32) (CAP - 1);
-				const bool last = (s + 1 >= nmin) || ((key[ts_sw(s + 1)] >> LOGC) != (k >> LOGC));
-				const u32 end = bend[hb];
-				const u32 xh = PXI[hb], xe = PXI[end];
-				const u32 pmh = xh & 0xFFFFu;
-				const u32 neq = (end - hb) - ((xe & 0xFFFFu) - pmh);
-				const u32 off = ((k >> (32 + LOGC)) & 1ull) ? neq : 0u;
-				const u32 out = hb + (s - pmh) + off;
-				const u32 hrel = (hs - pmh) + off;     // sub-bucket head, relative to the bucket head
-				const u32 nr = lr[w0 + hb] + hrel;
-				const u32 p = lp[w0 + e];
-				const bool single = hs == s && last;
-				if (hrel) R[p] = nr;
-				if (single) SA[nr] = p;
-				lp_out[w0 + out] = p;
-				lr_out[w0 + out] = nr;
-				cls_out[w0 + out] = (u8) (single ? CLS_DROP : CLS_SMALL);
-				if (last && s != hs) { u32 sz = s - hs + 1; mx = sz > mx ? sz : mx; }
-			}
+	for (int i = 0; i < ITEMS; i++) {
+		const u32 s = sb + i * 32 + l;
+		if ((u32) i * 32 < per2 && s < nmin) {
+			const u64 k = key[ts_sw(s)];
+			const u32 hs = (st[i] > wpre ? st[i] : wpre) - 1;
+			const u32 hb = (u32) (k >> (33 + LOGC));
+			const u32 e = (u32) k & (u32) (CAP - 1);
+			const bool last = (s + 1 >= nmin) || ((key[ts_sw(s + 1)] >> LOGC) != (k >> LOGC));
+			const u32 end = bend[hb];
+			const u32 xh = PXI[hb], xe = PXI[end];
+			const u32 pmh = xh & 0xFFFFu;
+			const u32 neq = (end - hb) - ((xe & 0xFFFFu) - pmh);
+			const u32 off = ((k >> (32 + LOGC)) & 1ull) ? neq : 0u;
+			const u32 out = hb + (s - pmh) + off;
+			const u32 hrel = (hs - pmh) + off;     // sub-bucket head, relative to the bucket head
+			const u32 nr = (STAGE ? lrs[hb + 1] : lr[w0 + hb]) + hrel;
+			const u32 p = STAGE ? lps[e] : lp[w0 + e];
+			const bool single = hs == s && last;
+			if (hrel) R[p] = nr;
+			if (single) SA[nr] = p;
+			lp_out[w0 + out] = p;
+			lr_out[w0 + out] = nr;
+			cls_out[w0 + out] = (u8) (single ? CLS_DROP : CLS_SMALL);
+			if (last && s != hs) { u32 sz = s - hs + 1; mx = sz > mx ? sz : mx; }
 		}
 	}
 	mx = warp_reduce_max(mx);
-	if (l == 0 && mx) atomicMax(&scal[0], mx);
+	if (l == 0 && mx > *reinterpret_cast<volatile u32 *>(scal)) atomicMax(&scal[0], mx);
 }
 
 template <int CAP> static void launch_tile_sort(Dev &d, const u32 *lp, const u32 *lr, const u32 *r2, u64 na, u32 maxb,
