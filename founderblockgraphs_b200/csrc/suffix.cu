@@ -89,13 +89,18 @@ template <int MODE> __global__ void __launch_bounds__(KM_THREADS) k1_kmer_kernel
 					if (cur == key) break;
 					if (cur == KD_EMPTY) {
 						u64 prev = atomicCAS(reinterpret_cast<unsigned long long *>(dk.key + s), (unsigned long long) KD_EMPTY, (unsigned long long) key);
-						if (prev == KD_EMPTY) { dk.first[s] = (u32) g; break; }
-						if (prev == key) break;
+						if (prev == KD_EMPTY || prev == key) break;
 					}
 					s = (s + 1) & dk.mask;
 					if (++probes > KD_MAX_PROBES) { *dk.overflow = 1u; s = U32_MAX; break; }
 				}
-				if (s != U32_MAX) { dk.ord_of[g] = atomicAdd(dk.cnt + s, 1u); dk.slot_of[g] = s; }
+				if (s != U32_MAX) {
+					dk.ord_of[g] = atomicAdd(dk.cnt + s, 1u);
+					dk.slot_of[g] = s;
+					// smallest member of the bucket: it orders the S list by text position (a reduction
+					// without a return value, so nothing waits for it)
+					atomicMin(dk.first + s, (u32) g);
+				}
 			}
 		} else {
 			u32 bin = (u32) (key >> sh.hshift);
@@ -644,7 +649,7 @@ __global__ void k1_dict_counts_kernel(const u32 *__restrict__ lv, const u32 *__r
 	u32 c = cnt[lv[t]];
 	call[t] = c; cbig[t] = c > BSMALL ? c : 0u;
 }
-// info[slot] = (rank, start of the bucket in its list, size, first arrival); A = directory of the small buckets by text position
+// info[slot] = (rank, start of the bucket in its list, size, smallest member); A = directory of the small buckets by text position
 __global__ void k1_dict_assign_kernel(const u32 *__restrict__ lv, const u32 *__restrict__ cnt, const u32 *__restrict__ first, const u32 *__restrict__ rk, const u32 *__restrict__ bs,
                                       u32 nd, u32 rank_off, uint4 *__restrict__ info, u32 *__restrict__ A, u32 *__restrict__ maxb) {
 	u32 t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -717,6 +722,7 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	d.begin(K_KMER);
 	FBG_CUDA(cudaMemsetAsync(dk.key, 0xFF, (u64) cap * sizeof(u64), d.stream));
 	FBG_CUDA(cudaMemsetAsync(dk.cnt, 0, (u64) cap * sizeof(u32), d.stream));
+	FBG_CUDA(cudaMemsetAsync(dk.first, 0xFF, (u64) cap * sizeof(u32), d.stream));
 	KmerShard sh;
 	sh.bin_lo = 0; sh.bin_hi = 0; sh.hshift = 0; sh.block_off = nullptr; sh.hist = nullptr; sh.block_cnt = nullptr;
 	k1_kmer_kernel<4><<<km_grid, KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, sh, nullptr, nullptr, dk);
