@@ -322,7 +322,7 @@ int fbg_get_stats(fbg_ctx *ctx, fbg_stats *out) {
 	p.dev.resolve();
 	std::memset(out, 0, sizeof *out);
 	out->m = p.m; out->n = p.n; out->text_len = p.N; out->gaps = p.gaps; out->to_ignore = p.toignore;
-	out->sa_rounds = p.sa_rounds; out->arena_peak_bytes = p.dev.arena_peak; out->dp_passes = p.dp_passes;
+	out->sa_rounds = p.sa_rounds; out->arena_peak_bytes = p.dev.arena_peak; out->dp_passes = p.dp_passes; out->kmer_dict = p.kmer_dict;
 	for (int k = 0; k < K_COUNT; k++) {
 		out->kernel_ms[k] = p.dev.stats[k].ms; out->kernel_bytes[k] = p.dev.stats[k].bytes; out->kernel_launches[k] = p.dev.stats[k].launches;
 	}

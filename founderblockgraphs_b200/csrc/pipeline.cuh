@@ -59,6 +59,7 @@ struct Pipeline {
 	bool keep_sa = false;
 	int sa_rounds = 0;
 	u64 dp_chunk = 0, dp_warm = 0; // 0 = defaults (segdp.cu); settable for the parity tests
+	int kmer_dict = 0;             // round 0 of the last index build went through the k-mer dictionary
 	int dp_passes = 0;             // verify passes of the last DP (0 = single chunk, < 0 = fell back to the whole-range wavefront)
 	bool have_msa = false, have_index = false, have_f = false, have_seg = false;
 	int seg_status = 0; // 0 ok, 1 "no segmentation"

@@ -798,6 +798,7 @@ void k1_suffix_array(Pipeline &p) {
 	while ((1 << b) < sigma) b++;
 	int K = 64 / b;
 	if (K > 32) K = 32;
+	if (K * b == 64) K--; // keep the all-ones key free: it marks the empty slots of the k-mer dictionary
 	const int key_bits0 = K * b;
 	const u32 km_grid = div_up(N, KM_TILE);
 
@@ -890,6 +891,7 @@ void k1_suffix_array(Pipeline &p) {
 	const bool debug = getenv("FBG_DEBUG") != nullptr;
 	const u32 tile_ratio = getenv("FBG_TILE_RATIO") ? (u32) atoi(getenv("FBG_TILE_RATIO")) : 2u;
 	if (debug) fprintf(stderr, "[fbg] rank %d K1 round 0 %s\n", dist.rank, by_dict ? "through the k-mer dictionary" : "by sorting all suffixes");
+	p.kmer_dict = by_dict ? 1 : 0;
 	if (by_dict) {
 		// the state a sorted round 0 ends in
 		p.sa_rounds = 1;

@@ -61,6 +61,7 @@ typedef struct fbg_stats {
 	double kernel_bytes[FBG_N_KERNELS];
 	uint64_t kernel_launches[FBG_N_KERNELS];
 	int64_t dp_passes;            /* K3: verify passes of the chunked DP (0 = one chunk, < 0 = that many passes were spent and the whole-range wavefront was needed) */
+	int64_t kmer_dict;            /* K1 round 0: 1 = through the k-mer dictionary, 0 = by sorting all suffixes (multi-GPU build, too many distinct k-mers, 64-bit k-mers) */
 } fbg_stats;
 
 /* index -> name for the arrays above ("pack", "kmer", "radix_hist", ...) */

@@ -87,6 +87,33 @@ def test_suffix_array_lcp_msa_like(gpu_ctx):
     _check_index(gpu_ctx, synth.make_msa(60, 5000, snp=0.002, gap_div=500, seed=11))
 
 
+def test_suffix_array_round0_paths(gpu_ctx, monkeypatch):
+    """Round 0 has two implementations: the k-mer dictionary (few distinct k-mers, the MSA case) and
+    the sort of all suffixes (everything else).  Both on the same inputs, and the switch between them."""
+    rng = np.random.default_rng(17)
+    msa_like = synth.make_msa(40, 3000, snp=0.003, gap_div=400, seed=3)
+    periodic = np.tile(np.frombuffer(b"ACGTAC" * 500, np.uint8), (4, 1)).copy()
+    big_bucket = np.full((3, 3000), ord("A"), np.uint8)   # one bucket above the tile path's limit
+    big_bucket[:, -8:] = np.frombuffer(b"CGTCGTCG", np.uint8)
+    for a in (msa_like, periodic, big_bucket):
+        _check_index(gpu_ctx, a)
+        assert gpu_ctx.stats()["kmer_dict"] == 1
+    monkeypatch.setenv("FBG_NO_KMER_DICT", "1")
+    for a in (msa_like, periodic, big_bucket):
+        _check_index(gpu_ctx, a)
+        assert gpu_ctx.stats()["kmer_dict"] == 0
+    monkeypatch.delenv("FBG_NO_KMER_DICT")
+    # unrelated rows: nearly every k-mer is distinct, the table overflows, the sort takes over
+    unrelated = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, size=(48, 8000))]
+    _check_index(gpu_ctx, unrelated)
+    assert gpu_ctx.stats()["kmer_dict"] == 0
+    # alphabets whose codes fill the 64-bit key exactly (b = 2: K = 32 -> 31; b = 4: K = 16 -> 15)
+    _check_index(gpu_ctx, np.tile(np.frombuffer(b"AC", np.uint8)[rng.integers(0, 2, size=700)], (6, 1)))
+    assert gpu_ctx.stats()["kmer_dict"] == 1
+    _check_index(gpu_ctx, np.tile(np.frombuffer(b"ACDEFGHIKLMNP", np.uint8)[rng.integers(0, 13, size=900)], (5, 1)))
+    assert gpu_ctx.stats()["kmer_dict"] == 1
+
+
 # ----------------------------------------------------------------- golden (reference)
 @pytest.mark.parametrize("case", elastic_cases(), ids=case_id)
 def test_elastic_golden(gpu_ctx, case, tmp_path):

@@ -27,4 +27,4 @@ for rep in range(3):
     T("run_device (all)", lambda: ctx.run_ptr(dev.data_ptr(), m, n, True))
     T("run_host pinned (all)", lambda: ctx.run_ptr(pin.data_ptr(), m, n, False))
 st = ctx.stats()
-print({k: (round(v["ms"], 2), v["launches"]) for k, v in st["kernels"].items()}, "rounds", st["sa_rounds"], "dp_passes", st["dp_passes"], "arena GB", st["arena_peak_bytes"] / 1e9)
+print({k: (round(v["ms"], 2), v["launches"]) for k, v in st["kernels"].items()}, "rounds", st["sa_rounds"], "dp_passes", st["dp_passes"], "kmer_dict", st["kmer_dict"], "arena GB", st["arena_peak_bytes"] / 1e9)
