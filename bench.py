@@ -34,13 +34,14 @@ import numpy as np  # noqa: E402
 DOMINANT_NAMES = {
     "tile_sort": "k1_tile_sort_kernel (bucket-local shared-memory sort of tied suffixes, K1)",
     "radix_scatter": "rs_scatter_kernel (radix scatter passes of K1)",
-    "doubling_aux": "k1_cls_write_kernel + k1_update_kernel (compaction with fused rank look-up, K1)",
+    "doubling_aux": "k1_cls_write_kernel + k1_dict_emit_kernel (list compaction / round-0 emission with fused rank look-up, K1)",
     "fcol": "k2_fcol_kernel (per-column f(x))",
 }
 ROOFLINE_NOTES = {
-    "tile_sort": "algorithmic HBM bytes are 25 B per tied suffix per round (read lp,lr,r2; write lp,lr,cls; 4 B rank scatter); the kernel is "
-                 "bound by shared-memory bandwidth and integer issue of the in-tile sorting network, not by HBM (ncu: profiles/README.md) - "
-                 "it replaced seven device-wide radix passes (470 B per suffix per round)",
+    "tile_sort": "algorithmic HBM bytes are 25 B per tied suffix per round (read lp,lr,r2; write lp,lr,cls; 4 B rank scatter); ncu DRAM "
+                 "traffic is 1.05x that (no re-reads).  The kernel is bound by instruction issue (61-72 % of the issue slots busy: head "
+                 "scans, prefix counts and the shared-memory sorting network of each bucket's minority), not by HBM "
+                 "(profiles/README.md) - it replaced seven device-wide radix passes (470 B per suffix per round)",
 }
 METRIC = "msa_cells_per_sec_end_to_end_efg_build"
 UNIT = "cells/s"
