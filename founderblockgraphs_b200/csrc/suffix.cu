@@ -81,33 +81,67 @@ template <int MODE> __global__ void __launch_bounds__(KM_THREADS) k1_kmer_kernel
 		kk[it] = key;
 		if (MODE == 0) { if (g < N) { keys[g] = key; vals[g] = (u32) g; } }
 		else if (MODE == 4) {
-			if (g < N) {
-				u32 s = kd_hash(key) & dk.mask, probes = 0;
-				for (;;) {
-					// a stale EMPTY only costs the CAS, and a slot that holds a key never changes
-					u64 cur = __ldcg(dk.key + s);
-					if (cur == key) break;
-					if (cur == KD_EMPTY) {
-						u64 prev = atomicCAS(reinterpret_cast<unsigned long long *>(dk.key + s), (unsigned long long) KD_EMPTY, (unsigned long long) key);
-						if (prev == KD_EMPTY || prev == key) break;
-					}
-					s = (s + 1) & dk.mask;
-					if (++probes > KD_MAX_PROBES) { *dk.overflow = 1u; s = U32_MAX; break; }
-				}
-				if (s != U32_MAX) {
-					dk.ord_of[g] = atomicAdd(dk.cnt + s, 1u);
-					dk.slot_of[g] = s;
-					// smallest member of the bucket: it orders the S list by text position (a reduction
-					// without a return value, so nothing waits for it)
-					atomicMin(dk.first + s, (u32) g);
-				}
-			}
+			// entered below, all items of the thread together
 		} else {
 			u32 bin = (u32) (key >> sh.hshift);
 			if (MODE == 1) { if (g < N) atomicAdd(&sh.hist[bin], 1u); }
 			else if (g < N && bin >= sh.bin_lo && bin < sh.bin_hi) mine |= 1u << it;
 		}
 		key = ((key << b) | sc[o + it + K]) & kmask;
+	}
+	if (MODE == 4) {
+		// The eight table accesses of a thread are independent: first probes, arrival counters and
+		// results each go out as a batch, so a thread waits for L2 three times, not 8 x 3 times.
+		const u64 g0 = base + o;
+		u32 sl[KM_ITEMS], od[KM_ITEMS];
+		u64 cur[KM_ITEMS];
+#pragma unroll
+		for (int it = 0; it < KM_ITEMS; it++) {
+			sl[it] = kd_hash(kk[it]) & dk.mask;
+			cur[it] = g0 + it < N ? __ldcg(dk.key + sl[it]) : kk[it];
+		}
+#pragma unroll
+		for (int it = 0; it < KM_ITEMS; it++) {
+			if (g0 + it < N && cur[it] != kk[it]) {
+				const u64 key = kk[it];
+				u32 s = sl[it], probes = 0;
+				u64 c = cur[it];
+				for (;;) {
+					// a stale EMPTY only costs the CAS, and a slot that holds a key never changes
+					if (c == key) break;
+					if (c == KD_EMPTY) {
+						u64 prev = atomicCAS(reinterpret_cast<unsigned long long *>(dk.key + s), (unsigned long long) KD_EMPTY, (unsigned long long) key);
+						if (prev == KD_EMPTY || prev == key) break;
+					}
+					s = (s + 1) & dk.mask;
+					if (++probes > KD_MAX_PROBES) { *dk.overflow = 1u; s = U32_MAX; break; }
+					c = __ldcg(dk.key + s);
+				}
+				sl[it] = s;
+			}
+		}
+		bool full = g0 + KM_ITEMS <= N;
+#pragma unroll
+		for (int it = 0; it < KM_ITEMS; it++) {
+			od[it] = 0;
+			if (g0 + it < N && sl[it] != U32_MAX) od[it] = atomicAdd(dk.cnt + sl[it], 1u);
+			else full = false;
+		}
+		if (full) {
+			// 32 contiguous bytes per thread and array
+			uint4 *so = reinterpret_cast<uint4 *>(dk.slot_of + g0), *oo = reinterpret_cast<uint4 *>(dk.ord_of + g0);
+			so[0] = make_uint4(sl[0], sl[1], sl[2], sl[3]); so[1] = make_uint4(sl[4], sl[5], sl[6], sl[7]);
+			oo[0] = make_uint4(od[0], od[1], od[2], od[3]); oo[1] = make_uint4(od[4], od[5], od[6], od[7]);
+		}
+#pragma unroll
+		for (int it = 0; it < KM_ITEMS; it++) {
+			if (g0 + it < N && sl[it] != U32_MAX) {
+				if (!full) { dk.slot_of[g0 + it] = sl[it]; dk.ord_of[g0 + it] = od[it]; }
+				// smallest member of the bucket: it orders the S list by text position (a reduction
+				// without a return value, so nothing waits for it)
+				atomicMin(dk.first + sl[it], (u32) (g0 + it));
+			}
+		}
 	}
 	if (MODE == 2 || MODE == 3) {
 		u32 tot;
@@ -267,19 +301,31 @@ __global__ void __launch_bounds__(CP_THREADS) k1_cls_write_kernel(const u8 *__re
 	u64 ex = partial[blockIdx.x] + (base ? *base : 0ull);
 	for (u32 ww = 0; ww < w; ww++) ex += wtot[ww];
 	u32 qs = (u32) ex, qb = (u32) (ex >> 32);
-	// pass 2
+	// pass 2, eight items at a time: their loads, then their rank look-ups, then the writes, each as
+	// one batch (the output arrays may alias the inputs as far as the compiler knows, so it would
+	// not reorder an item's loads over the stores of the item before)
 #pragma unroll
-	for (int i = 0; i < CP_ITEMS; i++) {
-		u64 t = w0 + (u64) i * 32 + l;
-		u32 ms = __ballot_sync(0xffffffffu, c[i] == CLS_SMALL), mb = __ballot_sync(0xffffffffu, c[i] == CLS_BIG);
-		if (c[i] != CLS_DROP) {
-			u32 p = lp[t], r = lr[t];
-			u64 q = (u64) p + hnext;
-			u32 r2 = q < N ? R[q] : 0u;
-			if (c[i] == CLS_SMALL) { u32 d = qs + __popc(ms & lanemask_lt()); o.Slp[d] = p; o.Slr[d] = r; o.Sr2[d] = r2; }
-			else { u32 d = qb + __popc(mb & lanemask_lt()); o.Bkey[d] = ((u64) r << nbits) | r2; o.Bval[d] = p; }
+	for (int i0 = 0; i0 < CP_ITEMS; i0 += 8) {
+		u32 pp[8], rr[8], r2[8];
+#pragma unroll
+		for (int k = 0; k < 8; k++) {
+			const u64 t = w0 + (u64) (i0 + k) * 32 + l;
+			pp[k] = 0; rr[k] = 0;
+			if (c[i0 + k] != CLS_DROP) { pp[k] = lp[t]; rr[k] = lr[t]; }
 		}
-		qs += __popc(ms); qb += __popc(mb);
+#pragma unroll
+		for (int k = 0; k < 8; k++) {
+			const u64 q = (u64) pp[k] + hnext;
+			r2[k] = (c[i0 + k] != CLS_DROP && q < N) ? R[q] : 0u;
+		}
+#pragma unroll
+		for (int k = 0; k < 8; k++) {
+			const int i = i0 + k;
+			const u32 ms = __ballot_sync(0xffffffffu, c[i] == CLS_SMALL), mb = __ballot_sync(0xffffffffu, c[i] == CLS_BIG);
+			if (c[i] == CLS_SMALL) { const u32 d = qs + __popc(ms & lanemask_lt()); o.Slp[d] = pp[k]; o.Slr[d] = rr[k]; o.Sr2[d] = r2[k]; }
+			else if (c[i] == CLS_BIG) { const u32 d = qb + __popc(mb & lanemask_lt()); o.Bkey[d] = ((u64) rr[k] << nbits) | r2[k]; o.Bval[d] = pp[k]; }
+			qs += __popc(ms); qb += __popc(mb);
+		}
 	}
 }
 
