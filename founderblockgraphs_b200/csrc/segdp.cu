@@ -144,13 +144,13 @@ __device__ __forceinline__ void elastic_scan(u64 j, u32 uj, u64 xmin, u32 n32, F
 // over the H/2 columns up to its own range: a single forced boundary would usually sit at a
 // column no good segmentation cuts at (f[t] - t can be hundreds of columns in gapped data).
 // One chunk (C > n) = the whole DP: then mml/bt are final.  bt may be null (chunked guess).
-__global__ void __launch_bounds__(DPW * 32) k3_elastic_dp_kernel(const u32 *__restrict__ f, const u32 *__restrict__ U, u64 n, u64 C, u64 H, u32 *mml, u32 *bt, u32 *fail) {
+__global__ void __launch_bounds__(DPW * 32) k3_elastic_dp_kernel(const u32 *__restrict__ f, const u32 *__restrict__ U, u64 n, u64 C, u64 H, u32 chunk0, u32 *mml, u32 *bt, u32 *fail) {
 	__shared__ u32 ring[DP_RING];   // mml (local values)
 	__shared__ u32 fring[DP_RING];  // f
 	__shared__ u32 uch[DP_CH];      // U[base .. base+DP_CH)
 	const u32 w = threadIdx.x >> 5, l = lane_id();
 	const u32 INV = (u32) n + 1;
-	const u64 s = (u64) blockIdx.x * C;
+	const u64 s = ((u64) blockIdx.x + chunk0) * C; // chunk0: first chunk of this GPU (sharded build)
 	const u64 e = s + C < n + 1 ? s + C : n + 1;
 	const u64 t = s > H ? s - H : 0;         // first source; nothing before it is looked at
 	const u64 t1 = s > H ? t + H / 2 : 0;    // last source
@@ -333,11 +333,11 @@ __device__ __forceinline__ void nonelastic_scan(u64 j, u32 vj, u64 jmin, FS fs, 
 }
 
 // chunk wavefront of the non-elastic DP; same chunk / origin convention as the elastic one
-__global__ void __launch_bounds__(DPW * 32) k3_nonelastic_dp_kernel(const u32 *__restrict__ v, u64 n, u64 C, u64 H, u32 *s, u32 *prev, u32 *fail) {
+__global__ void __launch_bounds__(DPW * 32) k3_nonelastic_dp_kernel(const u32 *__restrict__ v, u64 n, u64 C, u64 H, u32 chunk0, u32 *s, u32 *prev, u32 *fail) {
 	__shared__ u32 ring[DP_RING];
 	__shared__ u32 vch[DP_CH];
 	const u32 w = threadIdx.x >> 5, l = lane_id();
-	const u64 cs = (u64) blockIdx.x * C;
+	const u64 cs = ((u64) blockIdx.x + chunk0) * C;
 	const u64 e = cs + C < n ? cs + C : n;
 	// sources: prefixes ending at t0 .. t1 cost nothing (see the elastic kernel); jmin = t0 + 1
 	const u64 t0 = cs > H ? cs - H : 0, t1 = cs > H ? t0 + H / 2 : 0;
@@ -470,8 +470,8 @@ static void dp_solve(Pipeline &p, bool elastic, const u32 *U_or_v, u32 *val, u32
 	u32 *flags = reinterpret_cast<u32 *>(p.scalars + 26); // [0] warm-up lost, [1] changes of the last pass
 	u32 *h_flags = reinterpret_cast<u32 *>(p.h_scalars + 26);
 	auto whole = [&]() {
-		if (elastic) k3_elastic_dp_kernel<<<1, DPW * 32, 0, d.stream>>>(p.f, U_or_v, n, ncols + 1, 0, val, ptr, flags);
-		else k3_nonelastic_dp_kernel<<<1, DPW * 32, 0, d.stream>>>(U_or_v, n, ncols + 1, 0, val, ptr, flags);
+		if (elastic) k3_elastic_dp_kernel<<<1, DPW * 32, 0, d.stream>>>(p.f, U_or_v, n, ncols + 1, 0, 0u, val, ptr, flags);
+		else k3_nonelastic_dp_kernel<<<1, DPW * 32, 0, d.stream>>>(U_or_v, n, ncols + 1, 0, 0u, val, ptr, flags);
 		FBG_LAUNCH_CHECK();
 	};
 	// The warm-up must outlast the plateau (the optimal segment length so far), which is only
@@ -503,8 +503,22 @@ static void dp_solve(Pipeline &p, bool elastic, const u32 *U_or_v, u32 *val, u32
 		if (nchunks <= 1) break;
 		const u64 wq = C - H / 2 < 64 ? C - H / 2 : 64;
 		FBG_CUDA(cudaMemsetAsync(flags, 0, 2 * sizeof(u32), d.stream));
-		if (elastic) k3_elastic_dp_kernel<<<nchunks, DPW * 32, 0, d.stream>>>(p.f, U_or_v, n, C, H, val, nullptr, flags);
-		else k3_nonelastic_dp_kernel<<<nchunks, DPW * 32, 0, d.stream>>>(U_or_v, n, C, H, val, nullptr, flags);
+		// multi-GPU build: the chunks are independent, every GPU guesses its share of them and the
+		// guesses (each column written by one GPU, zero elsewhere) are merged by all-reduce(max)
+		u64 c0 = 0, c1 = nchunks;
+		const bool sharded = p.dist.world > 1;
+		if (sharded) {
+			plan_columns(nchunks, p.dist.world, p.dist.rank, &c0, &c1);
+			FBG_CUDA(cudaMemsetAsync(val, 0, ncols * sizeof(u32), d.stream));
+		}
+		if (c1 > c0) {
+			if (elastic) k3_elastic_dp_kernel<<<(u32) (c1 - c0), DPW * 32, 0, d.stream>>>(p.f, U_or_v, n, C, H, (u32) c0, val, nullptr, flags);
+			else k3_nonelastic_dp_kernel<<<(u32) (c1 - c0), DPW * 32, 0, d.stream>>>(U_or_v, n, C, H, (u32) c0, val, nullptr, flags);
+		}
+		if (sharded) {
+			p.dist.allreduce_max_u32(val, ncols, d.stream);
+			p.dist.allreduce_max_u32(flags, 1, d.stream);
+		}
 		k3_plateau_kernel<<<1, 1024, 0, d.stream>>>(val, ncols, C, H, wq, nchunks, (u32) n, !elastic, B);
 		k3_apply_plateau_kernel<<<div_up(ncols - C, 256), 256, 0, d.stream>>>(val, C, ncols, C, (u32) n, !elastic, B);
 		FBG_LAUNCH_CHECK();
