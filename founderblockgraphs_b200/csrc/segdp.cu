@@ -205,9 +205,9 @@ __global__ void __launch_bounds__(DPW * 32) k3_elastic_dp_kernel(const u32 *__re
 
 // One warp per column: (mml, bt) of column j from the values gin[] of its predecessors.
 __global__ void __launch_bounds__(256) k3_elastic_verify_kernel(const u32 *__restrict__ f, const u32 *__restrict__ U, u64 n, const u32 *__restrict__ gin,
-                                                                u32 *__restrict__ gout, u32 *__restrict__ bt, u32 *__restrict__ changes) {
-	const u64 j = (((u64) blockIdx.x * blockDim.x + threadIdx.x) >> 5) + 1;
-	if (j > n) return;
+                                                                u32 *__restrict__ gout, u32 *__restrict__ bt, u32 *__restrict__ changes, u64 j0, u64 j1) {
+	const u64 j = (((u64) blockIdx.x * blockDim.x + threadIdx.x) >> 5) + j0; // columns [j0, j1) of 1..n
+	if (j >= j1) return;
 	u32 best, bx;
 	elastic_scan(j, U[j], 0, (u32) n, [&](u64 x) { return f[x]; }, [&](u64 x) { return gin[x]; }, best, bx);
 	if (lane_id() == 0) {
@@ -265,6 +265,108 @@ __global__ void __launch_bounds__(32) k3_elastic_chase_kernel(const u32 *bt, con
 		return true;
 	});
 	if (l == 0) { out[0] = nb; out[1] = ld_vol(&mml[n]); }
+}
+
+// ---- backtrack in parallel
+// The chain n -> link(n) -> ... is a list traversal, and one warp walking it through staged
+// chunks took 6 ns per column (250 ms on 4*10^7 columns).  Links only point downwards, so:
+//   (1) every segment of CH_S columns resolves, for EACH of its columns, where a chain that
+//       passes through it leaves the segment (pointer jumping in shared memory);
+//   (2) one thread hops from segment to segment (one dependent load per segment) and notes
+//       where the chain enters each;
+//   (3) the entered segments walk their part of the chain in shared memory and mark it;
+//   (4) a scan of the marks places the boundaries in ascending order.
+// next(j): elastic  bt[j] (stop at 0 / none);  non-elastic  prev[j] - 1 (stop at prev = 0).
+constexpr u32 CH_S = 16384;
+constexpr u32 CH_STOP = U32_MAX;
+template <bool ELASTIC> __device__ __forceinline__ u32 chain_next(u32 link, u64 j) {
+	if (ELASTIC) return (link == 0 || link == U32_MAX || (u64) link >= j) ? CH_STOP : link;
+	return (link == 0 || (u64) link - 1 >= j) ? CH_STOP : link - 1;
+}
+
+template <bool ELASTIC> __global__ void __launch_bounds__(512) k3_chain_exit_kernel(const u32 *__restrict__ link, u64 ncols, u32 *__restrict__ E) {
+	extern __shared__ u32 ch_ex[];
+	const u64 s0 = (u64) blockIdx.x * CH_S;
+	const u32 len = (u32) (ncols - s0 < CH_S ? ncols - s0 : CH_S);
+	for (u32 i = threadIdx.x; i < len; i += blockDim.x) ch_ex[i] = chain_next<ELASTIC>(link[s0 + i], s0 + i);
+	__syncthreads();
+	for (;;) {
+		bool changed = false;
+		for (u32 i = threadIdx.x; i < len; i += blockDim.x) {
+			const u32 v = ch_ex[i];
+			if (v != CH_STOP && (u64) v >= s0) { ch_ex[i] = ch_ex[v - (u32) s0]; changed = true; } // old or new value: both lie on the chain
+		}
+		if (!__syncthreads_or(changed)) break;
+	}
+	for (u32 i = threadIdx.x; i < len; i += blockDim.x) E[s0 + i] = ch_ex[i];
+}
+
+// ent[seg] = where the chain enters the segment; out[1] = score, out[2] = status
+template <bool ELASTIC> __global__ void k3_chain_walk_kernel(const u32 *__restrict__ E, const u32 *__restrict__ val, u64 n, u32 *__restrict__ ent, u64 *out) {
+	if (blockIdx.x || threadIdx.x) return;
+	u64 cur = ELASTIC ? n : n - 1;
+	const u32 sc = val[cur];
+	out[1] = sc; out[2] = 0;
+	if (!ELASTIC && sc == (u32) n + 1) { out[2] = 1; return; } // no segmentation (fbg.cpp: the DP left its "infinity")
+	for (;;) {
+		ent[cur / CH_S] = (u32) cur;
+		const u32 e = __ldcg(E + cur);
+		if (e == CH_STOP) break;
+		cur = e;
+	}
+}
+
+template <bool ELASTIC> __global__ void __launch_bounds__(512) k3_chain_mark_kernel(const u32 *__restrict__ link, u64 ncols, const u32 *__restrict__ ent, u32 *__restrict__ mark) {
+	extern __shared__ u32 ch_ex[];
+	const u64 s0 = (u64) blockIdx.x * CH_S;
+	const u32 len = (u32) (ncols - s0 < CH_S ? ncols - s0 : CH_S);
+	const u32 en = ent[blockIdx.x];
+	if (en == U32_MAX) return; // the chain does not touch this segment (uniform)
+	for (u32 i = threadIdx.x; i < len; i += blockDim.x) ch_ex[i] = chain_next<ELASTIC>(link[s0 + i], s0 + i);
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		u32 j = en;
+		for (;;) {
+			mark[j] = 1u;
+			const u32 nx = ch_ex[j - (u32) s0];
+			if (nx == CH_STOP || (u64) nx < s0) break;
+			j = nx;
+		}
+	}
+}
+
+// pos = exclusive scan of mark; out[0] = number of boundaries
+template <bool ELASTIC> __global__ void k3_chain_emit_kernel(const u32 *__restrict__ mark, const u32 *__restrict__ pos, const u32 *__restrict__ total, u64 ncols, u64 n, u32 *__restrict__ bnd, u64 *out) {
+	const u64 j = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (j == 0) out[0] = *total;
+	if (j >= ncols || !mark[j]) return;
+	bnd[pos[j]] = ELASTIC ? (j == n ? (u32) n : (u32) j - 1) : (u32) j; // fbg.cpp:2026-2039: ends of the blocks, the last one = n
+}
+
+template <bool ELASTIC> static void dp_backtrack(Pipeline &p, const u32 *link, const u32 *val, u64 *out) {
+	Dev &d = p.dev;
+	const u64 n = p.n, ncols = ELASTIC ? n + 1 : n;
+	const u32 nseg = div_up(ncols, CH_S);
+	u32 *E = d.alloc<u32>(ncols + 1), *mark = d.alloc<u32>(ncols + 1), *ent = d.alloc<u32>(nseg + 1);
+	u32 *total = reinterpret_cast<u32 *>(p.scalars + 30);
+	FBG_CUDA(cudaMemsetAsync(mark, 0, (ncols + 1) * sizeof(u32), d.stream));
+	FBG_CUDA(cudaMemsetAsync(ent, 0xFF, ((u64) nseg + 1) * sizeof(u32), d.stream));
+	const size_t smem = (size_t) CH_S * sizeof(u32);
+	FBG_CUDA(cudaFuncSetAttribute(k3_chain_exit_kernel<ELASTIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+	FBG_CUDA(cudaFuncSetAttribute(k3_chain_mark_kernel<ELASTIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+	d.begin(K_DP);
+	k3_chain_exit_kernel<ELASTIC><<<nseg, 512, smem, d.stream>>>(link, ncols, E);
+	k3_chain_walk_kernel<ELASTIC><<<1, 32, 0, d.stream>>>(E, val, n, ent, out);
+	k3_chain_mark_kernel<ELASTIC><<<nseg, 512, smem, d.stream>>>(link, ncols, ent, mark);
+	FBG_LAUNCH_CHECK();
+	d.end((double) ncols * 16.0);
+	d.note_launches(K_DP, 2);
+	u32 *pos = E; // E is dead
+	device_scan<OpSumU32, true>(d, mark, pos, ncols, total);
+	d.begin(K_DP);
+	k3_chain_emit_kernel<ELASTIC><<<div_up(ncols, 256), 256, 0, d.stream>>>(mark, pos, total, ncols, n, p.bnd, out);
+	FBG_LAUNCH_CHECK();
+	d.end((double) ncols * 8.0);
 }
 
 // ------------------------------------------------------------ non-elastic
@@ -383,9 +485,9 @@ __global__ void __launch_bounds__(DPW * 32) k3_nonelastic_dp_kernel(const u32 *_
 }
 
 __global__ void __launch_bounds__(256) k3_nonelastic_verify_kernel(const u32 *__restrict__ v, u64 n, const u32 *__restrict__ gin, u32 *__restrict__ gout, u32 *__restrict__ prev,
-                                                                   u32 *__restrict__ changes) {
-	const u64 j = ((u64) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-	if (j >= n) return;
+                                                                   u32 *__restrict__ changes, u64 j0, u64 j1) {
+	const u64 j = (((u64) blockIdx.x * blockDim.x + threadIdx.x) >> 5) + j0; // columns [j0, j1) of 0..n-1
+	if (j >= j1) return;
 	u32 sj, pj;
 	nonelastic_scan(j, v[j], 0, [&](u64 x) { return gin[x]; }, sj, pj);
 	if (lane_id() == 0) {
@@ -525,14 +627,27 @@ static void dp_solve(Pipeline &p, bool elastic, const u32 *U_or_v, u32 *val, u32
 		d.note_launches(K_DP, 3);
 		if (debug) { dbg_guess.resize(ncols); FBG_CUDA(cudaMemcpyAsync(dbg_guess.data(), val, ncols * sizeof(u32), cudaMemcpyDeviceToHost, d.stream)); FBG_CUDA(cudaStreamSynchronize(d.stream)); dbgC = C; }
 		u32 *cur = val, *nxt = g2;
-		const u32 vgrid = div_up(ncols * 32, 256);
+		// the verify pass is one independent recomputation per column: every GPU takes a column range
+		const u64 jlo = elastic ? 1 : 0, jn = n;
+		u64 j0 = jlo, j1 = jlo + jn;
+		if (sharded) { plan_columns(jn, p.dist.world, p.dist.rank, &j0, &j1); j0 += jlo; j1 += jlo; }
+		const u32 vgrid = div_up((j1 - j0) * 32, 256);
 		for (int pass = 0; pass < 6; pass++) {
 			FBG_CUDA(cudaMemsetAsync(flags + 1, 0, sizeof(u32), d.stream));
+			if (sharded) {
+				FBG_CUDA(cudaMemsetAsync(nxt, 0, (ncols + 1) * sizeof(u32), d.stream));
+				FBG_CUDA(cudaMemsetAsync(ptr, 0, ncols * sizeof(u32), d.stream));
+			}
 			if (elastic) {
 				FBG_CUDA(cudaMemsetAsync(nxt, 0, sizeof(u32), d.stream)); // mml[0] = 0
-				k3_elastic_verify_kernel<<<vgrid, 256, 0, d.stream>>>(p.f, U_or_v, n, cur, nxt, ptr, flags + 1);
+				if (j1 > j0) k3_elastic_verify_kernel<<<vgrid, 256, 0, d.stream>>>(p.f, U_or_v, n, cur, nxt, ptr, flags + 1, j0, j1);
 			} else {
-				k3_nonelastic_verify_kernel<<<vgrid, 256, 0, d.stream>>>(U_or_v, n, cur, nxt, ptr, flags + 1);
+				if (j1 > j0) k3_nonelastic_verify_kernel<<<vgrid, 256, 0, d.stream>>>(U_or_v, n, cur, nxt, ptr, flags + 1, j0, j1);
+			}
+			if (sharded) {
+				p.dist.allreduce_max_u32(nxt, ncols, d.stream);
+				p.dist.allreduce_max_u32(ptr, ncols, d.stream);
+				p.dist.allreduce_max_u32(flags + 1, 1, d.stream); // "some GPU saw a change" is all the host asks
 			}
 			FBG_LAUNCH_CHECK();
 			FBG_CUDA(cudaMemcpyAsync(h_flags, flags, 2 * sizeof(u32), cudaMemcpyDeviceToHost, d.stream));
@@ -571,7 +686,7 @@ void k3_segment(Pipeline &p) {
 	const u64 n = p.n;
 	if (!p.bnd) p.bnd = p.dev.palloc<u32>(n + 2);
 	if (!p.dp_a) { p.dp_a = p.dev.palloc<u32>(n + 2); p.dp_b = p.dev.palloc<u32>(n + 2); p.dp_v = p.dev.palloc<u32>(n + 2); }
-	d.ensure((n + 2) * 12 + (n / 16 + 4) * 4 + (n / SCAN_TILE + 2) * 24 + (1u << 20));
+	d.ensure((n + 2) * 20 + (n / 16 + 4) * 4 + (n / CH_S + 4) * 4 + (n / SCAN_TILE + 2) * 24 + (1u << 20));
 	u64 mk = d.mark();
 	u32 *rev = d.alloc<u32>(n + 2);
 	u64 *out = p.scalars + 16;
@@ -587,11 +702,9 @@ void k3_segment(Pipeline &p) {
 		device_scan<OpMaxU32, false>(d, U, U, n + 1);
 		d.begin(K_DP);
 		dp_solve(p, true, U, p.dp_a, p.dp_b);
-		k3_elastic_chase_kernel<<<1, 32, 0, d.stream>>>(p.dp_b, p.dp_a, n, rev, out);
-		k3_reverse_kernel<<<NUM_SMS, 256, 0, d.stream>>>(rev, out, p.bnd);
 		FBG_LAUNCH_CHECK();
 		d.end((double) n * 24.0);
-		d.note_launches(K_DP, 2);
+		dp_backtrack<true>(p, p.dp_b, p.dp_a, out);
 	} else {
 		u32 *cnt = d.alloc<u32>(n + 2);
 		u32 *nonmono = reinterpret_cast<u32 *>(p.scalars + 24);
@@ -607,14 +720,17 @@ void k3_segment(Pipeline &p) {
 		k3_v_sequential_kernel<<<1, 32, 0, d.stream>>>(p.f, n, nonmono, p.dp_v);
 		if (p.opt.gap_limit == 1) {
 			dp_solve(p, false, p.dp_v, p.dp_a, p.dp_b);
-			k3_nonelastic_chase_kernel<<<1, 32, 0, d.stream>>>(p.dp_b, p.dp_a, n, rev, out);
+			FBG_LAUNCH_CHECK();
+			d.end((double) n * 24.0);
+			d.note_launches(K_DP, 2);
+			dp_backtrack<false>(p, p.dp_b, p.dp_a, out);
 		} else {
 			k3_greedy_dp_kernel<<<1, 32, 0, d.stream>>>(p.dp_v, n, p.dp_a, p.dp_b, rev, out);
+			k3_reverse_kernel<<<NUM_SMS, 256, 0, d.stream>>>(rev, out, p.bnd);
+			FBG_LAUNCH_CHECK();
+			d.end((double) n * 24.0);
+			d.note_launches(K_DP, 4);
 		}
-		k3_reverse_kernel<<<NUM_SMS, 256, 0, d.stream>>>(rev, out, p.bnd);
-		FBG_LAUNCH_CHECK();
-		d.end((double) n * 24.0);
-		d.note_launches(K_DP, 4);
 	}
 	FBG_CUDA(cudaMemcpyAsync(p.h_scalars + 16, out, 4 * sizeof(u64), cudaMemcpyDeviceToHost, d.stream));
 	FBG_CUDA(cudaStreamSynchronize(d.stream));
