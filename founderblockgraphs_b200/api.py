@@ -231,6 +231,10 @@ class Context:
 
     def compute_f(self) -> np.ndarray:
         self._check(self.lib.fbg_compute_f(self.h))
+        return self.get_f()
+
+    def get_f(self) -> np.ndarray:
+        """f of the last compute_f / run, read back from the device."""
         st = self.stats()
         out = np.zeros(st["n"], np.uint64)
         self._check(self.lib.fbg_get_f(self.h, out.ctypes.data_as(_u64p)))

@@ -214,14 +214,14 @@ int fbg_build_graph(fbg_ctx *ctx, int want_paths, fbg_graph *out) {
 		ctx->err = e.what(); cudaGetLastError(); delete h; return FBG_ERR_CUDA;
 	}
 	Graph &g = h->g;
-	out->n_blocks = g.heights.size(); out->n_nodes = g.node_block.size(); out->n_edges = g.edge_src.size();
+	out->n_blocks = g.n_heights; out->n_nodes = g.n_nodes; out->n_edges = g.n_edges;
 	out->n_rows = ctx->p.m; out->label_total = g.label_total;
 	u64 mh = 0;
-	for (u64 v : g.heights) mh = v > mh ? v : mh;
+	for (u64 i = 0; i < g.n_heights; i++) mh = g.heights[i] > mh ? g.heights[i] : mh;
 	out->max_height = mh;
-	out->block_height = g.heights.data(); out->node_block = g.node_block.data(); out->node_row = g.node_row.data();
-	out->edge_src = g.edge_src.data(); out->edge_dst = g.edge_dst.data();
-	out->node_of = g.node_of.empty() ? nullptr : g.node_of.data();
+	out->block_height = g.heights; out->node_block = g.node_block; out->node_row = g.node_row;
+	out->edge_src = g.edge_src; out->edge_dst = g.edge_dst;
+	out->node_of = g.n_node_of ? g.node_of : nullptr;
 	out->opaque = h;
 	return FBG_OK;
 }

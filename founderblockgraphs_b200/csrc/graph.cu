@@ -209,14 +209,12 @@ __global__ void k4_widen_kernel(const u32 *__restrict__ src, u64 *__restrict__ d
 	if (i < count) dst[i] = src[i];
 }
 
-// the C ABI hands out 64-bit arrays: widen on the device, one copy into the final vector
-static void d2h(std::vector<u64> &dst, const u32 *src, u64 count, u64 *wide, cudaStream_t s) {
-	dst.resize(count);
-	if (count) {
-		k4_widen_kernel<<<div_up(count, 256), 256, 0, s>>>(src, wide, count);
-		FBG_CUDA(cudaMemcpyAsync(dst.data(), wide, count * sizeof(u64), cudaMemcpyDeviceToHost, s));
-	}
-	FBG_CUDA(cudaStreamSynchronize(s));
+// the C ABI hands out 64-bit arrays: widen on the device, one copy into the page-locked block
+// (stream order keeps the staging buffer safe between two arrays; the caller synchronises once)
+static void d2h(u64 *dst, const u32 *src, u64 count, u64 *wide, cudaStream_t s) {
+	if (!count) return;
+	k4_widen_kernel<<<div_up(count, 256), 256, 0, s>>>(src, wide, count);
+	FBG_CUDA(cudaMemcpyAsync(dst, wide, count * sizeof(u64), cudaMemcpyDeviceToHost, s));
 }
 
 void k4_graph(Pipeline &p, Graph &g, bool want_node_of) {
@@ -281,17 +279,22 @@ void k4_graph(Pipeline &p, Graph &g, bool want_node_of) {
 	FBG_CUDA(cudaStreamSynchronize(d.stream));
 	u64 nn = *reinterpret_cast<u32 *>(p.h_scalars + 33), ne = *reinterpret_cast<u32 *>(p.h_scalars + 34);
 	g.label_total = p.h_scalars[35];
+	const u64 words = nb + 2 * nn + 2 * ne;
+	g.block = PinnedPool::get().take(words * sizeof(u64) + (want_node_of ? R * sizeof(u32) : 0) + 64);
+	u64 *hp = static_cast<u64 *>(g.block.ptr);
+	g.heights = hp; g.n_heights = nb; hp += nb;
+	g.node_block = hp; hp += nn;
+	g.node_row = hp; g.n_nodes = nn; hp += nn;
+	g.edge_src = hp; hp += ne;
+	g.edge_dst = hp; g.n_edges = ne; hp += ne;
+	g.node_of = want_node_of ? reinterpret_cast<u32 *>(hp) : nullptr; g.n_node_of = want_node_of ? R : 0;
 	d2h(g.heights, heights, nb, wide, d.stream);
 	d2h(g.node_block, node_block, nn, wide, d.stream);
 	d2h(g.node_row, node_row, nn, wide, d.stream);
 	d2h(g.edge_src, es, ne, wide, d.stream);
 	d2h(g.edge_dst, ed, ne, wide, d.stream);
-	g.node_of.clear();
-	if (want_node_of) {
-		g.node_of.resize(R);
-		if (R) FBG_CUDA(cudaMemcpyAsync(g.node_of.data(), node_of, R * sizeof(u32), cudaMemcpyDeviceToHost, d.stream));
-		FBG_CUDA(cudaStreamSynchronize(d.stream));
-	}
+	if (want_node_of && R) FBG_CUDA(cudaMemcpyAsync(g.node_of, node_of, R * sizeof(u32), cudaMemcpyDeviceToHost, d.stream));
+	FBG_CUDA(cudaStreamSynchronize(d.stream));
 	d.release(mk);
 }
 

@@ -14,6 +14,8 @@
 //   f      [n]   u32    minimal right extension
 //   bnd    [nb]  u32    inclusive block end columns (elastic: last = n)
 #pragma once
+#include <mutex>
+#include <vector>
 #include "prims.cuh"
 #include "dist.cuh"
 
@@ -29,14 +31,59 @@ struct Options {
 
 struct IgnoreSet { u32 bits[8]; };
 
+// Page-locked host blocks for the graph arrays handed out through the C ABI: the device
+// copies land in them at full PCIe speed, and a context that builds graph after graph gets the
+// same blocks back (fbg_graph_free returns them), so there is no cudaHostAlloc and no
+// first-touch page fault in steady state.  Process-wide because fbg_graph_free has no context.
+struct PinnedPool {
+	struct Block { void *ptr = nullptr; u64 bytes = 0; };
+	static constexpr size_t KEEP = 4; // free blocks kept for reuse
+	std::mutex mu;
+	std::vector<Block> free_blocks;
+	static PinnedPool &get() { static PinnedPool p; return p; }
+	Block take(u64 bytes) {
+		if (bytes == 0) bytes = 1;
+		{
+			std::lock_guard<std::mutex> lk(mu);
+			size_t best = free_blocks.size();
+			for (size_t i = 0; i < free_blocks.size(); i++)
+				if (free_blocks[i].bytes >= bytes && (best == free_blocks.size() || free_blocks[i].bytes < free_blocks[best].bytes)) best = i;
+			if (best != free_blocks.size()) { Block b = free_blocks[best]; free_blocks.erase(free_blocks.begin() + best); return b; }
+		}
+		Block b;
+		b.bytes = (bytes + (bytes >> 2) + 4095) & ~4095ull; // some slack: graphs of one workload differ a little in size
+		if (cudaHostAlloc(&b.ptr, b.bytes, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); throw cuda_error("cannot page-lock host memory for the graph arrays"); }
+		return b;
+	}
+	void give(Block b) {
+		if (!b.ptr) return;
+		Block drop;
+		{
+			std::lock_guard<std::mutex> lk(mu);
+			free_blocks.push_back(b);
+			if (free_blocks.size() > KEEP) { // let the smallest go
+				size_t s = 0;
+				for (size_t i = 1; i < free_blocks.size(); i++) if (free_blocks[i].bytes < free_blocks[s].bytes) s = i;
+				drop = free_blocks[s]; free_blocks.erase(free_blocks.begin() + s);
+			}
+		}
+		if (drop.ptr) cudaFreeHost(drop.ptr);
+	}
+};
+
 struct Graph {
-	// host-side result of K4
-	std::vector<u64> heights;    // per block
-	std::vector<u64> node_block; // per node
-	std::vector<u64> node_row;   // representative (first-occurrence) row
-	std::vector<u64> edge_src, edge_dst;
-	std::vector<u32> node_of;    // [nb][m], U32_MAX = empty label (only kept when requested)
+	// host-side result of K4: views into one page-locked block
+	PinnedPool::Block block;
+	u64 *heights = nullptr;     u64 n_heights = 0;  // per block
+	u64 *node_block = nullptr;  u64 n_nodes = 0;    // per node
+	u64 *node_row = nullptr;                        // representative (first-occurrence) row
+	u64 *edge_src = nullptr, *edge_dst = nullptr; u64 n_edges = 0;
+	u32 *node_of = nullptr;     u64 n_node_of = 0;  // [nb][m], U32_MAX = empty label (only kept when requested)
 	u64 label_total = 0;
+	Graph() = default;
+	Graph(const Graph &) = delete;
+	Graph &operator=(const Graph &) = delete;
+	~Graph() { PinnedPool::get().give(block); }
 };
 
 struct Pipeline {

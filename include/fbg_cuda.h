@@ -35,7 +35,10 @@ extern "C" {
 
 typedef struct fbg_ctx fbg_ctx;
 
-/* Result of fbg_build_graph; arrays are owned by the library until fbg_graph_free. */
+/* Result of fbg_build_graph; arrays are owned by the library until fbg_graph_free.  They live in
+ * one page-locked host block (the device copies run at full PCIe speed); fbg_graph_free hands the
+ * block back to a small process-wide pool, so a caller that builds graph after graph causes no
+ * page-locking and no first-touch page faults in steady state. */
 typedef struct fbg_graph {
 	uint64_t n_blocks, n_nodes, n_edges, n_rows;
 	uint64_t label_total;        /* "total length of node labels=" (fbg.cpp:695) */

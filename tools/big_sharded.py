@@ -52,7 +52,8 @@ def main():
         ctx.reset_stats()
         ctx.build_index()
         t_idx = time.perf_counter() - t
-        f = ctx.compute_f()
+        ctx._check(ctx.lib.fbg_compute_f(ctx.h))  # f stays on the device (it is an intermediate); read back for the checks below
+        torch.cuda.synchronize()
         t_f = time.perf_counter() - t
         b, score = ctx.segment()
         t_seg = time.perf_counter() - t
@@ -62,6 +63,7 @@ def main():
         t_all = time.perf_counter() - t
         times.append(dict(upload=t_up, index=t_idx - t_up, f=t_f - t_idx, segment=t_seg - t_f, graph=t_all - t_seg, total=t_all))
     st = ctx.stats()
+    f = ctx.get_f()
     # ---- properties
     bad = ctx.check_index(500_000, seed=11 + rank)
     x = np.arange(n, dtype=np.uint64)
