@@ -8,7 +8,9 @@
 //       after every doubling round the replicas are merged with an all-reduce(max):
 //       ranks only ever grow, and a rank array entry is written by its owner alone.
 //   K2  f(x) is sharded by contiguous column ranges and merged with the same all-reduce.
-//   K0, LCP, K3, K4 run replicated (O(N) streaming passes).
+//   K3  the chunk guesses and the verify passes of the DP are sharded by chunk / column range
+//       and merged the same way; plateau and backtrack run replicated.
+//   K0, LCP, K4 run replicated (O(N) streaming passes).
 // NCCL is loaded with dlopen so that the single-GPU library has no link-time dependency
 // on it; the few entry points used are declared here with NCCL's own ABI.
 #pragma once
