@@ -349,12 +349,16 @@ template <int CAP> struct TileCfg {
 	// windows up to 8192 slots also stage lr and lp in shared memory (one burst of asynchronous
 	// copies at the start, every later access at shared-memory latency)
 	static constexpr bool STAGE = CAP <= 8192;
-	static constexpr size_t SMEM = (size_t) CAP * 8 + ((size_t) CAP + 4) * 4 + (size_t) CAP * 2 + (STAGE ? ((size_t) CAP + 4) * 4 + (size_t) CAP * 4 : 0);
+	static constexpr size_t SMEM = (size_t) CAP * 8 + ((size_t) CAP + 4) * 4 + (size_t) CAP * 2 + (STAGE ? ((size_t) CAP + 8) * 4 + (size_t) CAP * 4 : 0);
 };
 
 __device__ __forceinline__ void cp_async4(void *smem_dst, const void *gsrc) {
 	const u32 d = (u32) __cvta_generic_to_shared(smem_dst);
 	asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc) {
+	const u32 d = (u32) __cvta_generic_to_shared(smem_dst);
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
 }
 __device__ __forceinline__ void cp_async_wait_all() {
 	asm volatile("cp.async.commit_group;" ::: "memory");
@@ -386,8 +390,8 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 	u32 *PXI = reinterpret_cast<u32 *>(k1_raw + (size_t) CAP * 8);
 	unsigned short *bend = reinterpret_cast<unsigned short *>(k1_raw + (size_t) CAP * 8 + ((size_t) CAP + 4) * 4);
 	constexpr bool STAGE = TileCfg<CAP>::STAGE;
-	u32 *lrs = reinterpret_cast<u32 *>(k1_raw + (size_t) CAP * 8 + ((size_t) CAP + 4) * 4 + (size_t) CAP * 2); // lrs[idx + 1] = lr of window element idx
-	u32 *lps = lrs + CAP + 4;
+	u32 *lrs = reinterpret_cast<u32 *>(k1_raw + (size_t) CAP * 8 + ((size_t) CAP + 4) * 4 + (size_t) CAP * 2); // lrs[idx + 4] = lr of window element idx
+	u32 *lps = lrs + CAP + 8;
 	__shared__ u32 s_first, s_end, s_wtot[32];
 	const u32 tid = threadIdx.x, w = tid >> 5, l = tid & 31;
 	const u64 w0 = (u64) blockIdx.x * tile;
@@ -410,12 +414,14 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 		}
 	}
 	if (STAGE) {
-#pragma unroll
-		for (int i = 0; i < ITEMS; i++) {
-			const u32 idx = i * THREADS + tid;
-			if (idx < wlen) { cp_async4(lrs + idx + 1, lr + w0 + idx); cp_async4(r2s + idx, r2 + w0 + idx); cp_async4(lps + idx, lp + w0 + idx); }
+		// the tile length is a multiple of four elements, so window and lists are 16-byte aligned
+		const u32 nq = wlen >> 2;
+		for (u32 q = tid; q < nq; q += THREADS) {
+			cp_async16(lrs + 4 + 4 * q, lr + w0 + 4 * q); cp_async16(r2s + 4 * q, r2 + w0 + 4 * q); cp_async16(lps + 4 * q, lp + w0 + 4 * q);
 		}
-		if (tid == 0 && w0 > 0) cp_async4(lrs, lr + w0 - 1);
+		const u32 idx = 4 * nq + tid;
+		if (idx < wlen) { cp_async4(lrs + 4 + idx, lr + w0 + idx); cp_async4(r2s + idx, r2 + w0 + idx); cp_async4(lps + idx, lp + w0 + idx); }
+		if (tid == 32 && w0 > 0) cp_async4(lrs + 3, lr + w0 - 1);
 		cp_async_wait_all();
 	}
 	__syncthreads();
@@ -427,7 +433,7 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 #pragma unroll
 	for (int i = 0; i < ITEMS; i++) {
 		const u32 idx = w * WCH + i * 32 + l;
-		st[i] = idx < wlen ? (STAGE ? lrs[idx + 1] : lr[w0 + idx]) : 0u;
+		st[i] = idx < wlen ? (STAGE ? lrs[idx + 4] : lr[w0 + idx]) : 0u;
 	}
 	if (!STAGE) {
 #pragma unroll
@@ -439,15 +445,19 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 	u32 hmask = 0;
 	u32 carry = 0, fmin = U32_MAX, emin = U32_MAX;
 	u32 pl = 0;
-	if (l == 0 && w * WCH < wlen && w0 + w * WCH > 0) pl = STAGE ? lrs[w * WCH] : lr[w0 + w * WCH - 1];
+	if (!STAGE && l == 0 && w * WCH < wlen && w0 + w * WCH > 0) pl = lr[w0 + w * WCH - 1];
 #pragma unroll
 	for (int i = 0; i < ITEMS; i++) {
 		const u32 base = w * WCH + i * 32;
 		const u32 idx = base + l;
 		const u32 v = st[i];
-		u32 pv = __shfl_up_sync(0xffffffffu, v, 1);
-		if (l == 0) pv = pl;
-		pl = __shfl_sync(0xffffffffu, v, 31);
+		u32 pv;
+		if (STAGE) pv = lrs[idx + 3]; // the element before (lrs[3] = the one before the window)
+		else {
+			pv = __shfl_up_sync(0xffffffffu, v, 1);
+			if (l == 0) pv = pl;
+			pl = __shfl_sync(0xffffffffu, v, 31);
+		}
 		const bool head = idx < wlen && (w0 + idx == 0 || pv != v);
 		const u32 hm = __ballot_sync(0xffffffffu, head);
 		hmask |= (head ? 1u : 0u) << i;
@@ -487,7 +497,7 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 			if (idx + 1 == endidx) last = true;
 			else if (l < 31) last = (hm >> (l + 1)) & 1u;
 			else if (i + 1 < ITEMS) last = hn & 1u;
-			else last = STAGE ? lrs[idx + 2] != lrs[idx + 1] : lr[w0 + idx + 1] != lr[w0 + idx];
+			else last = STAGE ? lrs[idx + 5] != lrs[idx + 4] : lr[w0 + idx + 1] != lr[w0 + idx];
 			if (last) bend[hb] = (unsigned short) (idx + 1);
 		}
 	}
@@ -547,7 +557,7 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 			pv4[c] = 0; rv4[c] = 0;
 			if ((u32) i * 32 < per && idx < endidx) {
 				if ((mmask >> i) & 1u) rv4[c] = r2[w0 + idx];
-				else if (STAGE) { pv4[c] = lps[idx]; rv4[c] = lrs[idx + 1]; }
+				else if (STAGE) { pv4[c] = lps[idx]; rv4[c] = lrs[idx + 4]; }
 				else { pv4[c] = lp[w0 + idx]; rv4[c] = lr[w0 + idx]; }
 			}
 		}
@@ -629,7 +639,7 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 			const u32 off = ((k >> (32 + LOGC)) & 1ull) ? neq : 0u;
 			const u32 out = hb + (s - pmh) + off;
 			const u32 hrel = (hs - pmh) + off;     // sub-bucket head, relative to the bucket head
-			const u32 nr = (STAGE ? lrs[hb + 1] : lr[w0 + hb]) + hrel;
+			const u32 nr = (STAGE ? lrs[hb + 4] : lr[w0 + hb]) + hrel;
 			const u32 p = STAGE ? lps[e] : lp[w0 + e];
 			const bool single = hs == s && last;
 			if (hrel) R[p] = nr;
@@ -646,7 +656,7 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 
 template <int CAP> static void launch_tile_sort(Dev &d, const u32 *lp, const u32 *lr, const u32 *r2, u64 na, u32 maxb,
                                                 u32 *R, u32 *SA, u32 *lp_out, u32 *lr_out, u8 *cls_out, u32 *scal) {
-	u32 tile = (u32) CAP - maxb;
+	u32 tile = ((u32) CAP - maxb) & ~3u; // a multiple of four: 16-byte aligned windows for the staging copies
 	const size_t smem = TileCfg<CAP>::SMEM;
 	FBG_CUDA(cudaFuncSetAttribute(k1_tile_sort_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
 	k1_tile_sort_kernel<CAP><<<div_up(na, tile), TileCfg<CAP>::THREADS, smem, d.stream>>>(lp, lr, r2, na, tile, R, SA, lp_out, lr_out, cls_out, scal);
