@@ -16,6 +16,12 @@
 #include "../../../include/fbg_cuda.h"
 #include <getopt.h>
 #include <chrono>
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <thread>
+#include <unistd.h>
+#include <utility>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -152,20 +158,34 @@ bool check_len(const std::string &identifier, size_t len, size_t expected) {
 	return false;
 }
 
+// fbg.cpp:151-201, same acceptance rules and messages; the file is mapped and every sequence
+// line is copied exactly once, straight into the row matrix (a rejected record is rolled back).
 bool read_input(const char *path, size_t gap_limit, bool elastic, bool output_paths, Msa &out) {
-	FILE *fp = fopen(path, "rb");
-	if (!fp) return false;
-	std::vector<char> data;
-	{
-		fseek(fp, 0, SEEK_END);
-		long sz = ftell(fp);
-		fseek(fp, 0, SEEK_SET);
-		if (sz < 0) { fclose(fp); return false; }
-		data.resize((size_t) sz);
-		if (sz && fread(data.data(), 1, (size_t) sz, fp) != (size_t) sz) { fclose(fp); return false; }
-		fclose(fp);
+	int fd = open(path, O_RDONLY);
+	if (fd < 0) return false;
+	struct stat sb;
+	if (fstat(fd, &sb) != 0) { close(fd); return false; }
+	size_t fsize = 0;
+	const char *base = nullptr;
+	bool mapped = false;
+	std::vector<char> piped; // pipes, process substitution: no mapping, read to the end
+	if (S_ISREG(sb.st_mode) && sb.st_size > 0) {
+		fsize = (size_t) sb.st_size;
+		void *mp = mmap(nullptr, fsize, PROT_READ, MAP_PRIVATE | MAP_POPULATE, fd, 0);
+		if (mp != MAP_FAILED) { madvise(mp, fsize, MADV_SEQUENTIAL); base = static_cast<const char *>(mp); mapped = true; }
 	}
-	const char *p = data.data(), *end = p + data.size();
+	if (!mapped) {
+		char buf[1 << 16];
+		for (;;) {
+			ssize_t got = read(fd, buf, sizeof buf);
+			if (got < 0) { close(fd); return false; }
+			if (got == 0) break;
+			piped.insert(piped.end(), buf, buf + got);
+		}
+		base = piped.data(); fsize = piped.size();
+	}
+	close(fd);
+	const char *p = base, *end = base + fsize;
 	auto next_line = [&](const char *&b, const char *&e) -> bool { // std::getline semantics
 		if (p >= end) return false;
 		b = p;
@@ -177,28 +197,29 @@ bool read_input(const char *path, size_t gap_limit, bool elastic, bool output_pa
 	std::string identifier;
 	if (next_line(b, e)) identifier.assign(b, e);
 	if (output_paths) out.identifiers.push_back(identifier.size() ? identifier.substr(1) : std::string());
-	std::vector<uint8_t> entry;
+	out.rows.reserve(fsize); // an upper bound: no reallocation while parsing
+	size_t row_start = out.rows.size();
 	size_t expected = 0;
 	bool is_first = true;
 	auto finish = [&]() {
-		if (is_first) { expected = entry.size(); is_first = false; }
-		if (check_len(identifier, entry.size(), expected) && (elastic || check_gaps(identifier, entry.data(), entry.size(), gap_limit))) {
-			out.rows.insert(out.rows.end(), entry.begin(), entry.end());
-			out.m++;
-		}
+		const size_t len = out.rows.size() - row_start;
+		if (is_first) { expected = len; is_first = false; }
+		if (check_len(identifier, len, expected) && (elastic || check_gaps(identifier, out.rows.data() + row_start, len, gap_limit))) out.m++;
+		else out.rows.resize(row_start);
+		row_start = out.rows.size();
 	};
 	while (next_line(b, e)) {
 		if (e > b && *b == '>') {
 			if (output_paths) out.identifiers.push_back(std::string(b + 1, e));
 			finish();
-			entry.clear();
 			identifier.assign(b, e);
 		} else {
-			entry.insert(entry.end(), (const uint8_t *) b, (const uint8_t *) e);
+			out.rows.insert(out.rows.end(), (const uint8_t *) b, (const uint8_t *) e);
 		}
 	}
 	finish();
 	out.n = expected;
+	if (mapped) munmap(const_cast<char *>(base), fsize);
 	return true;
 }
 
@@ -234,21 +255,37 @@ int main(int argc, char **argv) {
 	if (a.heuristic_subset != -1) { fprintf(stderr, "--heuristic-subset is not implemented in the GPU build.\n"); return EXIT_FAILURE; }
 
 	auto start = std::chrono::high_resolution_clock::now();
+	// FBG_TIMING=1: wall-clock per stage on stderr at the end (parse and write are host work)
+	const bool timing = getenv("FBG_TIMING") != nullptr;
+	std::vector<std::pair<const char *, double>> laps;
+	auto last = start;
+	auto lap = [&](const char *what) {
+		auto now = std::chrono::high_resolution_clock::now();
+		laps.emplace_back(what, std::chrono::duration<double, std::milli>(now - last).count());
+		last = now;
+	};
+	// the CUDA context takes a few hundred milliseconds to come up: create it while the FASTA is parsed
+	fbg_ctx *ctx = nullptr;
+	int ctx_rc = FBG_OK;
+	std::thread ctx_thread([&]() { ctx_rc = fbg_ctx_create(&ctx, -1); });
 	Msa msa;
 	bool opened = read_input(a.input.c_str(), (size_t) a.gap_limit, a.elastic, a.paths, msa);
-	if (!opened || msa.m == 0 || msa.n == 0) { fprintf(stderr, "Unable to read sequences from the input\n."); return EXIT_FAILURE; }
+	if (!opened || msa.m == 0 || msa.n == 0) { ctx_thread.join(); fprintf(stderr, "Unable to read sequences from the input\n."); return EXIT_FAILURE; }
 	fprintf(stderr, "Input MSA[1..%llu,1..%llu]\n", (unsigned long long) msa.m, (unsigned long long) msa.n);
 
-	if (a.elastic && !(a.threads == -1 || a.threads > 0)) { fprintf(stderr, "Invalid number of threads.\n"); return EXIT_FAILURE; }
+	if (a.elastic && !(a.threads == -1 || a.threads > 0)) { ctx_thread.join(); fprintf(stderr, "Invalid number of threads.\n"); return EXIT_FAILURE; }
 
-	fbg_ctx *ctx = nullptr;
-	if (fbg_ctx_create(&ctx, -1) != FBG_OK) return fail_cuda(nullptr, "cannot initialise the GPU");
+	lap("parse");
+	ctx_thread.join();
+	if (ctx_rc != FBG_OK) return fail_cuda(nullptr, "cannot initialise the GPU");
+	lap("GPU context (rest after the parse)");
 	if (fbg_set_options(ctx, a.elastic, a.gap_limit, (const uint8_t *) a.ignore.data(), a.ignore.size(), a.tricks_off) != FBG_OK) return fail_cuda(ctx, "options");
 	if (fbg_upload_msa(ctx, msa.rows.data(), msa.m, msa.n) != FBG_OK) return fail_cuda(ctx, "MSA upload");
 	fprintf(stderr, "Building the MSA index (suffix array, LCP) on the GPU.\n");
 	if (fbg_build_index(ctx) != FBG_OK) return fail_cuda(ctx, "index construction");
 	fbg_stats st;
 	fbg_get_stats(ctx, &st);
+	lap("upload + index");
 	fprintf(stderr, "MSA index construction complete, index requires %g MiB.\n", (double) st.text_len * 17.0 / (1024.0 * 1024.0));
 
 	uint64_t nb = 0, score = 0;
@@ -274,7 +311,9 @@ int main(int argc, char **argv) {
 	}
 	bnd.resize(nb);
 	if (fbg_get_boundaries(ctx, bnd.data()) != FBG_OK) return fail_cuda(ctx, "boundaries");
+	lap("f + segmentation");
 	if (fbg_build_graph(ctx, a.paths ? 1 : 0, &g) != FBG_OK) return fail_cuda(ctx, "graph construction");
+	lap("graph");
 
 	if (!a.elastic) {
 		fprintf(stderr, "#nodes=%llu\n", (unsigned long long) g.n_nodes);
@@ -301,8 +340,16 @@ int main(int argc, char **argv) {
 		fprintf(stderr, "ERROR: cannot write %s\n", a.output.c_str());
 		return EXIT_FAILURE;
 	}
+	lap("xGFA write");
 	fbg_graph_free(&g);
 	fbg_ctx_destroy(ctx);
+	lap("teardown");
+	if (timing) {
+		double tot = 0;
+		fprintf(stderr, "[fbg] stages (ms):");
+		for (auto &l : laps) { fprintf(stderr, " %s %.1f,", l.first, l.second); tot += l.second; }
+		fprintf(stderr, " total %.1f\n", tot);
+	}
 
 	auto end = std::chrono::high_resolution_clock::now();
 	auto secs = std::chrono::duration_cast<std::chrono::seconds>(end - start).count();
