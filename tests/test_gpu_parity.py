@@ -189,6 +189,34 @@ def test_cli_end_to_end_golden(tmp_path):
 
 
 # ------------------------------------------------------------------ oracle, seeded
+def test_xgfa_writer_threads_and_batches(gpu_ctx, tmp_path, monkeypatch):
+    """The writer formats blocks on several threads, batch after batch; its single-thread form is
+    pinned by the goldens, the threaded form must produce the same bytes."""
+    msa, c = synth.make_config("cfg3", 0.004)
+    gpu_ctx.set_options(elastic=True)
+    gpu_ctx.upload(msa)
+    gpu_ctx.build_index()
+    gpu_ctx.compute_f()
+    b, _ = gpu_ctx.segment()
+    gpu_ctx.build_graph(want_paths=True)
+    ids = [b"h%d" % i for i in range(msa.shape[0])]
+    outs = []
+    for threads, batch in (("1", None), ("7", None), ("3", "5000"), ("16", "1")):
+        monkeypatch.setenv("FBG_WRITER_THREADS", threads)
+        if batch is None:
+            monkeypatch.delenv("FBG_WRITER_BATCH", raising=False)
+        else:
+            monkeypatch.setenv("FBG_WRITER_BATCH", batch)
+        path = str(tmp_path / ("w%s_%s.xgfa" % (threads, batch)))
+        gpu_ctx.write_xgfa(path, msa, b, ids=ids)
+        outs.append(open(path, "rb").read())
+    assert len(outs[0]) > 1000 and all(o == outs[0] for o in outs[1:])
+    if not (msa == 45).all(axis=1).any():
+        ref = str(tmp_path / "oracle.xgfa")
+        O.write_xgfa(ref, msa, b, ids)
+        assert outs[0] == open(ref, "rb").read()
+
+
 def _check_elastic(ctx, msa, ignore=b"", tricks_off=False, tmp=None):
     ctx.set_options(elastic=True, ignore_chars=ignore, disable_tricks=tricks_off)
     ctx.upload(msa)
