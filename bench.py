@@ -255,7 +255,7 @@ def run_ours(args):
     sampler.stop_flag = True
     sampler.join()
     g = ctx._graph
-    d2h = int((g.n_blocks + 2 * g.n_nodes + 2 * g.n_edges) * 4 + 64)
+    d2h = int((g.n_blocks + 2 * g.n_nodes + 2 * g.n_edges) * 8 + 64)  # the C ABI hands out 64-bit arrays
     nb, score = e2e[-1][2], e2e[-1][3]
 
     t_dev = torch.tensor([sum(dev_secs), sum(x[1] for x in e2e)], dtype=torch.float64, device="cuda")
@@ -327,7 +327,11 @@ def run_ours(args):
                          "note": ROOFLINE_NOTES.get(dom, ""),
                          "other_hbm_kernels": {nm: round(((v["bytes"] / 1e9) / (v["ms"] / 1e3)) / peak, 4) for nm, v in ks.items() if v["ms"] > 0 and nm != dom},
                          "algorithmic_bytes_per_launch": k["bytes"] / max(1, k["launches"]), "launches": int(k["launches"]),
-                         "share_of_kernel_time": k["ms"] / total_ms if total_ms else None},
+                         "share_of_kernel_time": k["ms"] / total_ms if total_ms else None,
+                         # all algorithmic bytes of a step over the step's device time
+                         "pipeline": {"algorithmic_bytes_per_step": sum(v["bytes"] for v in ks.values()) / args.steps,
+                                      "achieved": (sum(v["bytes"] for v in ks.values()) / 1e9) / t_dev_total if t_dev_total > 0 else 0.0,
+                                      "frac": ((sum(v["bytes"] for v in ks.values()) / 1e9) / t_dev_total) / peak if t_dev_total > 0 else 0.0}},
             "kernels": {nm: {"ms_per_step": v["ms"] / args.steps, "GBps": ((v["bytes"] / 1e9) / (v["ms"] / 1e3)) if v["ms"] > 0 else 0.0,
                              "launches_per_step": v["launches"] / args.steps} for nm, v in ks.items()},
             "cpu_baseline": {"value": cb_v, "unit": UNIT, "cores": cb_cores, "kind": cb_kind, "sample": cb_sample, "seconds": cb_secs,
