@@ -41,37 +41,6 @@ __global__ void k3_scatter_u_kernel(const u32 *__restrict__ f, u64 n, u32 *__res
 constexpr u32 DP_RING = 4096;
 constexpr u32 DP_CH = 1024;
 
-// Walks a predecessor chain backwards through chunks staged in shared memory; every lane
-// follows the same chain, lane 0 records it.  STEP(b, j): false = stop, else sets the value
-// to record and the next j.
-template <class STEP> __device__ __forceinline__ u64 dp_chase(const u32 *link, u64 j, u64 nb, u32 *rev, u32 *stage, STEP step) {
-	const u32 l = lane_id();
-	__threadfence_block();
-	for (;;) {
-		u64 cb = j + 1 >= DP_CH ? j + 1 - DP_CH : 0;
-		__syncwarp();
-		for (u32 i0 = 0; i0 < DP_CH && cb + i0 <= j; i0 += 256) { // eight independent loads in flight per lane
-			u32 tmp[8];
-#pragma unroll
-			for (int q = 0; q < 8; q++) { u32 i = i0 + q * 32 + l; tmp[q] = cb + i <= j ? __ldcg(&link[cb + i]) : 0u; }
-#pragma unroll
-			for (int q = 0; q < 8; q++) stage[i0 + q * 32 + l] = tmp[q];
-		}
-		__syncwarp();
-		bool done = false;
-		for (;;) {
-			u32 rec; u64 nj;
-			if (!step(stage[j - cb], rec, nj)) { done = true; break; }
-			if (l == 0) rev[nb] = rec;
-			nb++;
-			j = nj;
-			if (j < cb) break;
-		}
-		if (done) break;
-	}
-	return nb;
-}
-
 // bnd[a] = rev[nb-1-a]; nb read from the device word the DP kernel left
 __global__ void k3_reverse_kernel(const u32 *__restrict__ rev, const u64 *__restrict__ out, u32 *__restrict__ bnd) {
 	u64 nb = out[0];
@@ -252,19 +221,6 @@ __global__ void k3_apply_plateau_kernel(u32 *__restrict__ g, u64 first, u64 n_co
 	u32 v = g[x], b = B[x / C];
 	bool ok = nonelastic ? v != (u32) x + 2 : v <= limit;
 	if (ok && b > v) g[x] = b;
-}
-
-// backtrack, fbg.cpp:2026-2039. out[0] = nb, out[1] = mml[n]
-__global__ void __launch_bounds__(32) k3_elastic_chase_kernel(const u32 *bt, const u32 *mml, u64 n, u32 *rev, u64 *out) {
-	__shared__ u32 stage[DP_CH];
-	const u32 l = lane_id();
-	if (l == 0) rev[0] = (u32) n;
-	u64 nb = dp_chase(bt, n, 1, rev, stage, [](u32 b, u32 &rec, u64 &nj) {
-		if (b == 0 || b == U32_MAX) return false;
-		rec = b - 1; nj = b;
-		return true;
-	});
-	if (l == 0) { out[0] = nb; out[1] = ld_vol(&mml[n]); }
 }
 
 // ---- backtrack in parallel
@@ -494,21 +450,6 @@ __global__ void __launch_bounds__(256) k3_nonelastic_verify_kernel(const u32 *__
 		gout[j] = sj; prev[j] = pj;
 		if (gin[j] != sj) atomicAdd(changes, 1u);
 	}
-}
-
-// out[0]=nb, out[1]=s[n-1], out[2]=status
-__global__ void __launch_bounds__(32) k3_nonelastic_chase_kernel(const u32 *prev, const u32 *s, u64 n, u32 *rev, u64 *out) {
-	__shared__ u32 stage[DP_CH];
-	const u32 l = lane_id();
-	u32 sc = ld_vol(&s[n - 1]);
-	if (sc == (u32) n + 1) { if (l == 0) { out[0] = 0; out[1] = sc; out[2] = 1; } return; }
-	if (l == 0) rev[0] = (u32) (n - 1);
-	u64 nb = dp_chase(prev, n - 1, 1, rev, stage, [](u32 pv, u32 &rec, u64 &nj) {
-		if (pv == 0) return false;
-		rec = pv - 1; nj = (u64) pv - 1;
-		return true;
-	});
-	if (l == 0) { out[0] = nb; out[1] = sc; out[2] = 0; }
 }
 
 // fbg.cpp:827-865 (greedy, not optimal by design); sequential by construction

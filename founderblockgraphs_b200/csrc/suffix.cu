@@ -945,7 +945,6 @@ void k1_suffix_array(Pipeline &p) {
 	int key_bits = key_bits0;
 	p.sa_rounds = 0;
 	const bool debug = getenv("FBG_DEBUG") != nullptr;
-	const u32 tile_ratio = getenv("FBG_TILE_RATIO") ? (u32) atoi(getenv("FBG_TILE_RATIO")) : 2u;
 	if (debug) fprintf(stderr, "[fbg] rank %d K1 round 0 %s\n", dist.rank, by_dict ? "through the k-mer dictionary" : "by sorting all suffixes");
 	p.kmer_dict = by_dict ? 1 : 0;
 	if (by_dict) {
@@ -965,9 +964,9 @@ void k1_suffix_array(Pipeline &p) {
 		// ---- S path
 		if (nS) {
 			d.begin(K_TILE_SORT);
-			if (tile_ratio * maxb <= 2048) launch_tile_sort<2048>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
-			else if (tile_ratio * maxb <= 4096) launch_tile_sort<4096>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
-			else if (tile_ratio * maxb <= 8192) launch_tile_sort<8192>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
+			if (2 * maxb <= 2048) launch_tile_sort<2048>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
+			else if (2 * maxb <= 4096) launch_tile_sort<4096>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
+			else if (2 * maxb <= 8192) launch_tile_sort<8192>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
 			else launch_tile_sort<16384>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
 			d.end((double) nS * (12.0 + 4.0 + 9.0));
 		}

@@ -402,3 +402,15 @@ def test_default_chunking_on_long_msa(gpu_ctx):
     assert gpu_ctx.stats()["dp_passes"] > 0  # proven by a verify pass, not by the whole-range fallback
     _check_nonelastic(gpu_ctx, synth.make_msa(50, 7000, snp=0.01, seed=9), 1)
     assert gpu_ctx.stats()["dp_passes"] > 0
+
+
+def test_backtrack_across_many_segments(gpu_ctx):
+    """The parallel backtrack cuts the columns into segments of 16384: chains that cross several of
+    them, elastic and non-elastic, against the oracle's sequential walk."""
+    _check_elastic(gpu_ctx, synth.make_msa(8, 60000, snp=0.02, gap_div=300, seed=21))
+    _check_nonelastic(gpu_ctx, synth.make_msa(10, 50000, snp=0.02, seed=22), 1)
+    # a chain of one-column hops: every segment is entered at its last column
+    rng = np.random.default_rng(23)
+    a = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, size=(4, 40000))]
+    _check_nonelastic(gpu_ctx, a, 1)
+
