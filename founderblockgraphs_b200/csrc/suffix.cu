@@ -219,6 +219,8 @@ __global__ void __launch_bounds__(256) k1_update_kernel(const u64 *__restrict__ 
 constexpr int CP_THREADS = 256;
 constexpr int CP_ITEMS = 16;
 constexpr int CP_TILE = CP_THREADS * CP_ITEMS;
+constexpr int CP_CHUNK = 4;      // items whose loads / look-ups / stores go out together in the write kernel
+constexpr int CP_MINB = 6;       // CTAs per SM the write kernel's registers are held to (it is bound by memory latency)
 
 // Round 0 lays the S list out by text position instead of by rank: buckets are ordered by
 // their smallest member, so neighbouring tiles hold neighbouring MSA columns and the rank
@@ -278,7 +280,7 @@ struct CompactOut {
 // the offsets this call appends at (same packing), or null for 0.  A warp owns 512
 // consecutive entries and walks them 32 at a time: coalesced reads, ballot/popc ranks,
 // compacted (hence nearly coalesced) writes.
-__global__ void __launch_bounds__(CP_THREADS) k1_cls_write_kernel(const u8 *__restrict__ cls, const u32 *__restrict__ lp, const u32 *__restrict__ lr, u64 na,
+__global__ void __launch_bounds__(CP_THREADS, CP_MINB) k1_cls_write_kernel(const u8 *__restrict__ cls, const u32 *__restrict__ lp, const u32 *__restrict__ lr, u64 na,
                                                                   const u64 *__restrict__ partial, const u64 *__restrict__ base, int skip_small,
                                                                   const u32 *__restrict__ R, u64 hnext, u64 N, int nbits, CompactOut o) {
 	__shared__ u64 wtot[CP_THREADS / 32];
@@ -301,25 +303,25 @@ __global__ void __launch_bounds__(CP_THREADS) k1_cls_write_kernel(const u8 *__re
 	u64 ex = partial[blockIdx.x] + (base ? *base : 0ull);
 	for (u32 ww = 0; ww < w; ww++) ex += wtot[ww];
 	u32 qs = (u32) ex, qb = (u32) (ex >> 32);
-	// pass 2, eight items at a time: their loads, then their rank look-ups, then the writes, each as
+	// pass 2, CP_CHUNK items at a time: their loads, then their rank look-ups, then the writes, each as
 	// one batch (the output arrays may alias the inputs as far as the compiler knows, so it would
 	// not reorder an item's loads over the stores of the item before)
 #pragma unroll
-	for (int i0 = 0; i0 < CP_ITEMS; i0 += 8) {
-		u32 pp[8], rr[8], r2[8];
+	for (int i0 = 0; i0 < CP_ITEMS; i0 += CP_CHUNK) {
+		u32 pp[CP_CHUNK], rr[CP_CHUNK], r2[CP_CHUNK];
 #pragma unroll
-		for (int k = 0; k < 8; k++) {
+		for (int k = 0; k < CP_CHUNK; k++) {
 			const u64 t = w0 + (u64) (i0 + k) * 32 + l;
 			pp[k] = 0; rr[k] = 0;
 			if (c[i0 + k] != CLS_DROP) { pp[k] = lp[t]; rr[k] = lr[t]; }
 		}
 #pragma unroll
-		for (int k = 0; k < 8; k++) {
+		for (int k = 0; k < CP_CHUNK; k++) {
 			const u64 q = (u64) pp[k] + hnext;
 			r2[k] = (c[i0 + k] != CLS_DROP && q < N) ? R[q] : 0u;
 		}
 #pragma unroll
-		for (int k = 0; k < 8; k++) {
+		for (int k = 0; k < CP_CHUNK; k++) {
 			const int i = i0 + k;
 			const u32 ms = __ballot_sync(0xffffffffu, c[i] == CLS_SMALL), mb = __ballot_sync(0xffffffffu, c[i] == CLS_BIG);
 			if (c[i] == CLS_SMALL) { const u32 d = qs + __popc(ms & lanemask_lt()); o.Slp[d] = pp[k]; o.Slr[d] = rr[k]; o.Sr2[d] = r2[k]; }
@@ -707,7 +709,7 @@ __global__ void k1_dict_counts_kernel(const u32 *__restrict__ lv, const u32 *__r
 }
 // info[slot] = (rank, start of the bucket in its list, size, smallest member); A = directory of the small buckets by text position
 __global__ void k1_dict_assign_kernel(const u32 *__restrict__ lv, const u32 *__restrict__ cnt, const u32 *__restrict__ first, const u32 *__restrict__ rk, const u32 *__restrict__ bs,
-                                      u32 nd, u32 rank_off, uint4 *__restrict__ info, u32 *__restrict__ A, u32 *__restrict__ maxb) {
+                                      u32 nd, u32 rank_off, uint4 *__restrict__ info, u32 *__restrict__ rank_of_slot, u32 *__restrict__ A, u32 *__restrict__ maxb) {
 	u32 t = blockIdx.x * blockDim.x + threadIdx.x;
 	u32 small = 0;
 	if (t < nd) {
@@ -715,6 +717,7 @@ __global__ void k1_dict_assign_kernel(const u32 *__restrict__ lv, const u32 *__r
 		if (c > BSMALL) start = bs[t];
 		else if (c > 1) { A[f] = c; small = c; }
 		info[s] = make_uint4(rank_off + rk[t], start, c, f);
+		rank_of_slot[s] = rank_off + rk[t];
 	}
 	small = warp_reduce_max(small);
 	if (lane_id() == 0 && small) atomicMax(maxb, small);
@@ -729,15 +732,15 @@ __global__ void k1_dict_fold_kernel(const u32 *__restrict__ lv, u32 nd, uint4 *_
 // what the sort-based round 0 leaves behind: ranks, SA entries of the suffixes alone in their
 // bucket, the S and B lists of the next round with R[p+h] looked up (through the table: no
 // rank has to be visible yet)
-__global__ void __launch_bounds__(256) k1_dict_emit_kernel(const u32 *__restrict__ slot_of, const u32 *__restrict__ ord_of, const uint4 *__restrict__ info, u64 N, u64 hnext, int nbits,
-                                                           u32 *__restrict__ R, u32 *__restrict__ SA, CompactOut o) {
+__global__ void __launch_bounds__(256) k1_dict_emit_kernel(const u32 *__restrict__ slot_of, const u32 *__restrict__ ord_of, const uint4 *__restrict__ info, const u32 *__restrict__ rank_of_slot,
+                                                           u64 N, u64 hnext, int nbits, u32 *__restrict__ R, u32 *__restrict__ SA, CompactOut o) {
 	u64 p = (u64) blockIdx.x * blockDim.x + threadIdx.x;
 	if (p >= N) return;
 	const uint4 v = __ldg(info + slot_of[p]);
 	R[p] = v.x;
 	if (v.z == 1) { SA[v.x] = (u32) p; return; }
 	const u64 pn = p + hnext;
-	const u32 r2 = pn < N ? __ldg(info + slot_of[pn]).x : 0u;
+	const u32 r2 = pn < N ? __ldg(rank_of_slot + slot_of[pn]) : 0u; // 4-byte entries: a quarter of the L2 traffic of info[]
 	const u32 q = v.y + ord_of[p];
 	if (v.z <= BSMALL) { o.Slp[q] = (u32) p; o.Slr[q] = v.x; o.Sr2[q] = r2; }
 	else { o.Bkey[q] = ((u64) v.x << nbits) | r2; o.Bval[q] = (u32) p; }
@@ -769,6 +772,7 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	dk.overflow = sc + 1;
 	uint4 *info = d.alloc<uint4>(cap);
 	u32 *pos = d.alloc<u32>(cap);
+	u32 *rank_of_slot = pos; // the occupancy scan is dead once the distinct k-mers are listed
 	RadixBuffers lb;
 	lb.k[0] = d.alloc<u64>(ndmax); lb.k[1] = d.alloc<u64>(ndmax);
 	lb.v[0] = d.alloc<u32>(ndmax); lb.v[1] = d.alloc<u32>(ndmax);
@@ -809,13 +813,13 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	device_scan<OpSumU32, true>(d, cbig, cbig, nd, sc + 3);
 	d.begin(K_DOUBLING_AUX);
 	FBG_CUDA(cudaMemsetAsync(A, 0, N * sizeof(u32), d.stream));
-	k1_dict_assign_kernel<<<gn, 256, 0, d.stream>>>(lv, dk.cnt, dk.first, call, cbig, nd, 0u, info, A, sc + 4);
+	k1_dict_assign_kernel<<<gn, 256, 0, d.stream>>>(lv, dk.cnt, dk.first, call, cbig, nd, 0u, info, rank_of_slot, A, sc + 4);
 	FBG_LAUNCH_CHECK();
 	d.end((double) nd * 40.0 + (double) N * 4.0);
 	device_scan<OpSumU32, true>(d, A, A, N, sc + 2);
 	d.begin(K_DOUBLING_AUX);
 	k1_dict_fold_kernel<<<gn, 256, 0, d.stream>>>(lv, nd, info, A);
-	k1_dict_emit_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, N, hnext, nbits, p.ISA, p.SA, o);
+	k1_dict_emit_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, p.ISA, p.SA, o);
 	FBG_LAUNCH_CHECK();
 	d.end((double) N * (8.0 + 4.0 + 4.0 + 12.0) + (double) nd * 24.0);
 	d.note_launches(K_DOUBLING_AUX, 1);
