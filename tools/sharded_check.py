@@ -54,6 +54,9 @@ def main():
         cases.append(("one symbol", np.full((3, 3000), ord("A"), np.uint8), True, b""))
         cases.append(("msa-like gapped N", synth.make_msa(60, 5000, snp=0.002, gap_div=500, n_div=2000, seed=11), True, b"N"))
         cases.append(("cfg2 twin", synth.make_msa(1000, 3000, snp=0.001, seed=2), False, b""))
+        # long inputs: many DP chunks per GPU (guess and verify are sharded) and several backtrack segments
+        cases.append(("long elastic", synth.make_msa(12, 40000, snp=0.02, gap_div=300, seed=21), True, b""))
+        cases.append(("long non-elastic", synth.make_msa(10, 30000, snp=0.02, seed=22), False, b""))
     ctx = pkg.Context(local)
     uid = [pkg.api.dist_unique_id() if rank == 0 else None]
     dist.broadcast_object_list(uid, src=0)
