@@ -22,7 +22,7 @@ CLI_PATH = os.path.join(_PKG, "founderblockgraph")
 
 FBG_OK, FBG_ERR_CUDA, FBG_ERR_ARG, FBG_ERR_NOSEG, FBG_ERR_UNSUPPORTED = 0, -1, -2, -3, -4
 FBG_NO_NODE = 0xFFFFFFFF
-N_KERNELS = 12
+N_KERNELS = 13
 
 _u8p = C.POINTER(C.c_uint8)
 _u32p = C.POINTER(C.c_uint32)
@@ -50,6 +50,7 @@ EXPORTS = [
     "fbg_graph_free", "fbg_run", "fbg_run_device", "fbg_get_stream", "fbg_get_stats", "fbg_reset_stats", "fbg_get_f", "fbg_get_text",
     "fbg_get_sa", "fbg_get_isa", "fbg_get_lcp", "fbg_get_dp", "fbg_radix_sort_pairs", "fbg_radix_sort_bench", "fbg_write_xgfa",
     "fbg_check_index", "fbg_set_dp_chunking", "fbg_dist_unique_id", "fbg_dist_init", "fbg_dist_shutdown", "fbg_plan_key_ranges", "fbg_plan_columns",
+    "fbg_format_xgfa", "fbg_read_xgfa", "fbg_save_xgfa",
 ]
 
 _lib = None
@@ -105,6 +106,9 @@ def load_library():
     lib.fbg_radix_sort_pairs.argtypes = [C.c_void_p, _u64p, _u32p, C.c_uint64, C.c_int, C.c_int]
     lib.fbg_radix_sort_bench.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double)]
     lib.fbg_write_xgfa.argtypes = [C.c_char_p, C.c_void_p, C.c_uint64, C.c_uint64, _u64p, C.POINTER(FbgGraph), C.c_int, C.POINTER(C.c_char_p)]
+    lib.fbg_format_xgfa.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(FbgGraph), _u64p]
+    lib.fbg_read_xgfa.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p]
+    lib.fbg_save_xgfa.argtypes = [C.c_void_p, C.c_char_p]
     lib.fbg_set_dp_chunking.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64]
     lib.fbg_check_index.argtypes = [C.c_void_p, C.c_uint32, C.c_uint64, _u32p]
     lib.fbg_dist_unique_id.argtypes = [_u8p]
@@ -281,6 +285,31 @@ class Context:
         if rc != FBG_OK:
             raise FbgError(rc, "cannot write " + path)
 
+    def format_xgfa(self, ids=None) -> dict:
+        """K4 + K5: graph and xGFA bytes formatted on the device (nothing but counts comes back)."""
+        g = FbgGraph()
+        nbytes = C.c_uint64()
+        arr = (C.c_char_p * len(ids))(*[bytes(i) for i in ids]) if ids is not None else None
+        self._check(self.lib.fbg_format_xgfa(self.h, int(ids is not None), arr, C.byref(g), C.byref(nbytes)))
+        self._xgfa_len = nbytes.value
+        return dict(n_blocks=g.n_blocks, n_nodes=g.n_nodes, n_edges=g.n_edges, label_total=g.label_total,
+                    max_height=g.max_height, n_bytes=nbytes.value)
+
+    def read_xgfa(self, offset: int = 0, length: int | None = None) -> bytes:
+        """Bytes [offset, offset + length) of the xGFA formatted by format_xgfa."""
+        if length is None:
+            length = self._xgfa_len - offset
+        buf = np.zeros(max(length, 1), np.uint8)
+        self._check(self.lib.fbg_read_xgfa(self.h, offset, length, buf.ctypes.data))
+        return buf[:length].tobytes()
+
+    def xgfa_bytes(self, ids=None) -> bytes:
+        info = self.format_xgfa(ids)
+        return self.read_xgfa(0, info["n_bytes"])
+
+    def save_xgfa(self, path: str):
+        self._check(self.lib.fbg_save_xgfa(self.h, path.encode()))
+
     def stream_ptr(self) -> int:
         return int(self.lib.fbg_get_stream(self.h) or 0)
 
@@ -426,10 +455,16 @@ def segment2elasticValid(msa: np.ndarray, gap_limit: int = 0, ctx: Context | Non
     return b, score, g
 
 
-def output_efg(boundaries, msa: np.ndarray, output_paths: bool, identifiers, dst_path: str, ctx: Context):
-    """output_efg (fbg.cpp:1185-1301) for the segmentation held by ctx."""
-    ctx.build_graph(want_paths=output_paths)
-    ctx.write_xgfa(dst_path, msa, boundaries, identifiers if output_paths else None)
+def output_efg(boundaries, msa: np.ndarray, output_paths: bool, identifiers, dst_path: str, ctx: Context, host_writer: bool = False):
+    """output_efg (fbg.cpp:1185-1301) for the segmentation held by ctx: formatted on the device
+    (K5) and streamed to dst_path, or -- host_writer -- graph arrays copied out and formatted by
+    the host writer.  Same bytes."""
+    if host_writer:
+        ctx.build_graph(want_paths=output_paths)
+        ctx.write_xgfa(dst_path, msa, boundaries, identifiers if output_paths else None)
+    else:
+        ctx.format_xgfa(identifiers if output_paths else None)
+        ctx.save_xgfa(dst_path)
 
 
 def main(argv, **kw):

@@ -1,6 +1,8 @@
 // capi.cu -- the extern "C" surface declared in include/fbg_cuda.h.
 #include "../../include/fbg_cuda.h"
 #include "pipeline.cuh"
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -42,12 +44,12 @@ void Pipeline::free_all() {
 	T = nullptr; msa = nullptr;
 	col = ISA = SA = PLCP = f = bnd = dp_a = dp_b = dp_v = nullptr;
 	dev.pers_top = 0;
-	have_msa = have_index = have_f = have_seg = false;
+	have_msa = have_index = have_f = have_seg = have_xgfa = false;
 }
 
 } // namespace fbg
 
-static const char *KNAMES[K_COUNT] = {"pack", "kmer", "radix_hist", "radix_scatter", "scan", "doubling_aux", "lcp", "fcol", "dp", "graph", "tile_sort", "comm"};
+static const char *KNAMES[K_COUNT] = {"pack", "kmer", "radix_hist", "radix_scatter", "scan", "doubling_aux", "lcp", "fcol", "dp", "graph", "tile_sort", "comm", "emit"};
 
 #define FBG_TRY(ctx) try {
 #define FBG_CATCH(ctx)                                                         \
@@ -99,6 +101,7 @@ void fbg_ctx_destroy(fbg_ctx *ctx) {
 	ctx->p.free_all();
 	if (ctx->p.scalars) cudaFree(ctx->p.scalars);
 	if (ctx->p.h_scalars) cudaFreeHost(ctx->p.h_scalars);
+	if (ctx->p.xgfa) cudaFree(ctx->p.xgfa);
 	ctx->p.dev.destroy();
 	if (ctx->p.dev.stream) cudaStreamDestroy(ctx->p.dev.stream);
 	delete ctx;
@@ -116,7 +119,7 @@ int fbg_set_options(fbg_ctx *ctx, int elastic, int64_t gap_limit, const uint8_t 
 	// ignore characters only take part in the elastic path (fbg.cpp:3393)
 	if (elastic && ignore_chars)
 		for (size_t i = 0; i < n_ignore; i++) { u8 c = ignore_chars[i]; o.ignore_bits[c >> 5] |= 1u << (c & 31); o.n_ignore++; }
-	ctx->p.have_f = ctx->p.have_seg = false;
+	ctx->p.have_f = ctx->p.have_seg = ctx->p.have_xgfa = false;
 	return FBG_OK;
 }
 
@@ -125,6 +128,7 @@ static int upload_common(fbg_ctx *ctx, const void *rows, uint64_t m, uint64_t n,
 	if (m >= (1u << 24)) { ctx->err = "more than 2^24 rows"; return FBG_ERR_UNSUPPORTED; }
 	FBG_TRY(ctx)
 	FBG_CUDA(cudaSetDevice(ctx->p.dev.device));
+	ctx->p.have_xgfa = false;
 	if (device) k0_upload_device(ctx->p, (const u8 *) rows, m, n);
 	else k0_upload_host(ctx->p, (const u8 *) rows, m, n);
 	FBG_CATCH(ctx)
@@ -209,7 +213,7 @@ int fbg_build_graph(fbg_ctx *ctx, int want_paths, fbg_graph *out) {
 	std::memset(out, 0, sizeof *out);
 	GraphHolder *h = new GraphHolder();
 	try {
-		k4_graph(ctx->p, h->g, want_paths != 0);
+		k4_graph(ctx->p, &h->g, want_paths != 0);
 	} catch (const std::exception &e) {
 		ctx->err = e.what(); cudaGetLastError(); delete h; return FBG_ERR_CUDA;
 	}
@@ -224,6 +228,85 @@ int fbg_build_graph(fbg_ctx *ctx, int want_paths, fbg_graph *out) {
 	out->node_of = g.n_node_of ? g.node_of : nullptr;
 	out->opaque = h;
 	return FBG_OK;
+}
+
+// K4 + K5 without a host copy of the graph arrays
+int fbg_format_xgfa(fbg_ctx *ctx, int output_paths, const char *const *ids, fbg_graph *counts, uint64_t *n_bytes) {
+	if (!ctx || !ctx->p.have_seg || ctx->p.seg_status) { if (ctx) ctx->err = "no segmentation available"; return FBG_ERR_ARG; }
+	if (output_paths && !ids) { ctx->err = "output_paths needs the sequence headers"; return FBG_ERR_ARG; }
+	if (counts) std::memset(counts, 0, sizeof *counts);
+	FBG_TRY(ctx)
+	Pipeline &p = ctx->p;
+	FBG_CUDA(cudaSetDevice(p.dev.device));
+	p.have_xgfa = false;
+	XgfaJob x;
+	x.paths = output_paths != 0; x.ids = ids;
+	k4_graph(p, nullptr, false, &x);
+	if (counts) {
+		counts->n_blocks = p.nb; counts->n_nodes = x.n_nodes; counts->n_edges = x.n_edges; counts->n_rows = p.m;
+		counts->label_total = x.label_total; counts->max_height = x.max_height;
+	}
+	if (n_bytes) *n_bytes = x.n_bytes;
+	p.dev.resolve();
+	FBG_CATCH(ctx)
+	return FBG_OK;
+}
+
+int fbg_read_xgfa(fbg_ctx *ctx, uint64_t offset, uint64_t len, uint8_t *dst) {
+	if (!ctx || !ctx->p.have_xgfa || (len && !dst) || offset > ctx->p.xgfa_len || len > ctx->p.xgfa_len - offset) {
+		if (ctx) ctx->err = ctx->p.have_xgfa ? "range outside the formatted xGFA" : "no formatted xGFA (call fbg_format_xgfa)";
+		return FBG_ERR_ARG;
+	}
+	FBG_TRY(ctx)
+	Pipeline &p = ctx->p;
+	FBG_CUDA(cudaSetDevice(p.dev.device));
+	if (len) FBG_CUDA(cudaMemcpyAsync(dst, p.xgfa + offset, len, cudaMemcpyDeviceToHost, p.dev.stream));
+	FBG_CUDA(cudaStreamSynchronize(p.dev.stream));
+	FBG_CATCH(ctx)
+	return FBG_OK;
+}
+
+// device bytes -> file through two page-locked staging buffers: the copy of chunk k+1 runs
+// while chunk k is handed to write()
+int fbg_save_xgfa(fbg_ctx *ctx, const char *path) {
+	if (!ctx || !path || !ctx->p.have_xgfa) { if (ctx) ctx->err = "no formatted xGFA (call fbg_format_xgfa)"; return FBG_ERR_ARG; }
+	FILE *fp = fopen(path, "wb");
+	if (!fp) { ctx->err = std::string("cannot open ") + path; return FBG_ERR_ARG; }
+	setvbuf(fp, nullptr, _IONBF, 0);
+	u64 chunk = 8u << 20;
+	if (const char *e = getenv("FBG_SAVE_CHUNK")) { long long v = atoll(e); if (v >= 1) chunk = (u64) v; } // test hook
+	PinnedPool::Block blk;
+	cudaEvent_t ev[2] = {nullptr, nullptr};
+	int rc = FBG_OK;
+	try {
+		Pipeline &p = ctx->p;
+		FBG_CUDA(cudaSetDevice(p.dev.device));
+		blk = PinnedPool::get().take(2 * chunk);
+		u8 *buf[2] = {static_cast<u8 *>(blk.ptr), static_cast<u8 *>(blk.ptr) + chunk};
+		FBG_CUDA(cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming));
+		FBG_CUDA(cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming));
+		const u64 total = p.xgfa_len, nchunks = (total + chunk - 1) / chunk;
+		auto issue = [&](u64 k) {
+			const u64 off = k * chunk, len = total - off < chunk ? total - off : chunk;
+			FBG_CUDA(cudaMemcpyAsync(buf[k & 1], p.xgfa + off, len, cudaMemcpyDeviceToHost, p.dev.stream));
+			FBG_CUDA(cudaEventRecord(ev[k & 1], p.dev.stream));
+		};
+		if (nchunks) issue(0);
+		for (u64 k = 0; k < nchunks; k++) {
+			if (k + 1 < nchunks) issue(k + 1); // into the buffer written out in the iteration before
+			FBG_CUDA(cudaEventSynchronize(ev[k & 1]));
+			const u64 off = k * chunk, len = total - off < chunk ? total - off : chunk;
+			if (fwrite(buf[k & 1], 1, len, fp) != len) { ctx->err = std::string("cannot write ") + path; rc = FBG_ERR_ARG; break; }
+		}
+		FBG_CUDA(cudaStreamSynchronize(p.dev.stream));
+	} catch (const std::exception &e) {
+		ctx->err = e.what(); cudaGetLastError(); rc = FBG_ERR_CUDA;
+	}
+	if (ev[0]) cudaEventDestroy(ev[0]);
+	if (ev[1]) cudaEventDestroy(ev[1]);
+	PinnedPool::get().give(blk);
+	if (fclose(fp) != 0 && rc == FBG_OK) { ctx->err = std::string("cannot write ") + path; rc = FBG_ERR_ARG; }
+	return rc;
 }
 
 void fbg_graph_free(fbg_graph *g) {

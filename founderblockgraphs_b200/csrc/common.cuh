@@ -49,6 +49,7 @@ enum KernelId {
 	K_GRAPH,         // K4: label hash / dedup / edges
 	K_TILE_SORT,     // K1: bucket-local shared-memory sort of tied suffixes
 	K_COMM,          // NCCL collectives of a multi-GPU build (rank replicas, f)
+	K_EMIT,          // K5: xGFA formatting (item lengths, offsets, byte writes)
 	K_COUNT
 };
 

@@ -15,6 +15,7 @@
 //      emitted in ascending (src,dst) order like std::set<pair>
 #include "pipeline.cuh"
 #include "blocksort.cuh"
+#include <cstring>
 
 namespace fbg {
 
@@ -217,13 +218,15 @@ static void d2h(u64 *dst, const u32 *src, u64 count, u64 *wide, cudaStream_t s) 
 	FBG_CUDA(cudaMemcpyAsync(dst, wide, count * sizeof(u64), cudaMemcpyDeviceToHost, s));
 }
 
-void k4_graph(Pipeline &p, Graph &g, bool want_node_of) {
+void k4_graph(Pipeline &p, Graph *gp, bool want_node_of, XgfaJob *x) {
 	Dev &d = p.dev;
 	const u64 m = p.m, nb = p.nb, R = m * nb;
 	if (R >= 0xFFFFFFF0ull) throw cuda_error("more than 2^32 (row,block) records");
 	GroupCfg gc = group_cfg(m);
 	if (gc.mpad > 8192) throw cuda_error("more than 8192 rows is not supported by the shared-memory dedup kernel yet");
-	d.ensure(R * 72 + (nb + 1) * 12 + (R / SCAN_TILE + 2) * 24 + (4u << 20));
+	u64 id_bytes = 0;
+	if (x && x->paths) for (u64 i = 0; i < m; i++) id_bytes += strlen(x->ids[i]);
+	d.ensure(R * 72 + (nb + 1) * 12 + (R / SCAN_TILE + 2) * 24 + (4u << 20) + (x ? k5_scratch_need(m, nb, x->paths, id_bytes) : 0));
 	u64 mk = d.mark();
 	u64 *H1 = d.alloc<u64>(R), *H2 = d.alloc<u64>(R);
 	u32 *LEN = d.alloc<u32>(R), *POS = d.alloc<u32>(R), *REP = d.alloc<u32>(R), *HEAD = d.alloc<u32>(R), *NIDX = d.alloc<u32>(R);
@@ -278,23 +281,34 @@ void k4_graph(Pipeline &p, Graph &g, bool want_node_of) {
 	FBG_CUDA(cudaMemcpyAsync(p.h_scalars + 32, p.scalars + 32, 8 * sizeof(u64), cudaMemcpyDeviceToHost, d.stream));
 	FBG_CUDA(cudaStreamSynchronize(d.stream));
 	u64 nn = *reinterpret_cast<u32 *>(p.h_scalars + 33), ne = *reinterpret_cast<u32 *>(p.h_scalars + 34);
-	g.label_total = p.h_scalars[35];
-	const u64 words = nb + 2 * nn + 2 * ne;
-	g.block = PinnedPool::get().take(words * sizeof(u64) + (want_node_of ? R * sizeof(u32) : 0) + 64);
-	u64 *hp = static_cast<u64 *>(g.block.ptr);
-	g.heights = hp; g.n_heights = nb; hp += nb;
-	g.node_block = hp; hp += nn;
-	g.node_row = hp; g.n_nodes = nn; hp += nn;
-	g.edge_src = hp; hp += ne;
-	g.edge_dst = hp; g.n_edges = ne; hp += ne;
-	g.node_of = want_node_of ? reinterpret_cast<u32 *>(hp) : nullptr; g.n_node_of = want_node_of ? R : 0;
-	d2h(g.heights, heights, nb, wide, d.stream);
-	d2h(g.node_block, node_block, nn, wide, d.stream);
-	d2h(g.node_row, node_row, nn, wide, d.stream);
-	d2h(g.edge_src, es, ne, wide, d.stream);
-	d2h(g.edge_dst, ed, ne, wide, d.stream);
-	if (want_node_of && R) FBG_CUDA(cudaMemcpyAsync(g.node_of, node_of, R * sizeof(u32), cudaMemcpyDeviceToHost, d.stream));
-	FBG_CUDA(cudaStreamSynchronize(d.stream));
+	const u64 label_sum = p.h_scalars[35];
+	if (gp) {
+		Graph &g = *gp;
+		g.label_total = label_sum;
+		const u64 words = nb + 2 * nn + 2 * ne;
+		g.block = PinnedPool::get().take(words * sizeof(u64) + (want_node_of ? R * sizeof(u32) : 0) + 64);
+		u64 *hp = static_cast<u64 *>(g.block.ptr);
+		g.heights = hp; g.n_heights = nb; hp += nb;
+		g.node_block = hp; hp += nn;
+		g.node_row = hp; g.n_nodes = nn; hp += nn;
+		g.edge_src = hp; hp += ne;
+		g.edge_dst = hp; g.n_edges = ne; hp += ne;
+		g.node_of = want_node_of ? reinterpret_cast<u32 *>(hp) : nullptr; g.n_node_of = want_node_of ? R : 0;
+		d2h(g.heights, heights, nb, wide, d.stream);
+		d2h(g.node_block, node_block, nn, wide, d.stream);
+		d2h(g.node_row, node_row, nn, wide, d.stream);
+		d2h(g.edge_src, es, ne, wide, d.stream);
+		d2h(g.edge_dst, ed, ne, wide, d.stream);
+		if (want_node_of && R) FBG_CUDA(cudaMemcpyAsync(g.node_of, node_of, R * sizeof(u32), cudaMemcpyDeviceToHost, d.stream));
+		FBG_CUDA(cudaStreamSynchronize(d.stream));
+	}
+	if (x) {
+		GraphDev gd;
+		gd.m = m; gd.nb = nb; gd.nn = nn; gd.ne = ne;
+		gd.heights = heights; gd.node_block = node_block; gd.node_row = node_row; gd.es = es; gd.ed = ed;
+		gd.EOFF = EOFF; gd.node_of = node_of; gd.LEN = LEN; gd.POS = POS; gd.label_total = label_sum;
+		k5_emit_xgfa(p, gd, *x);
+	}
 	d.release(mk);
 }
 

@@ -312,8 +312,19 @@ int main(int argc, char **argv) {
 	bnd.resize(nb);
 	if (fbg_get_boundaries(ctx, bnd.data()) != FBG_OK) return fail_cuda(ctx, "boundaries");
 	lap("f + segmentation");
-	if (fbg_build_graph(ctx, a.paths ? 1 : 0, &g) != FBG_OK) return fail_cuda(ctx, "graph construction");
-	lap("graph");
+	// Graph and xGFA bytes: formatted on the device and streamed to the file (K5, default), or --
+	// FBG_HOST_WRITER=1 -- graph arrays copied out and formatted by the host writer.  Same bytes.
+	const bool host_writer = getenv("FBG_HOST_WRITER") != nullptr;
+	const bool ids_bad = a.paths && msa.identifiers.size() != msa.m; // the reference asserts at the end of output_efg (fbg.cpp:1292)
+	std::vector<const char *> ids;
+	if (a.paths && !ids_bad) for (auto &s : msa.identifiers) ids.push_back(s.c_str());
+	uint64_t xgfa_bytes = 0;
+	if (host_writer) {
+		if (fbg_build_graph(ctx, a.paths ? 1 : 0, &g) != FBG_OK) return fail_cuda(ctx, "graph construction");
+	} else if (!ids_bad) {
+		if (fbg_format_xgfa(ctx, a.paths ? 1 : 0, a.paths ? ids.data() : nullptr, &g, &xgfa_bytes) != FBG_OK) return fail_cuda(ctx, "graph construction");
+	}
+	lap(host_writer ? "graph" : "graph + xGFA bytes");
 
 	if (!a.elastic) {
 		fprintf(stderr, "#nodes=%llu\n", (unsigned long long) g.n_nodes);
@@ -328,15 +339,13 @@ int main(int argc, char **argv) {
 		}
 	}
 	fprintf(stderr, "Writing the xGFA to disk\xE2\x80\xA6\n");
-	std::vector<const char *> ids;
-	if (a.paths) {
-		if (msa.identifiers.size() != msa.m) { // the reference asserts here (fbg.cpp:1292)
-			fprintf(stderr, "founderblockgraph: identifiers.size() == paths.size() failed (rows were skipped while reading; fbg.cpp:1292)\n");
-			return 134;
-		}
-		for (auto &s : msa.identifiers) ids.push_back(s.c_str());
+	if (ids_bad) {
+		fprintf(stderr, "founderblockgraph: identifiers.size() == paths.size() failed (rows were skipped while reading; fbg.cpp:1292)\n");
+		return 134;
 	}
-	if (fbg_write_xgfa(a.output.c_str(), msa.rows.data(), msa.m, msa.n, bnd.data(), &g, a.paths ? 1 : 0, a.paths ? ids.data() : nullptr) != FBG_OK) {
+	const int wrc = host_writer ? fbg_write_xgfa(a.output.c_str(), msa.rows.data(), msa.m, msa.n, bnd.data(), &g, a.paths ? 1 : 0, a.paths ? ids.data() : nullptr)
+	                            : fbg_save_xgfa(ctx, a.output.c_str());
+	if (wrc != FBG_OK) {
 		fprintf(stderr, "ERROR: cannot write %s\n", a.output.c_str());
 		return EXIT_FAILURE;
 	}

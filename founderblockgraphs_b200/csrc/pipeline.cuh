@@ -13,6 +13,7 @@
 //   PLCP   [N]   u32    LCP[ISA[p]]      (text order)
 //   f      [n]   u32    minimal right extension
 //   bnd    [nb]  u32    inclusive block end columns (elastic: last = n)
+//   xgfa   bytes        the formatted graph (K5), only when asked for
 #pragma once
 #include <mutex>
 #include <vector>
@@ -86,6 +87,27 @@ struct Graph {
 	~Graph() { PinnedPool::get().give(block); }
 };
 
+// device-side view of the K4 result while it is still in the scratch arena (input of K5)
+struct GraphDev {
+	u64 m = 0, nb = 0, nn = 0, ne = 0;
+	const u32 *heights = nullptr;    // [nb+1], heights[nb] = 0
+	const u32 *node_block = nullptr, *node_row = nullptr; // [nn]
+	const u32 *es = nullptr, *ed = nullptr;               // [ne], grouped by destination block
+	const u32 *EOFF = nullptr;       // [nb] edges arriving in the blocks before j
+	const u32 *node_of = nullptr;    // [nb][m]
+	const u32 *LEN = nullptr, *POS = nullptr;             // [nb][m] label length / text position
+	u64 label_total = 0;
+};
+
+// K5 request: format the xGFA of the graph on the device (emit.cu); the bytes stay in
+// Pipeline::xgfa until they are read or saved
+struct XgfaJob {
+	bool paths = false;
+	const char *const *ids = nullptr; // m header strings when paths
+	// results
+	u64 n_nodes = 0, n_edges = 0, label_total = 0, max_height = 0, n_bytes = 0;
+};
+
 struct Pipeline {
 	Dev dev;
 	Dist dist;
@@ -110,6 +132,10 @@ struct Pipeline {
 	int dp_passes = 0;             // verify passes of the last DP (0 = single chunk, < 0 = fell back to the whole-range wavefront)
 	bool have_msa = false, have_index = false, have_f = false, have_seg = false;
 	int seg_status = 0; // 0 ok, 1 "no segmentation"
+	// K5: formatted xGFA bytes (own allocation, grown on demand, kept across builds)
+	u8 *xgfa = nullptr;
+	u64 xgfa_cap = 0, xgfa_len = 0;
+	bool have_xgfa = false;
 
 	void free_all();
 };
@@ -122,7 +148,11 @@ void k1_suffix_array(Pipeline &p);
 void k1_lcp(Pipeline &p);
 void k2_compute_f(Pipeline &p);
 void k3_segment(Pipeline &p);
-void k4_graph(Pipeline &p, Graph &g, bool want_node_of);
+// g: host copy of the graph arrays (may be null); x: also format the xGFA on the device (may be null)
+void k4_graph(Pipeline &p, Graph *g, bool want_node_of, XgfaJob *x = nullptr);
+void k5_emit_xgfa(Pipeline &p, const GraphDev &gd, XgfaJob &x);
+// scratch bytes K5 needs on top of K4's (R = m * nb records)
+u64 k5_scratch_need(u64 m, u64 nb, bool paths, u64 id_bytes);
 
 // bytes of the persistent arena one m x n MSA can need (N <= m*n + m + 1)
 static inline u64 persistent_need(u64 m, u64 n) {

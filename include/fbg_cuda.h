@@ -54,7 +54,7 @@ typedef struct fbg_graph {
 
 /* Per-kernel accounting for the roofline: accumulated CUDA-event milliseconds,
  * algorithmic bytes (DESIGN.md states the per-unit figures) and launch counts. */
-#define FBG_N_KERNELS 12
+#define FBG_N_KERNELS 13
 typedef struct fbg_stats {
 	uint64_t m, n, text_len;      /* N = non-gap cells + m + 1 */
 	uint64_t gaps, to_ignore;     /* fbg.cpp:1858-1859 */
@@ -102,6 +102,21 @@ int fbg_get_boundaries(fbg_ctx *ctx, uint64_t *out);
 /* K4: nodes + edges (fbg.cpp:1222-1260 / 666-728). want_paths != 0 also fills node_of. */
 int fbg_build_graph(fbg_ctx *ctx, int want_paths, fbg_graph *out);
 void fbg_graph_free(fbg_graph *g);
+
+/* K4 + K5: nodes and edges as above, and the xGFA bytes of output_efg
+ * (fbg.cpp:1185-1301: M, X, B lines, per block S then L lines, P lines with output_paths)
+ * formatted ON THE DEVICE; the graph arrays are not copied to the host.  ids = m header strings
+ * (needed with output_paths).  counts (may be NULL) receives the scalar fields of fbg_graph
+ * (n_blocks, n_nodes, n_edges, n_rows, label_total, max_height); its array pointers stay NULL
+ * and it needs no fbg_graph_free.  The bytes stay in device memory until the next
+ * fbg_format_xgfa / upload on this context; read or save them with the two calls below.
+ * Byte-identical to fbg_write_xgfa. */
+int fbg_format_xgfa(fbg_ctx *ctx, int output_paths, const char *const *ids, fbg_graph *counts, uint64_t *n_bytes);
+/* dst[len] <- bytes [offset, offset + len) of the formatted xGFA. */
+int fbg_read_xgfa(fbg_ctx *ctx, uint64_t offset, uint64_t len, uint8_t *dst);
+/* Streams the formatted xGFA into a file (device -> two page-locked staging buffers -> write(),
+ * copy and write overlapped).  Replaces the std::fstream of output_efg (fbg.cpp:1193). */
+int fbg_save_xgfa(fbg_ctx *ctx, const char *path);
 
 /* Whole path in one call: upload (host buffer) -> index -> f -> DP -> graph. */
 int fbg_run(fbg_ctx *ctx, const uint8_t *rows_rowmajor, uint64_t m, uint64_t n, int want_paths,

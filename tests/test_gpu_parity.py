@@ -142,7 +142,10 @@ def test_elastic_golden(gpu_ctx, case, tmp_path):
         assert mml[ok].tolist() == np.array(case["mml"])[ok].tolist()
         assert bt[ok].tolist() == np.array(case["backtrack"])[ok].tolist()
     out = str(tmp_path / "o.xgfa")
-    pkg.output_efg(b, msa, o["paths"], ids, out, ctx)
+    pkg.output_efg(b, msa, o["paths"], ids, out, ctx)  # formatted on the device (K5)
+    assert open(out, "rb").read() == case["xgfa"]
+    out = str(tmp_path / "h.xgfa")
+    pkg.output_efg(b, msa, o["paths"], ids, out, ctx, host_writer=True)
     assert open(out, "rb").read() == case["xgfa"]
 
 
@@ -188,6 +191,23 @@ def test_cli_end_to_end_golden(tmp_path):
             assert l in err, (l, err)
 
 
+def test_cli_device_and_host_writer_agree(tmp_path):
+    """The executable writes the xGFA formatted on the device by default and with the host writer
+    under FBG_HOST_WRITER=1: same file, elastic with P lines and the --nonelastic-gfa extension."""
+    for name, scale, flags in (("cfg3", 0.004, ["--elastic", "--gfa", "-p"]), ("cfg2", 0.02, ["--gap-limit=1", "--nonelastic-gfa"])):
+        msa, _ = synth.make_config(name, scale)
+        fa = str(tmp_path / (name + ".fasta"))
+        O.write_fasta(fa, [r.tobytes() for r in msa], names=[b"seq %d" % i for i in range(msa.shape[0])])
+        outs = []
+        for host in (False, True):
+            out = str(tmp_path / ("%s_%d.xgfa" % (name, host)))
+            env = dict(os.environ, FBG_HOST_WRITER="1") if host else {k: v for k, v in os.environ.items() if k != "FBG_HOST_WRITER"}
+            pr = pkg.main(["--input", fa, "--output", out] + flags, capture_output=True, env=env)
+            assert pr.returncode == 0, pr.stderr.decode()
+            outs.append(open(out, "rb").read())
+        assert len(outs[0]) > 1000 and outs[0] == outs[1]
+
+
 # ------------------------------------------------------------------ oracle, seeded
 def test_xgfa_writer_threads_and_batches(gpu_ctx, tmp_path, monkeypatch):
     """The writer formats blocks on several threads, batch after batch; its single-thread form is
@@ -210,6 +230,21 @@ def test_xgfa_writer_threads_and_batches(gpu_ctx, tmp_path, monkeypatch):
         path = str(tmp_path / ("w%s_%s.xgfa" % (threads, batch)))
         gpu_ctx.write_xgfa(path, msa, b, ids=ids)
         outs.append(open(path, "rb").read())
+    # the device-side writer: whole buffer, slices, and the double-buffered save with tiny chunks
+    dev = gpu_ctx.xgfa_bytes(ids)
+    outs.append(dev)
+    assert gpu_ctx.read_xgfa(1000, 777) == dev[1000:1777] and gpu_ctx.read_xgfa(len(dev), 0) == b""
+    with pytest.raises(pkg.FbgError):
+        gpu_ctx.read_xgfa(len(dev) - 5, 6)
+    for chunk in ("1000", "4096", "99999999"):
+        monkeypatch.setenv("FBG_SAVE_CHUNK", chunk)
+        path = str(tmp_path / ("d%s.xgfa" % chunk))
+        gpu_ctx.save_xgfa(path)
+        outs.append(open(path, "rb").read())
+    monkeypatch.delenv("FBG_SAVE_CHUNK")
+    outs.append(gpu_ctx.xgfa_bytes(None) + b"")  # without P lines: a prefix of the full file
+    assert outs[-1] == outs[0][:len(outs[-1])] and b"\nP\t" not in outs[-1]
+    outs.pop()
     assert len(outs[0]) > 1000 and all(o == outs[0] for o in outs[1:])
     if not (msa == 45).all(axis=1).any():
         ref = str(tmp_path / "oracle.xgfa")
@@ -244,12 +279,19 @@ def _check_elastic(ctx, msa, ignore=b"", tricks_off=False, tmp=None):
     node_of[node_of == O.INVALID] = pkg.api.FBG_NO_NODE
     assert np.array_equal(g.node_of.astype(np.uint64), node_of)
     assert g.label_total == go["label_total"]
-    if tmp is not None and not (msa == 45).all(axis=1).any():
+    if tmp is not None:
         ids = [b"row%d" % i for i in range(msa.shape[0])]
         a, bpath = str(tmp / "gpu.xgfa"), str(tmp / "cpu.xgfa")
         ctx.write_xgfa(a, msa, b, ids)
-        O.write_xgfa(bpath, msa, b_ref, ids)
-        assert open(a, "rb").read() == open(bpath, "rb").read()
+        host_bytes = open(a, "rb").read()
+        if not (msa == 45).all(axis=1).any():  # all-gap rows with -p: UB in the reference (Q4)
+            O.write_xgfa(bpath, msa, b_ref, ids)
+            assert host_bytes == open(bpath, "rb").read()
+        # device-side writer (K5): same bytes, same counts
+        info = ctx.format_xgfa(ids)
+        assert (info["n_nodes"], info["n_edges"], info["label_total"]) == (g.n_nodes, g.n_edges, g.label_total)
+        assert info["max_height"] == g.max_height and info["n_bytes"] == len(host_bytes)
+        assert ctx.read_xgfa() == host_bytes
 
 
 @pytest.mark.parametrize("seed", range(24))
