@@ -36,6 +36,11 @@ class FbgGraph(C.Structure):
                 ("edge_src", _u64p), ("edge_dst", _u64p), ("node_of", _u32p), ("opaque", C.c_void_p)]
 
 
+class FbgMsa(C.Structure):
+    _fields_ = [("rows", _u8p), ("m", C.c_uint64), ("n", C.c_uint64), ("ids", C.POINTER(C.c_char_p)), ("n_ids", C.c_uint64),
+                ("messages", C.c_char_p), ("opaque", C.c_void_p)]
+
+
 class FbgStats(C.Structure):
     _fields_ = [("m", C.c_uint64), ("n", C.c_uint64), ("text_len", C.c_uint64), ("gaps", C.c_uint64), ("to_ignore", C.c_uint64),
                 ("sa_rounds", C.c_uint64), ("arena_peak_bytes", C.c_uint64),
@@ -50,7 +55,7 @@ EXPORTS = [
     "fbg_graph_free", "fbg_run", "fbg_run_device", "fbg_get_stream", "fbg_get_stats", "fbg_reset_stats", "fbg_get_f", "fbg_get_text",
     "fbg_get_sa", "fbg_get_isa", "fbg_get_lcp", "fbg_get_dp", "fbg_radix_sort_pairs", "fbg_radix_sort_bench", "fbg_write_xgfa",
     "fbg_check_index", "fbg_set_dp_chunking", "fbg_dist_unique_id", "fbg_dist_init", "fbg_dist_shutdown", "fbg_plan_key_ranges", "fbg_plan_columns",
-    "fbg_format_xgfa", "fbg_read_xgfa", "fbg_save_xgfa",
+    "fbg_format_xgfa", "fbg_read_xgfa", "fbg_save_xgfa", "fbg_read_fasta", "fbg_msa_free",
 ]
 
 _lib = None
@@ -109,6 +114,9 @@ def load_library():
     lib.fbg_format_xgfa.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(FbgGraph), _u64p]
     lib.fbg_read_xgfa.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p]
     lib.fbg_save_xgfa.argtypes = [C.c_void_p, C.c_char_p]
+    lib.fbg_read_fasta.argtypes = [C.c_char_p, C.c_uint64, C.c_int, C.c_int, C.c_int, C.POINTER(FbgMsa)]
+    lib.fbg_msa_free.argtypes = [C.POINTER(FbgMsa)]
+    lib.fbg_msa_free.restype = None
     lib.fbg_set_dp_chunking.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64]
     lib.fbg_check_index.argtypes = [C.c_void_p, C.c_uint32, C.c_uint64, _u32p]
     lib.fbg_dist_unique_id.argtypes = [_u8p]
@@ -423,6 +431,24 @@ def read_input(input_path: str, gap_limit: int, elastic: bool, output_paths: boo
     if not rows or expected == 0:
         return np.zeros((0, 0), np.uint8), ids
     return np.frombuffer(b"".join(rows), np.uint8).reshape(len(rows), expected).copy(), ids
+
+
+def read_fasta(input_path: str, gap_limit: int, elastic: bool, output_paths: bool = False, threads: int = 0):
+    """The library's own reader (host C++, several threads; what the executable uses): returns
+    (msa uint8[m,n], identifiers, stderr lines of the skipped records)."""
+    lib = load_library()
+    out = FbgMsa()
+    rc = lib.fbg_read_fasta(input_path.encode(), gap_limit, int(elastic), int(output_paths), threads, C.byref(out))
+    if rc != FBG_OK:
+        raise FbgError(rc, "cannot read " + input_path)
+    try:
+        m, n = out.m, out.n
+        msa = np.ctypeslib.as_array(out.rows, shape=(m * n,)).reshape(m, n).copy() if m and n else np.zeros((m, n), np.uint8)
+        ids = [out.ids[i] for i in range(out.n_ids)]
+        msgs = out.messages.decode("utf-8", "replace").split("\n")[:-1]
+    finally:
+        lib.fbg_msa_free(C.byref(out))
+    return msa, ids, msgs
 
 
 def segment_elastic_minmaxlength(msa: np.ndarray, ignorechars: bytes = b"", disable_efg_tricks: bool = False, ctx: Context | None = None):

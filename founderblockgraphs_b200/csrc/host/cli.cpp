@@ -16,11 +16,7 @@
 #include "../../../include/fbg_cuda.h"
 #include <getopt.h>
 #include <chrono>
-#include <fcntl.h>
-#include <sys/mman.h>
-#include <sys/stat.h>
 #include <thread>
-#include <unistd.h>
 #include <utility>
 #include <cstdio>
 #include <cstdlib>
@@ -130,99 +126,6 @@ int parse_args(int argc, char **argv, Args &a) {
 	return err;
 }
 
-// ------------------------------------------------------------ FASTA (fbg.cpp:103-201)
-struct Msa {
-	std::vector<uint8_t> rows; // row-major, kept rows only
-	uint64_t m = 0, n = 0;
-	std::vector<std::string> identifiers;
-};
-
-bool check_gaps(const std::string &identifier, const uint8_t *seq, size_t len, size_t gap_limit) {
-	if (gap_limit == 0) return true;
-	size_t run = 0, best = 0;
-	for (size_t i = 0; i < len; i++) {
-		if (seq[i] == '-') run++;
-		else { if (run > best) best = run; run = 0; }
-	}
-	if (run > best) best = run;
-	if (best < gap_limit) return true;
-	fprintf(stderr, "NOTICE: Sequence \xE2\x80\x9C%s\xE2\x80\x9D contained a gap run with %zu characters.\n",
-	        identifier.size() ? identifier.c_str() + 1 : "", best);
-	return false;
-}
-
-bool check_len(const std::string &identifier, size_t len, size_t expected) {
-	if (len == expected) return true;
-	fprintf(stderr, "WARNING: length of the sequence \xE2\x80\x9C%s\xE2\x80\x9D does not match that of the first sequence; skipping. (%zu vs. %zu)\n",
-	        identifier.size() ? identifier.c_str() + 1 : "", expected, len);
-	return false;
-}
-
-// fbg.cpp:151-201, same acceptance rules and messages; the file is mapped and every sequence
-// line is copied exactly once, straight into the row matrix (a rejected record is rolled back).
-bool read_input(const char *path, size_t gap_limit, bool elastic, bool output_paths, Msa &out) {
-	int fd = open(path, O_RDONLY);
-	if (fd < 0) return false;
-	struct stat sb;
-	if (fstat(fd, &sb) != 0) { close(fd); return false; }
-	size_t fsize = 0;
-	const char *base = nullptr;
-	bool mapped = false;
-	std::vector<char> piped; // pipes, process substitution: no mapping, read to the end
-	if (S_ISREG(sb.st_mode) && sb.st_size > 0) {
-		fsize = (size_t) sb.st_size;
-		void *mp = mmap(nullptr, fsize, PROT_READ, MAP_PRIVATE | MAP_POPULATE, fd, 0);
-		if (mp != MAP_FAILED) { madvise(mp, fsize, MADV_SEQUENTIAL); base = static_cast<const char *>(mp); mapped = true; }
-	}
-	if (!mapped) {
-		char buf[1 << 16];
-		for (;;) {
-			ssize_t got = read(fd, buf, sizeof buf);
-			if (got < 0) { close(fd); return false; }
-			if (got == 0) break;
-			piped.insert(piped.end(), buf, buf + got);
-		}
-		base = piped.data(); fsize = piped.size();
-	}
-	close(fd);
-	const char *p = base, *end = base + fsize;
-	auto next_line = [&](const char *&b, const char *&e) -> bool { // std::getline semantics
-		if (p >= end) return false;
-		b = p;
-		const char *nl = (const char *) memchr(p, '\n', (size_t) (end - p));
-		if (nl) { e = nl; p = nl + 1; } else { e = end; p = end; }
-		return true;
-	};
-	const char *b, *e;
-	std::string identifier;
-	if (next_line(b, e)) identifier.assign(b, e);
-	if (output_paths) out.identifiers.push_back(identifier.size() ? identifier.substr(1) : std::string());
-	out.rows.reserve(fsize); // an upper bound: no reallocation while parsing
-	size_t row_start = out.rows.size();
-	size_t expected = 0;
-	bool is_first = true;
-	auto finish = [&]() {
-		const size_t len = out.rows.size() - row_start;
-		if (is_first) { expected = len; is_first = false; }
-		if (check_len(identifier, len, expected) && (elastic || check_gaps(identifier, out.rows.data() + row_start, len, gap_limit))) out.m++;
-		else out.rows.resize(row_start);
-		row_start = out.rows.size();
-	};
-	while (next_line(b, e)) {
-		if (e > b && *b == '>') {
-			if (output_paths) out.identifiers.push_back(std::string(b + 1, e));
-			finish();
-			identifier.assign(b, e);
-		} else {
-			out.rows.insert(out.rows.end(), (const uint8_t *) b, (const uint8_t *) e);
-		}
-	}
-	finish();
-	out.n = expected;
-	if (mapped) munmap(const_cast<char *>(base), fsize);
-	return true;
-}
-
 void write_graphviz_empty(const char *path) {
 	// elastic mode never fills node_labels/edges (fbg.cpp:3503,3511-3515): empty digraph
 	FILE *fp = fopen(path, "wb");
@@ -268,8 +171,10 @@ int main(int argc, char **argv) {
 	fbg_ctx *ctx = nullptr;
 	int ctx_rc = FBG_OK;
 	std::thread ctx_thread([&]() { ctx_rc = fbg_ctx_create(&ctx, -1); });
-	Msa msa;
-	bool opened = read_input(a.input.c_str(), (size_t) a.gap_limit, a.elastic, a.paths, msa);
+	// read_input (fbg.cpp:151-201): host/fasta_reader.cpp, mapped file, several threads
+	fbg_msa msa;
+	bool opened = fbg_read_fasta(a.input.c_str(), (uint64_t) a.gap_limit, a.elastic, a.paths, 0, &msa) == FBG_OK;
+	if (opened && msa.messages) fputs(msa.messages, stderr);
 	if (!opened || msa.m == 0 || msa.n == 0) { ctx_thread.join(); fprintf(stderr, "Unable to read sequences from the input\n."); return EXIT_FAILURE; }
 	fprintf(stderr, "Input MSA[1..%llu,1..%llu]\n", (unsigned long long) msa.m, (unsigned long long) msa.n);
 
@@ -280,7 +185,7 @@ int main(int argc, char **argv) {
 	if (ctx_rc != FBG_OK) return fail_cuda(nullptr, "cannot initialise the GPU");
 	lap("GPU context (rest after the parse)");
 	if (fbg_set_options(ctx, a.elastic, a.gap_limit, (const uint8_t *) a.ignore.data(), a.ignore.size(), a.tricks_off) != FBG_OK) return fail_cuda(ctx, "options");
-	if (fbg_upload_msa(ctx, msa.rows.data(), msa.m, msa.n) != FBG_OK) return fail_cuda(ctx, "MSA upload");
+	if (fbg_upload_msa(ctx, msa.rows, msa.m, msa.n) != FBG_OK) return fail_cuda(ctx, "MSA upload");
 	fprintf(stderr, "Building the MSA index (suffix array, LCP) on the GPU.\n");
 	if (fbg_build_index(ctx) != FBG_OK) return fail_cuda(ctx, "index construction");
 	fbg_stats st;
@@ -315,14 +220,13 @@ int main(int argc, char **argv) {
 	// Graph and xGFA bytes: formatted on the device and streamed to the file (K5, default), or --
 	// FBG_HOST_WRITER=1 -- graph arrays copied out and formatted by the host writer.  Same bytes.
 	const bool host_writer = getenv("FBG_HOST_WRITER") != nullptr;
-	const bool ids_bad = a.paths && msa.identifiers.size() != msa.m; // the reference asserts at the end of output_efg (fbg.cpp:1292)
-	std::vector<const char *> ids;
-	if (a.paths && !ids_bad) for (auto &s : msa.identifiers) ids.push_back(s.c_str());
+	const bool ids_bad = a.paths && msa.n_ids != msa.m; // the reference asserts at the end of output_efg (fbg.cpp:1292)
+	const char *const *ids = msa.ids;
 	uint64_t xgfa_bytes = 0;
 	if (host_writer) {
 		if (fbg_build_graph(ctx, a.paths ? 1 : 0, &g) != FBG_OK) return fail_cuda(ctx, "graph construction");
 	} else if (!ids_bad) {
-		if (fbg_format_xgfa(ctx, a.paths ? 1 : 0, a.paths ? ids.data() : nullptr, &g, &xgfa_bytes) != FBG_OK) return fail_cuda(ctx, "graph construction");
+		if (fbg_format_xgfa(ctx, a.paths ? 1 : 0, a.paths ? ids : nullptr, &g, &xgfa_bytes) != FBG_OK) return fail_cuda(ctx, "graph construction");
 	}
 	lap(host_writer ? "graph" : "graph + xGFA bytes");
 
@@ -343,7 +247,7 @@ int main(int argc, char **argv) {
 		fprintf(stderr, "founderblockgraph: identifiers.size() == paths.size() failed (rows were skipped while reading; fbg.cpp:1292)\n");
 		return 134;
 	}
-	const int wrc = host_writer ? fbg_write_xgfa(a.output.c_str(), msa.rows.data(), msa.m, msa.n, bnd.data(), &g, a.paths ? 1 : 0, a.paths ? ids.data() : nullptr)
+	const int wrc = host_writer ? fbg_write_xgfa(a.output.c_str(), msa.rows, msa.m, msa.n, bnd.data(), &g, a.paths ? 1 : 0, a.paths ? ids : nullptr)
 	                            : fbg_save_xgfa(ctx, a.output.c_str());
 	if (wrc != FBG_OK) {
 		fprintf(stderr, "ERROR: cannot write %s\n", a.output.c_str());
@@ -351,6 +255,7 @@ int main(int argc, char **argv) {
 	}
 	lap("xGFA write");
 	fbg_graph_free(&g);
+	fbg_msa_free(&msa);
 	fbg_ctx_destroy(ctx);
 	lap("teardown");
 	if (timing) {

@@ -177,6 +177,25 @@ int fbg_radix_sort_bench(fbg_ctx *ctx, uint64_t count, int lo_bit, int hi_bit, i
 int fbg_write_xgfa(const char *path, const uint8_t *rows_rowmajor, uint64_t m, uint64_t n,
                    const uint64_t *boundaries, const fbg_graph *g, int output_paths, const char *const *ids);
 
+/* Host-side FASTA reader: read_input / check_sequence_length / check_gaps (fbg.cpp:103-201),
+ * same acceptance rules; the file is mapped and the records are located, measured, filtered
+ * and copied by several threads (threads <= 0: as many as the host offers, at most 16).
+ * rows: m x n kept rows, row-major, what fbg_upload_msa takes.  ids: EVERY header without its
+ * first byte when output_paths (fbg.cpp:161,169; may outnumber m), else NULL.
+ * messages: the reference's WARNING / NOTICE stderr lines of the skipped records, in file
+ * order, for the caller to print.  FBG_ERR_ARG when the file cannot be read.  Everything is
+ * owned by the library until fbg_msa_free. */
+typedef struct fbg_msa {
+	uint8_t *rows;
+	uint64_t m, n;
+	const char *const *ids;
+	uint64_t n_ids;
+	const char *messages;
+	void *opaque;
+} fbg_msa;
+int fbg_read_fasta(const char *path, uint64_t gap_limit, int elastic, int output_paths, int threads, fbg_msa *out);
+void fbg_msa_free(fbg_msa *msa);
+
 #ifdef __cplusplus
 }
 #endif
