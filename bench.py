@@ -4,11 +4,13 @@
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg2]
 
 One "step" = one pass of the whole hot path (K0 pack -> K1 SA/LCP -> K2 f(x) -> K3 DP ->
-K4 nodes/edges) over one synthetic MSA of the named BASELINE shape.
-  value : cells/s with the MSA already resident in HBM when the timed region starts
-          (CUDA events on the library's own stream, max over ranks)
-  e2e   : the same through the reference-facing C-ABI call with a pinned HOST buffer;
-          H2D of the MSA and D2H of the graph arrays are inside the timed region
+K4 nodes/edges -> K5 xGFA bytes) over one synthetic MSA of the named BASELINE shape: from the
+MSA in memory to the bytes of the output file ("after FASTA parse to xGFA bytes ready",
+SURVEY M1).
+  value : cells/s with the MSA already resident in HBM when the timed region starts and the
+          xGFA bytes left in HBM (CUDA events on the library's own stream, max over ranks)
+  e2e   : the same through the reference-facing C-ABI calls with a pinned HOST buffer;
+          H2D of the MSA and D2H of the xGFA bytes are inside the timed region
   roofline     : dominant kernel (radix scatter passes) algorithmic bytes / event time
   cpu_baseline : the reference's own CPU code (oracle/_ref/ref_harness, built from
                  /root/reference) on a bounded sample of the same workload
@@ -216,6 +218,10 @@ def run_ours(args):
     dev_msa = [torch.from_numpy(v).cuda() for v in variants]
     pin_msa = [torch.from_numpy(v).pin_memory() for v in variants]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    # host destination of the xGFA bytes in the end-to-end arm (sized by a first untimed build)
+    _, _, info0 = ctx.run_xgfa_ptr(dev_msa[0].data_ptr(), m, n, device=True)
+    pin_out = torch.empty(int(info0["n_bytes"] * 1.5) + 4096, dtype=torch.uint8).pin_memory()
+    last_info = [info0]
 
     def barrier():
         torch.cuda.synchronize()
@@ -230,7 +236,8 @@ def run_ours(args):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter()
         a.record(ext)
-        nb, score = ctx.run_ptr(src.data_ptr(), m, n, device=not host)
+        nb, score, last_info[0] = ctx.run_xgfa_ptr(src.data_ptr(), m, n, device=not host,
+                                                    host_out=pin_out.data_ptr() if host else 0, host_cap=pin_out.numel())
         b.record(ext)
         b.synchronize()
         wall = time.perf_counter() - t0
@@ -254,8 +261,7 @@ def run_ours(args):
     barrier()
     sampler.stop_flag = True
     sampler.join()
-    g = ctx._graph
-    d2h = int((g.n_blocks + 2 * g.n_nodes + 2 * g.n_edges) * 8 + 64)  # the C ABI hands out 64-bit arrays
+    d2h = int(last_info[0]["n_bytes"])  # the xGFA bytes of the step
     nb, score = e2e[-1][2], e2e[-1][3]
 
     t_dev = torch.tensor([sum(dev_secs), sum(x[1] for x in e2e)], dtype=torch.float64, device="cuda")
@@ -281,7 +287,7 @@ def run_ours(args):
             barrier()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record(ext)
-            nb_s, score_s = ctx.run_ptr(shared[i % 2].data_ptr(), m, n, device=True)
+            nb_s, score_s, _ = ctx.run_xgfa_ptr(shared[i % 2].data_ptr(), m, n, device=True)
             b.record(ext)
             b.synchronize()
             return a.elapsed_time(b) / 1000.0, nb_s, score_s
@@ -317,6 +323,8 @@ def run_ours(args):
             "ms_per_step": 1000.0 * t_dev_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u8/u32", "data": "synthetic",
             "config": config_dict(name, c, {"blocks": int(nb), "score": int(score), "text_len": int(st["text_len"]), "sa_rounds": int(st["sa_rounds"]),
+                                            "step": "MSA -> xGFA bytes (K0..K5)", "xgfa_bytes": int(last_info[0]["n_bytes"]),
+                                            "nodes": int(last_info[0]["n_nodes"]), "edges": int(last_info[0]["n_edges"]),
                                             "parallelism": "1 MSA per GPU, independent" if world > 1 else "single GPU"}),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(cells), "d2h_bytes_per_step": d2h,
                     "ms_per_step": 1000.0 * t_e2e_total / args.steps},

@@ -283,6 +283,22 @@ class Context:
         self._graph = g
         return nb.value, sc.value
 
+    def run_xgfa_ptr(self, ptr: int, m: int, n: int, device: bool, ids=None, host_out: int = 0, host_cap: int = 0):
+        """Whole path, MSA -> xGFA bytes: upload (host or device buffer), index, f, DP, graph and the
+        bytes of the file formatted on the device (K5).  host_out: address of a host buffer that
+        receives the bytes (end-to-end use); 0 leaves them in device memory.
+        Returns (n_blocks, score, counts)."""
+        self.free_graph()
+        self._check((self.lib.fbg_upload_msa_device if device else self.lib.fbg_upload_msa)(self.h, ptr, m, n))
+        nb, sc = C.c_uint64(), C.c_uint64()
+        self._check(self.lib.fbg_segment(self.h, C.byref(nb), C.byref(sc)))
+        info = self.format_xgfa(ids)
+        if host_out:
+            if info["n_bytes"] > host_cap:
+                raise FbgError(FBG_ERR_ARG, "host buffer too small for the xGFA")
+            self._check(self.lib.fbg_read_xgfa(self.h, 0, info["n_bytes"], host_out))
+        return nb.value, sc.value, info
+
     def write_xgfa(self, path: str, msa: np.ndarray, boundaries: np.ndarray, ids=None):
         assert self._graph is not None
         msa = np.ascontiguousarray(msa, dtype=np.uint8)

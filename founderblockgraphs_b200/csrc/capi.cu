@@ -273,7 +273,7 @@ int fbg_save_xgfa(fbg_ctx *ctx, const char *path) {
 	FILE *fp = fopen(path, "wb");
 	if (!fp) { ctx->err = std::string("cannot open ") + path; return FBG_ERR_ARG; }
 	setvbuf(fp, nullptr, _IONBF, 0);
-	u64 chunk = 8u << 20;
+	u64 chunk = 4u << 20;
 	if (const char *e = getenv("FBG_SAVE_CHUNK")) { long long v = atoll(e); if (v >= 1) chunk = (u64) v; } // test hook
 	PinnedPool::Block blk;
 	cudaEvent_t ev[2] = {nullptr, nullptr};
@@ -281,24 +281,33 @@ int fbg_save_xgfa(fbg_ctx *ctx, const char *path) {
 	try {
 		Pipeline &p = ctx->p;
 		FBG_CUDA(cudaSetDevice(p.dev.device));
-		blk = PinnedPool::get().take(2 * chunk);
-		u8 *buf[2] = {static_cast<u8 *>(blk.ptr), static_cast<u8 *>(blk.ptr) + chunk};
-		FBG_CUDA(cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming));
-		FBG_CUDA(cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming));
-		const u64 total = p.xgfa_len, nchunks = (total + chunk - 1) / chunk;
-		auto issue = [&](u64 k) {
-			const u64 off = k * chunk, len = total - off < chunk ? total - off : chunk;
-			FBG_CUDA(cudaMemcpyAsync(buf[k & 1], p.xgfa + off, len, cudaMemcpyDeviceToHost, p.dev.stream));
-			FBG_CUDA(cudaEventRecord(ev[k & 1], p.dev.stream));
-		};
-		if (nchunks) issue(0);
-		for (u64 k = 0; k < nchunks; k++) {
-			if (k + 1 < nchunks) issue(k + 1); // into the buffer written out in the iteration before
-			FBG_CUDA(cudaEventSynchronize(ev[k & 1]));
-			const u64 off = k * chunk, len = total - off < chunk ? total - off : chunk;
-			if (fwrite(buf[k & 1], 1, len, fp) != len) { ctx->err = std::string("cannot write ") + path; rc = FBG_ERR_ARG; break; }
+		const u64 total = p.xgfa_len;
+		if (total <= 2 * chunk) {
+			// small file: page-locking the staging buffers would cost more than the copy
+			std::vector<u8> tmp(total);
+			if (total) FBG_CUDA(cudaMemcpyAsync(tmp.data(), p.xgfa, total, cudaMemcpyDeviceToHost, p.dev.stream));
+			FBG_CUDA(cudaStreamSynchronize(p.dev.stream));
+			if (total && fwrite(tmp.data(), 1, total, fp) != total) { ctx->err = std::string("cannot write ") + path; rc = FBG_ERR_ARG; }
+		} else {
+			blk = PinnedPool::get().take(2 * chunk);
+			u8 *buf[2] = {static_cast<u8 *>(blk.ptr), static_cast<u8 *>(blk.ptr) + chunk};
+			FBG_CUDA(cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming));
+			FBG_CUDA(cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming));
+			const u64 nchunks = (total + chunk - 1) / chunk;
+			auto issue = [&](u64 k) {
+				const u64 off = k * chunk, len = total - off < chunk ? total - off : chunk;
+				FBG_CUDA(cudaMemcpyAsync(buf[k & 1], p.xgfa + off, len, cudaMemcpyDeviceToHost, p.dev.stream));
+				FBG_CUDA(cudaEventRecord(ev[k & 1], p.dev.stream));
+			};
+			issue(0);
+			for (u64 k = 0; k < nchunks; k++) {
+				if (k + 1 < nchunks) issue(k + 1); // into the buffer written out in the iteration before
+				FBG_CUDA(cudaEventSynchronize(ev[k & 1]));
+				const u64 off = k * chunk, len = total - off < chunk ? total - off : chunk;
+				if (fwrite(buf[k & 1], 1, len, fp) != len) { ctx->err = std::string("cannot write ") + path; rc = FBG_ERR_ARG; break; }
+			}
+			FBG_CUDA(cudaStreamSynchronize(p.dev.stream));
 		}
-		FBG_CUDA(cudaStreamSynchronize(p.dev.stream));
 	} catch (const std::exception &e) {
 		ctx->err = e.what(); cudaGetLastError(); rc = FBG_ERR_CUDA;
 	}
