@@ -45,6 +45,7 @@ void Pipeline::free_all() {
 	col = ISA = SA = PLCP = f = bnd = dp_a = dp_b = dp_v = nullptr;
 	dev.pers_top = 0;
 	have_msa = have_index = have_f = have_seg = have_xgfa = false;
+	want_full_index = index_lazy = false; lazy_depth = 0;
 }
 
 } // namespace fbg
@@ -137,13 +138,17 @@ static int upload_common(fbg_ctx *ctx, const void *rows, uint64_t m, uint64_t n,
 int fbg_upload_msa(fbg_ctx *ctx, const uint8_t *rows, uint64_t m, uint64_t n) { return upload_common(ctx, rows, m, n, false); }
 int fbg_upload_msa_device(fbg_ctx *ctx, const void *rows, uint64_t m, uint64_t n) { return upload_common(ctx, rows, m, n, true); }
 
-int fbg_build_index(fbg_ctx *ctx) {
+// full = the true SA / ISA / LCP are wanted (explicit fbg_build_index, read-backs); otherwise K1 may
+// stop at the sufficient index (suffix.cu).  A sufficient index is replaced when the full one is asked for.
+static int build_index_impl(fbg_ctx *ctx, bool full) {
 	if (!ctx || !ctx->p.have_msa) { if (ctx) ctx->err = "no MSA uploaded"; return FBG_ERR_ARG; }
 	FBG_TRY(ctx)
 	Pipeline &p = ctx->p;
 	FBG_CUDA(cudaSetDevice(p.dev.device));
-	if (p.have_index) return FBG_OK;
-	k0_pack(p);
+	if (p.have_index && !(full && p.index_lazy)) return FBG_OK;
+	if (full) p.want_full_index = true;
+	if (!p.have_index) k0_pack(p);
+	p.have_index = false;
 	k1_suffix_array(p);
 	k1_lcp(p);
 	p.have_index = true;
@@ -151,9 +156,11 @@ int fbg_build_index(fbg_ctx *ctx) {
 	return FBG_OK;
 }
 
+int fbg_build_index(fbg_ctx *ctx) { return build_index_impl(ctx, true); }
+
 int fbg_compute_f(fbg_ctx *ctx) {
 	if (!ctx) return FBG_ERR_ARG;
-	int rc = fbg_build_index(ctx);
+	int rc = build_index_impl(ctx, false);
 	if (rc) return rc;
 	FBG_TRY(ctx)
 	Pipeline &p = ctx->p;
@@ -415,6 +422,7 @@ int fbg_get_stats(fbg_ctx *ctx, fbg_stats *out) {
 	std::memset(out, 0, sizeof *out);
 	out->m = p.m; out->n = p.n; out->text_len = p.N; out->gaps = p.gaps; out->to_ignore = p.toignore;
 	out->sa_rounds = p.sa_rounds; out->arena_peak_bytes = p.dev.arena_peak; out->dp_passes = p.dp_passes; out->kmer_dict = p.kmer_dict;
+	out->index_depth = p.index_lazy ? (int64_t) p.lazy_depth : 0;
 	for (int k = 0; k < K_COUNT; k++) {
 		out->kernel_ms[k] = p.dev.stats[k].ms; out->kernel_bytes[k] = p.dev.stats[k].bytes; out->kernel_launches[k] = p.dev.stats[k].launches;
 	}
@@ -442,14 +450,17 @@ int fbg_get_text(fbg_ctx *ctx, uint8_t *out) {
 }
 int fbg_get_sa(fbg_ctx *ctx, uint64_t *out) {
 	if (!ctx || !out || !ctx->p.have_index) { if (ctx) ctx->err = "index not built"; return FBG_ERR_ARG; }
+	if (int rc = build_index_impl(ctx, true)) return rc;
 	return copy_u32_as_u64(ctx, ctx->p.SA, ctx->p.N, out);
 }
 int fbg_get_isa(fbg_ctx *ctx, uint64_t *out) {
 	if (!ctx || !out || !ctx->p.have_index) { if (ctx) ctx->err = "index not built"; return FBG_ERR_ARG; }
+	if (int rc = build_index_impl(ctx, true)) return rc;
 	return copy_u32_as_u64(ctx, ctx->p.ISA, ctx->p.N, out);
 }
 int fbg_get_lcp(fbg_ctx *ctx, uint64_t *out) {
 	if (!ctx || !out || !ctx->p.have_index) { if (ctx) ctx->err = "index not built"; return FBG_ERR_ARG; }
+	if (int rc = build_index_impl(ctx, true)) return rc;
 	FBG_TRY(ctx)
 	Pipeline &p = ctx->p;
 	std::vector<u32> plcp(p.N), sa(p.N);
@@ -473,6 +484,7 @@ int fbg_get_dp(fbg_ctx *ctx, uint64_t *a, uint64_t *b, uint64_t *v) {
 
 int fbg_check_index(fbg_ctx *ctx, uint32_t nsamples, uint64_t seed, uint32_t *n_bad) {
 	if (!ctx || !n_bad || !ctx->p.have_index) { if (ctx) ctx->err = "index not built"; return FBG_ERR_ARG; }
+	if (int rc = build_index_impl(ctx, true)) return rc;
 	FBG_TRY(ctx)
 	Pipeline &p = ctx->p;
 	FBG_CUDA(cudaSetDevice(p.dev.device));

@@ -132,6 +132,11 @@ struct Pipeline {
 	int dp_passes = 0;             // verify passes of the last DP (0 = single chunk, < 0 = fell back to the whole-range wavefront)
 	bool have_msa = false, have_index = false, have_f = false, have_seg = false;
 	int seg_status = 0; // 0 ok, 1 "no segmentation"
+	// K1 may stop early on gapless MSAs (suffix.cu, "sufficient index"): SA / ISA / PLCP are then exact
+	// everywhere except inside the column-pure buckets left at depth lazy_depth.  fbg_build_index
+	// and the read-back calls set want_full_index and get the true arrays.
+	bool want_full_index = false, index_lazy = false;
+	u64 lazy_depth = 0;
 	// K5: formatted xGFA bytes (own allocation, grown on demand, kept across builds)
 	u8 *xgfa = nullptr;
 	u64 xgfa_cap = 0, xgfa_len = 0;

@@ -830,13 +830,80 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	return true;
 }
 
+// ---- sufficient index for gapless MSAs: stop as soon as every tied bucket is COLUMN-PURE
+// What K2 takes from the index is, per column x, the runs of consecutive ranks inside
+// C_x = {rank of p_i(x)} and minima of LCP over them (fcol.cu).  In a gapless MSA C_x is the set
+// of ALL text positions of column x, so a bucket (= all suffixes sharing a prefix of length D)
+// whose members lie in one column is a subset of C_x: it sits inside one run whatever the order
+// of its members, the LCP between two of its members is >= D, and the LCP between a member and
+// anything outside is < D and the same for every member.  Every minimum K2 takes ranges over at
+// least one bucket boundary, so it never sees an LCP from inside a bucket: the order inside
+// column-pure buckets and the exact LCP values inside them cannot change f.  Prefix doubling
+// may therefore stop at the first depth D at which all buckets still tied are column-pure
+// (cfg2: D = K = 21, straight after the k-mer round; MSAs with repeats across columns go on
+// until the repeats are resolved).  The members of the remaining buckets get consecutive
+// ranks in list order, PLCP = D for all but the first, and LCP at bucket heads and single
+// suffixes is found by direct comparison (< D characters).  SA, ISA and PLCP then differ from
+// the true arrays only inside those buckets; fbg_build_index and the read-back calls build the
+// full index.  tests/test_gpu_parity.py::test_sufficient_index_* compare both on gapless inputs.
+constexpr u64 LAZY_MAX_DEPTH = 96;   // direct LCP comparisons stay below this many characters
+constexpr u32 PLCP_INNER = 0x80000000u; // mark: "inside a column-pure bucket, value = depth"
+
+// *impure = 1 when two neighbours of the list share the bucket rank but not the column
+template <bool BLIST> __global__ void k1_pure_check_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, const u64 *__restrict__ bkey, int nbits, u64 na,
+                                                           const u32 *__restrict__ col, u32 *__restrict__ impure) {
+	u64 t = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (t + 1 >= na) return;
+	const u32 ra = BLIST ? (u32) (bkey[t] >> nbits) : lr[t], rb = BLIST ? (u32) (bkey[t + 1] >> nbits) : lr[t + 1];
+	if (ra == rb && col[lp[t]] != col[lp[t + 1]]) *impure = 1u;
+}
+// hd[t] = t + 1 at the first entry of a bucket, else 0 (inclusive max-scan: list index + 1 of the bucket's first entry)
+template <bool BLIST> __global__ void k1_pure_heads_kernel(const u32 *__restrict__ lr, const u64 *__restrict__ bkey, int nbits, u64 na, u32 *__restrict__ hd) {
+	u64 t = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= na) return;
+	const u32 ra = BLIST ? (u32) (bkey[t] >> nbits) : lr[t];
+	const u32 rp = t ? (BLIST ? (u32) (bkey[t - 1] >> nbits) : lr[t - 1]) : 0u;
+	hd[t] = (t == 0 || ra != rp) ? (u32) t + 1u : 0u;
+}
+// consecutive ranks in list order; all but the first member are marked "inside"
+template <bool BLIST> __global__ void k1_pure_final_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, const u64 *__restrict__ bkey, int nbits, u64 na,
+                                                           const u32 *__restrict__ hd, u32 depth, u32 *__restrict__ R, u32 *__restrict__ SA, u32 *__restrict__ PLCP) {
+	u64 t = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= na) return;
+	const u32 ra = BLIST ? (u32) (bkey[t] >> nbits) : lr[t];
+	const u32 j = (u32) t - (hd[t] - 1u);
+	const u32 p = lp[t];
+	R[p] = ra + j;
+	SA[ra + j] = p;
+	if (j) PLCP[p] = PLCP_INNER | depth;
+}
+// LCP of the sufficient index: marked positions keep the depth, every other suffix is compared
+// with its predecessor in SA (a bucket head or a single suffix: fewer than `depth` characters agree)
+__global__ void k1_lazy_lcp_kernel(const u8 *__restrict__ T, const u32 *__restrict__ SA, u64 N, u32 *__restrict__ PLCP) {
+	u64 k = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (k >= N) return;
+	const u32 p = SA[k];
+	const u32 v = PLCP[p];
+	if (v & PLCP_INNER) { PLCP[p] = v & ~PLCP_INNER; return; }
+	u32 len = 0;
+	if (k > 0) {
+		const u32 q = SA[k - 1];
+		while ((u64) p + len < N && (u64) q + len < N && T[p + len] == T[q + len]) len++;
+	}
+	PLCP[p] = len;
+}
+
 void k1_suffix_array(Pipeline &p) {
 	Dev &d = p.dev;
 	const Dist &dist = p.dist;
 	const bool sharded = dist.world > 1;
 	const u64 N = p.N;
-	p.ISA = p.dev.palloc<u32>(N + 1);
-	p.SA = p.dev.palloc<u32>(N + 1);
+	if (!p.ISA) p.ISA = p.dev.palloc<u32>(N + 1); // (a full index built after a sufficient one re-uses the arrays)
+	if (!p.SA) p.SA = p.dev.palloc<u32>(N + 1);
+	if (!p.PLCP) p.PLCP = p.dev.palloc<u32>(N + 1);
+	p.index_lazy = false; p.lazy_depth = 0;
+	// the sufficient index (above): gapless rows, one GPU, unless the full index was asked for
+	const bool lazy_ok = !sharded && p.gaps == 0 && !p.want_full_index && !getenv("FBG_FULL_INDEX");
 	d.ensure((sharded ? 1u : 0u) * (u64) (4u << KM_HBITS) + (1u << 20));
 	u64 mk = d.mark();
 
@@ -962,6 +1029,50 @@ void k1_suffix_array(Pipeline &p) {
 	}
 	for (;;) {
 		if (by_dict && nS + nB == 0) break; // every k-mer was unique
+		if (lazy_ok && p.sa_rounds >= 1 && h / 2 <= LAZY_MAX_DEPTH && nS + nB) {
+			// ranks are exact to depth h / 2: are all buckets still tied column-pure?
+			u32 *impure = reinterpret_cast<u32 *>(p.scalars + 12);
+			u32 *h_impure = reinterpret_cast<u32 *>(p.h_scalars + 12);
+			const u64 *bk = (const u64 *) rb.k[rb.cur];
+			const u32 *bv = rb.v[rb.cur];
+			FBG_CUDA(cudaMemsetAsync(impure, 0, sizeof(u64), d.stream));
+			d.begin(K_DOUBLING_AUX);
+			if (nS) k1_pure_check_kernel<false><<<div_up(nS, 256), 256, 0, d.stream>>>(Slp[sc], Slr[sc], nullptr, nbits, nS, p.col, impure);
+			if (nB) k1_pure_check_kernel<true><<<div_up(nB, 256), 256, 0, d.stream>>>(bv, nullptr, bk, nbits, nB, p.col, impure);
+			FBG_LAUNCH_CHECK();
+			d.end((double) nS * 12.0 + (double) nB * 16.0);
+			FBG_CUDA(cudaMemcpyAsync(h_impure, impure, sizeof(u32), cudaMemcpyDeviceToHost, d.stream));
+			FBG_CUDA(cudaStreamSynchronize(d.stream));
+			if (debug) fprintf(stderr, "[fbg] K1 depth %llu: tied buckets %s\n", (unsigned long long) (h / 2), *h_impure ? "span several columns" : "are all column-pure: stop");
+			if (*h_impure == 0) {
+				const u32 depth = (u32) (h / 2);
+				FBG_CUDA(cudaMemsetAsync(p.PLCP, 0, N * sizeof(u32), d.stream));
+				if (nS) {
+					d.begin(K_DOUBLING_AUX);
+					k1_pure_heads_kernel<false><<<div_up(nS, 256), 256, 0, d.stream>>>(Slr[sc], nullptr, nbits, nS, lp_out);
+					FBG_LAUNCH_CHECK();
+					d.end((double) nS * 8.0);
+					device_scan<OpMaxU32, false>(d, lp_out, lp_out, nS);
+					d.begin(K_DOUBLING_AUX);
+					k1_pure_final_kernel<false><<<div_up(nS, 256), 256, 0, d.stream>>>(Slp[sc], Slr[sc], nullptr, nbits, nS, lp_out, depth, p.ISA, p.SA, p.PLCP);
+					FBG_LAUNCH_CHECK();
+					d.end((double) nS * 24.0);
+				}
+				if (nB) {
+					d.begin(K_DOUBLING_AUX);
+					k1_pure_heads_kernel<true><<<div_up(nB, 256), 256, 0, d.stream>>>(nullptr, bk, nbits, nB, HR);
+					FBG_LAUNCH_CHECK();
+					d.end((double) nB * 12.0);
+					device_scan<OpMaxU32, false>(d, HR, HR, nB);
+					d.begin(K_DOUBLING_AUX);
+					k1_pure_final_kernel<true><<<div_up(nB, 256), 256, 0, d.stream>>>(bv, nullptr, bk, nbits, nB, HR, depth, p.ISA, p.SA, p.PLCP);
+					FBG_LAUNCH_CHECK();
+					d.end((double) nB * 28.0);
+				}
+				p.index_lazy = true; p.lazy_depth = depth;
+				break;
+			}
+		}
 		if (debug) fprintf(stderr, "[fbg] rank %d K1 round %d: depth %llu, S list %llu (largest bucket %u), B list %llu\n", dist.rank, p.sa_rounds,
 		                   (unsigned long long) (p.sa_rounds ? h / 2 : 0), (unsigned long long) nS, maxb, (unsigned long long) nB);
 		FBG_CUDA(cudaMemsetAsync(p.scalars + 8, 0, 4 * sizeof(u64), d.stream));
@@ -1105,7 +1216,14 @@ __global__ void k1_plcp_kernel(u32 *__restrict__ M, u64 N) {
 void k1_lcp(Pipeline &p) {
 	Dev &d = p.dev;
 	const u64 N = p.N;
-	p.PLCP = p.dev.palloc<u32>(N + 1);
+	if (!p.PLCP) p.PLCP = p.dev.palloc<u32>(N + 1);
+	if (p.index_lazy) {
+		d.begin(K_LCP);
+		k1_lazy_lcp_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(p.T, p.SA, N, p.PLCP);
+		FBG_LAUNCH_CHECK();
+		d.end((double) N * 12.0);
+		return;
+	}
 	d.ensure(N * 16 + (N / SCAN_TILE + 2) * 24 + (4u << 20));
 	u64 mk = d.mark();
 	u32 *flag = d.alloc<u32>(N), *pos = d.alloc<u32>(N), *ia = d.alloc<u32>(N), *ib = d.alloc<u32>(N);

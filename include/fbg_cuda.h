@@ -65,6 +65,7 @@ typedef struct fbg_stats {
 	uint64_t kernel_launches[FBG_N_KERNELS];
 	int64_t dp_passes;            /* K3: verify passes of the chunked DP (0 = one chunk, < 0 = that many passes were spent and the whole-range wavefront was needed) */
 	int64_t kmer_dict;            /* K1 round 0: 1 = through the k-mer dictionary, 0 = by sorting all suffixes (multi-GPU build, too many distinct k-mers, 64-bit k-mers) */
+	int64_t index_depth;          /* 0 = the full index; D > 0 = K1 stopped at depth D, where every bucket still tied lay in one column of a gapless MSA (the "sufficient index": same f, segmentation and graph) */
 } fbg_stats;
 
 /* index -> name for the arrays above ("pack", "kmer", "radix_hist", ...) */
@@ -86,7 +87,12 @@ int fbg_upload_msa(fbg_ctx *ctx, const uint8_t *rows_rowmajor, uint64_t m, uint6
 /* Same, from a device buffer on the context's device (inputs resident in HBM). */
 int fbg_upload_msa_device(fbg_ctx *ctx, const void *device_rows_rowmajor, uint64_t m, uint64_t n);
 
-/* K0+K1: text, suffix array, inverse, LCP. Replaces load_cst -> sdsl::construct (fbg.cpp:3378, 428). */
+/* K0+K1: text, suffix array, inverse, LCP. Replaces load_cst -> sdsl::construct (fbg.cpp:3378, 428).
+ * Called explicitly it builds the FULL index (true SA / ISA / LCP, what the read-backs below return).
+ * The later stages need less and build it themselves when this call is left out: on a gapless MSA
+ * (all of non-elastic --gap-limit=1) prefix doubling stops at the first depth at which every bucket
+ * of tied suffixes lies in one column -- order and LCP inside such a bucket cannot change f(x)
+ * (suffix.cu) -- see fbg_stats.index_depth.  FBG_FULL_INDEX=1 in the environment switches that off. */
 int fbg_build_index(fbg_ctx *ctx);
 /* K2: f(x). Replaces compute_f / compute_f_range (fbg.cpp:1923, 2278-2289); in non-elastic
  * mode computes f with tricks disabled, the quantity v[j] is derived from (fbg.cpp:552-611). */

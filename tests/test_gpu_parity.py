@@ -476,3 +476,89 @@ def test_randomised_shapes(gpu_ctx):
             _check_nonelastic(gpu_ctx, msa, 1)
     assert len(kinds) == 8
 
+
+
+# ------------------------------------------------- sufficient index (gapless MSAs, K1 early stop)
+def _gapless_cases():
+    rng = np.random.default_rng(77)
+    acgt = np.frombuffer(b"ACGT", np.uint8)
+    out = {}
+    out["cfg2_twin"] = synth.make_msa(200, 3000, snp=0.005, seed=11)
+    base = acgt[rng.integers(0, 4, size=1500)]
+    rows = np.tile(base, (60, 1))
+    snp = rng.random(rows.shape) < 0.004
+    rows[snp] = acgt[rng.integers(0, 4, size=int(snp.sum()))]
+    r30 = rows.copy(); r30[:, 900:930] = r30[:, 200:230]          # a repeat across columns shorter than 42: pure at depth 42
+    out["repeat30"] = r30
+    r60 = rows.copy(); r60[:, 1000:1060] = r60[:, 300:360]        # needs depth 84
+    out["repeat60"] = r60
+    r300 = rows.copy(); r300[:, 1100:1400] = r300[:, 100:400]     # longer than the lazy limit: falls back to the full index
+    out["repeat300"] = r300
+    out["identical_rows"] = np.tile(base[:700], (25, 1))
+    out["periodic"] = np.tile(np.frombuffer(b"ACGGT" * 80, np.uint8), (9, 1))
+    polya = rows[:20, :800].copy(); polya[:, 300:420] = 65
+    out["poly_a"] = polya
+    withn = rows[:30, :1000].copy(); withn[rng.random(withn.shape) < 0.002] = 78
+    out["with_N"] = withn
+    out["one_row"] = rows[:1, :500].copy()
+    out["two_columns"] = rows[:40, :2].copy()
+    out["unrelated_rows"] = acgt[rng.integers(0, 4, size=(12, 400))]
+    return out
+
+
+@pytest.mark.parametrize("name", sorted(_gapless_cases()))
+def test_sufficient_index_matches_full_index(gpu_ctx, name, monkeypatch):
+    """Gapless MSA: the early-stopped index and the full index give the same f, DP tables,
+    boundaries and graph (and both match the oracle through the checks above)."""
+    msa = _gapless_cases()[name]
+    ctx = gpu_ctx
+    res = {}
+    for full in (False, True):
+        if full:
+            monkeypatch.setenv("FBG_FULL_INDEX", "1")
+        else:
+            monkeypatch.delenv("FBG_FULL_INDEX", raising=False)
+        r = []
+        for elastic, ign, toff in ((True, b"", False), (True, b"N", True), (False, b"", False)):
+            ctx.set_options(elastic=elastic, gap_limit=1, ignore_chars=ign, disable_tricks=toff)
+            ctx.upload(msa)
+            f = ctx.compute_f()
+            depth = ctx.stats()["index_depth"]
+            assert (depth == 0) if full else True
+            try:
+                b, score = ctx.segment()
+            except pkg.NoSegmentation:
+                r.append((f.tolist(), "noseg", depth))
+                continue
+            g = ctx.build_graph(want_paths=True)
+            r.append((f.tolist(), b.tolist(), score, [x.tolist() for x in ctx.dp(elastic)], g.node_row.tolist(), g.edge_src.tolist(),
+                      g.edge_dst.tolist(), g.node_of.tolist(), depth))
+        res[full] = r
+    for a, bb in zip(res[False], res[True]):
+        assert a[:-1] == bb[:-1]
+    depths = [a[-1] for a in res[False]]
+    expect = {"cfg2_twin": 21, "repeat30": 42, "repeat60": 84, "repeat300": 0, "identical_rows": 21}
+    if name in expect:
+        assert depths[0] == expect[name], depths
+    # the oracle on the elastic default and the non-elastic mode
+    f_ref = O.compute_f(msa, b"", False)
+    assert res[False][0][0] == f_ref.tolist()
+    assert res[False][2][0] == O.compute_f(msa, b"", True).tolist()
+
+
+def test_sufficient_index_then_full_index_on_request(gpu_ctx):
+    """compute_f builds the sufficient index; the read-backs then rebuild and return the true arrays."""
+    msa = synth.make_msa(50, 1200, snp=0.01, seed=5)
+    ctx = gpu_ctx
+    ctx.set_options(elastic=True)
+    ctx.upload(msa)
+    f = ctx.compute_f()
+    assert ctx.stats()["index_depth"] == 21
+    T, _, _, _ = O.text(msa)
+    SA, ISA, LCP = O.sa_lcp(T)
+    assert np.array_equal(ctx.sa(), SA.astype(np.uint64))
+    assert ctx.stats()["index_depth"] == 0
+    assert np.array_equal(ctx.isa(), ISA.astype(np.uint64)) and np.array_equal(ctx.lcp(), LCP.astype(np.uint64))
+    assert ctx.check_index(20000, 3) == 0
+    b, score = ctx.segment()
+    assert np.array_equal(ctx.get_f(), f) and np.array_equal(f, O.compute_f(msa, b"", False))

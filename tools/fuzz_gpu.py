@@ -82,8 +82,12 @@ def main():
             traceback.print_exc()
             sys.exit(1)
         done[kind] = done.get(kind, 0) + 1
+        if ctx.stats()["index_depth"]:
+            done["(sufficient index)"] = done.get("(sufficient index)", 0) + 1
         seed += 1
-    print("fuzz ok: %d cases in %.0f s, seeds up to %d, by kind %s" % (sum(done.values()), time.time() - t0, seed - 1, done), flush=True)
+    n_lazy = done.pop("(sufficient index)", 0)
+    print("fuzz ok: %d cases in %.0f s (%d of them through the sufficient index), seeds up to %d, by kind %s" % (
+        sum(done.values()), time.time() - t0, n_lazy, seed - 1, done), flush=True)
 
 
 if __name__ == "__main__":
