@@ -689,6 +689,85 @@ __global__ void k1_active_total_kernel(const u64 *sc64, u64 *tot) {
 	*tot = (a & 0xFFFFFFFFull) + (a >> 32) + (b & 0xFFFFFFFFull) + (b >> 32);
 }
 
+// ---- sufficient index for gapless MSAs: stop as soon as every tied bucket is COLUMN-PURE
+// What K2 takes from the index is, per column x, the runs of consecutive ranks inside
+// C_x = {rank of p_i(x)} and minima of LCP over them (fcol.cu).  In a gapless MSA C_x is the set
+// of ALL text positions of column x, so a bucket (= all suffixes sharing a prefix of length D)
+// whose members lie in one column is a subset of C_x: it sits inside one run whatever the order
+// of its members, the LCP between two of its members is >= D, and the LCP between a member and
+// anything outside is < D and the same for every member.  Every minimum K2 takes ranges over at
+// least one bucket boundary, so it never sees an LCP from inside a bucket: the order inside
+// column-pure buckets and the exact LCP values inside them cannot change f.  Prefix doubling
+// may therefore stop at the first depth D at which all buckets still tied are column-pure
+// (cfg2: D = K = 21, straight after the k-mer round; MSAs with repeats across columns go on
+// until the repeats are resolved).  The members of the remaining buckets get consecutive
+// ranks in list order, PLCP = D for all but the first, and LCP at bucket heads and single
+// suffixes is found by direct comparison (< D characters).  SA, ISA and PLCP then differ from
+// the true arrays only inside those buckets; fbg_build_index and the read-back calls build the
+// full index.  tests/test_gpu_parity.py::test_sufficient_index_* compare both on gapless inputs.
+constexpr u64 LAZY_MAX_DEPTH = 96;   // direct LCP comparisons stay below this many characters
+constexpr u32 PLCP_TODO = 0xFFFFFFFFu; // mark: bucket head or single suffix, LCP still to be found by comparison
+
+// *impure = 1 when two neighbours of the list share the bucket rank but not the column
+template <bool BLIST> __global__ void k1_pure_check_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, const u64 *__restrict__ bkey, int nbits, u64 na,
+                                                           const u32 *__restrict__ col, u32 *__restrict__ impure) {
+	u64 t = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (t + 1 >= na) return;
+	const u32 ra = BLIST ? (u32) (bkey[t] >> nbits) : lr[t], rb = BLIST ? (u32) (bkey[t + 1] >> nbits) : lr[t + 1];
+	if (ra == rb && col[lp[t]] != col[lp[t + 1]]) *impure = 1u;
+}
+// hd[t] = t + 1 at the first entry of a bucket, else 0 (inclusive max-scan: list index + 1 of the bucket's first entry)
+template <bool BLIST> __global__ void k1_pure_heads_kernel(const u32 *__restrict__ lr, const u64 *__restrict__ bkey, int nbits, u64 na, u32 *__restrict__ hd) {
+	u64 t = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= na) return;
+	const u32 ra = BLIST ? (u32) (bkey[t] >> nbits) : lr[t];
+	const u32 rp = t ? (BLIST ? (u32) (bkey[t - 1] >> nbits) : lr[t - 1]) : 0u;
+	hd[t] = (t == 0 || ra != rp) ? (u32) t + 1u : 0u;
+}
+// consecutive ranks in list order; all but the first member are marked "inside"
+template <bool BLIST> __global__ void k1_pure_final_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, const u64 *__restrict__ bkey, int nbits, u64 na,
+                                                           const u32 *__restrict__ hd, u32 depth, u32 *__restrict__ R, u32 *__restrict__ SA, u32 *__restrict__ PLCP) {
+	u64 t = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= na) return;
+	const u32 ra = BLIST ? (u32) (bkey[t] >> nbits) : lr[t];
+	const u32 j = (u32) t - (hd[t] - 1u);
+	const u32 p = lp[t];
+	R[p] = ra + j;
+	SA[ra + j] = p;
+	if (j) PLCP[p] = depth;
+}
+// LCP of the sufficient index, in text order: members inside a bucket already hold the depth; a
+// bucket head or single suffix (still marked) is compared with its predecessor in SA -- fewer
+// than `depth` characters agree
+__global__ void k1_lazy_lcp_kernel(const u8 *__restrict__ T, const u32 *__restrict__ SA, const u32 *__restrict__ ISA, u64 N, u32 *__restrict__ PLCP) {
+	u64 p = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (p >= N || PLCP[p] != PLCP_TODO) return;
+	const u32 k = ISA[p];
+	u32 len = 0;
+	if (k > 0) {
+		const u32 q = SA[k - 1];
+		while (p + len < N && (u64) q + len < N && T[p + len] == T[q + len]) len++;
+	}
+	PLCP[p] = len;
+}
+
+// Round 0 through the dictionary, speculating that every k-mer bucket is column-pure (the usual
+// case for a gapless MSA): final ranks (bucket rank + arrival number), SA entries and PLCP marks
+// straight from the table, in text order, and no S / B lists.  *impure is raised when a bucket
+// holds two columns; the caller then emits the lists as usual (R, SA are rewritten).
+__global__ void __launch_bounds__(256) k1_dict_emit_pure_kernel(const u32 *__restrict__ slot_of, const u32 *__restrict__ ord_of, const uint4 *__restrict__ info,
+                                                                const u32 *__restrict__ col, u64 N, u32 depth, u32 *__restrict__ R, u32 *__restrict__ SA,
+                                                                u32 *__restrict__ PLCP, u32 *__restrict__ impure) {
+	u64 p = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (p >= N) return;
+	const uint4 v = __ldg(info + slot_of[p]);
+	const u32 j = v.z == 1 ? 0u : ord_of[p];
+	R[p] = v.x + j;
+	SA[v.x + j] = (u32) p;
+	PLCP[p] = j ? depth : PLCP_TODO;
+	if (v.z > 1 && col[p] != __ldg(col + v.w)) *impure = 1u; // v.w = the bucket's smallest member
+}
+
 // ---- round 0 through the k-mer dictionary (single GPU)
 __global__ void k1_dict_flag_kernel(const u64 *__restrict__ key, u32 cap, u32 *__restrict__ flag) {
 	u32 s = blockIdx.x * blockDim.x + threadIdx.x;
@@ -759,7 +838,7 @@ static u64 dict_scratch_bytes(u64 N) {
 // Returns false (nothing written that matters) when the text has too many distinct k-mers for
 // the table: the caller then sorts all suffixes as before.
 static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int key_bits0, u32 km_grid, u32 *slot_of, u32 *ord_of, u32 *A,
-                           u64 hnext, int nbits, CompactOut o, u64 *nS, u64 *nB, u32 *maxb) {
+                           u64 hnext, int nbits, CompactOut o, u64 *nS, u64 *nB, u32 *maxb, bool try_pure) {
 	Dev &d = p.dev;
 	const u64 N = p.N;
 	const u32 cap = dict_capacity(N), ndmax = cap / 2;
@@ -816,6 +895,24 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	k1_dict_assign_kernel<<<gn, 256, 0, d.stream>>>(lv, dk.cnt, dk.first, call, cbig, nd, 0u, info, rank_of_slot, A, sc + 4);
 	FBG_LAUNCH_CHECK();
 	d.end((double) nd * 40.0 + (double) N * 4.0);
+	if (try_pure) {
+		// sufficient index (above k1_suffix_array): if no bucket spans two columns this is all of K1
+		u32 *impure = reinterpret_cast<u32 *>(p.scalars + 12);
+		u32 *h_impure = reinterpret_cast<u32 *>(p.h_scalars + 12);
+		FBG_CUDA(cudaMemsetAsync(impure, 0, sizeof(u64), d.stream));
+		d.begin(K_DOUBLING_AUX);
+		k1_dict_emit_pure_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, p.col, N, (u32) K, p.ISA, p.SA, p.PLCP, impure);
+		FBG_LAUNCH_CHECK();
+		d.end((double) N * (8.0 + 4.0 + 4.0 + 4.0 + 4.0) + (double) nd * 16.0);
+		FBG_CUDA(cudaMemcpyAsync(h_impure, impure, sizeof(u32), cudaMemcpyDeviceToHost, d.stream));
+		FBG_CUDA(cudaStreamSynchronize(d.stream));
+		if (*h_impure == 0) {
+			p.index_lazy = true; p.lazy_depth = (u64) K;
+			*nS = 0; *nB = 0; *maxb = 0;
+			d.release(mk);
+			return true;
+		}
+	}
 	device_scan<OpSumU32, true>(d, A, A, N, sc + 2);
 	d.begin(K_DOUBLING_AUX);
 	k1_dict_fold_kernel<<<gn, 256, 0, d.stream>>>(lv, nd, info, A);
@@ -828,69 +925,6 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	*nS = h_sc[2]; *nB = h_sc[3]; *maxb = h_sc[4];
 	d.release(mk);
 	return true;
-}
-
-// ---- sufficient index for gapless MSAs: stop as soon as every tied bucket is COLUMN-PURE
-// What K2 takes from the index is, per column x, the runs of consecutive ranks inside
-// C_x = {rank of p_i(x)} and minima of LCP over them (fcol.cu).  In a gapless MSA C_x is the set
-// of ALL text positions of column x, so a bucket (= all suffixes sharing a prefix of length D)
-// whose members lie in one column is a subset of C_x: it sits inside one run whatever the order
-// of its members, the LCP between two of its members is >= D, and the LCP between a member and
-// anything outside is < D and the same for every member.  Every minimum K2 takes ranges over at
-// least one bucket boundary, so it never sees an LCP from inside a bucket: the order inside
-// column-pure buckets and the exact LCP values inside them cannot change f.  Prefix doubling
-// may therefore stop at the first depth D at which all buckets still tied are column-pure
-// (cfg2: D = K = 21, straight after the k-mer round; MSAs with repeats across columns go on
-// until the repeats are resolved).  The members of the remaining buckets get consecutive
-// ranks in list order, PLCP = D for all but the first, and LCP at bucket heads and single
-// suffixes is found by direct comparison (< D characters).  SA, ISA and PLCP then differ from
-// the true arrays only inside those buckets; fbg_build_index and the read-back calls build the
-// full index.  tests/test_gpu_parity.py::test_sufficient_index_* compare both on gapless inputs.
-constexpr u64 LAZY_MAX_DEPTH = 96;   // direct LCP comparisons stay below this many characters
-constexpr u32 PLCP_INNER = 0x80000000u; // mark: "inside a column-pure bucket, value = depth"
-
-// *impure = 1 when two neighbours of the list share the bucket rank but not the column
-template <bool BLIST> __global__ void k1_pure_check_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, const u64 *__restrict__ bkey, int nbits, u64 na,
-                                                           const u32 *__restrict__ col, u32 *__restrict__ impure) {
-	u64 t = (u64) blockIdx.x * blockDim.x + threadIdx.x;
-	if (t + 1 >= na) return;
-	const u32 ra = BLIST ? (u32) (bkey[t] >> nbits) : lr[t], rb = BLIST ? (u32) (bkey[t + 1] >> nbits) : lr[t + 1];
-	if (ra == rb && col[lp[t]] != col[lp[t + 1]]) *impure = 1u;
-}
-// hd[t] = t + 1 at the first entry of a bucket, else 0 (inclusive max-scan: list index + 1 of the bucket's first entry)
-template <bool BLIST> __global__ void k1_pure_heads_kernel(const u32 *__restrict__ lr, const u64 *__restrict__ bkey, int nbits, u64 na, u32 *__restrict__ hd) {
-	u64 t = (u64) blockIdx.x * blockDim.x + threadIdx.x;
-	if (t >= na) return;
-	const u32 ra = BLIST ? (u32) (bkey[t] >> nbits) : lr[t];
-	const u32 rp = t ? (BLIST ? (u32) (bkey[t - 1] >> nbits) : lr[t - 1]) : 0u;
-	hd[t] = (t == 0 || ra != rp) ? (u32) t + 1u : 0u;
-}
-// consecutive ranks in list order; all but the first member are marked "inside"
-template <bool BLIST> __global__ void k1_pure_final_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, const u64 *__restrict__ bkey, int nbits, u64 na,
-                                                           const u32 *__restrict__ hd, u32 depth, u32 *__restrict__ R, u32 *__restrict__ SA, u32 *__restrict__ PLCP) {
-	u64 t = (u64) blockIdx.x * blockDim.x + threadIdx.x;
-	if (t >= na) return;
-	const u32 ra = BLIST ? (u32) (bkey[t] >> nbits) : lr[t];
-	const u32 j = (u32) t - (hd[t] - 1u);
-	const u32 p = lp[t];
-	R[p] = ra + j;
-	SA[ra + j] = p;
-	if (j) PLCP[p] = PLCP_INNER | depth;
-}
-// LCP of the sufficient index: marked positions keep the depth, every other suffix is compared
-// with its predecessor in SA (a bucket head or a single suffix: fewer than `depth` characters agree)
-__global__ void k1_lazy_lcp_kernel(const u8 *__restrict__ T, const u32 *__restrict__ SA, u64 N, u32 *__restrict__ PLCP) {
-	u64 k = (u64) blockIdx.x * blockDim.x + threadIdx.x;
-	if (k >= N) return;
-	const u32 p = SA[k];
-	const u32 v = PLCP[p];
-	if (v & PLCP_INNER) { PLCP[p] = v & ~PLCP_INNER; return; }
-	u32 len = 0;
-	if (k > 0) {
-		const u32 q = SA[k - 1];
-		while ((u64) p + len < N && (u64) q + len < N && T[p + len] == T[q + len]) len++;
-	}
-	PLCP[p] = len;
 }
 
 void k1_suffix_array(Pipeline &p) {
@@ -989,7 +1023,7 @@ void k1_suffix_array(Pipeline &p) {
 		CompactOut o;
 		o.Slp = Slp[1]; o.Slr = Slr[1]; o.Sr2 = Sr2[1];
 		o.Bkey = (u64 *) rb.k[1]; o.Bval = rb.v[1];
-		by_dict = k1_round0_dict(p, tab, K, b, key_bits0, km_grid, HR, newr, lp_out, (u64) K, nbits, o, &nS, &nB, &maxb);
+		by_dict = k1_round0_dict(p, tab, K, b, key_bits0, km_grid, HR, newr, lp_out, (u64) K, nbits, o, &nS, &nB, &maxb, lazy_ok && (u64) K <= LAZY_MAX_DEPTH);
 	}
 	if (!by_dict) d.begin(K_KMER);
 	if (by_dict) {
@@ -1046,7 +1080,7 @@ void k1_suffix_array(Pipeline &p) {
 			if (debug) fprintf(stderr, "[fbg] K1 depth %llu: tied buckets %s\n", (unsigned long long) (h / 2), *h_impure ? "span several columns" : "are all column-pure: stop");
 			if (*h_impure == 0) {
 				const u32 depth = (u32) (h / 2);
-				FBG_CUDA(cudaMemsetAsync(p.PLCP, 0, N * sizeof(u32), d.stream));
+				FBG_CUDA(cudaMemsetAsync(p.PLCP, 0xFF, N * sizeof(u32), d.stream)); // PLCP_TODO everywhere
 				if (nS) {
 					d.begin(K_DOUBLING_AUX);
 					k1_pure_heads_kernel<false><<<div_up(nS, 256), 256, 0, d.stream>>>(Slr[sc], nullptr, nbits, nS, lp_out);
@@ -1219,9 +1253,9 @@ void k1_lcp(Pipeline &p) {
 	if (!p.PLCP) p.PLCP = p.dev.palloc<u32>(N + 1);
 	if (p.index_lazy) {
 		d.begin(K_LCP);
-		k1_lazy_lcp_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(p.T, p.SA, N, p.PLCP);
+		k1_lazy_lcp_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(p.T, p.SA, p.ISA, N, p.PLCP);
 		FBG_LAUNCH_CHECK();
-		d.end((double) N * 12.0);
+		d.end((double) N * 4.0);
 		return;
 	}
 	d.ensure(N * 16 + (N / SCAN_TILE + 2) * 24 + (4u << 20));
