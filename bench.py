@@ -38,8 +38,14 @@ DOMINANT_NAMES = {
     "radix_scatter": "rs_scatter_kernel (radix scatter passes of K1)",
     "doubling_aux": "k1_cls_write_kernel + k1_dict_emit_kernel (list compaction / round-0 emission with fused rank look-up, K1)",
     "fcol": "k2_fcol_kernel (per-column f(x))",
+    "kmer": "k1_kmer_kernel<4> (every text position enters its k-mer into the open-addressing table, K1 round 0)",
+    "graph": "k4_hash / k4_group / k4_verify / k4_edges (label hash, per-block dedup, edges, K4)",
+    "pack": "k0_mask / k0_chunk_* / k0_text (bitmaps, rank tables, gap-free text, K0)",
 }
 ROOFLINE_NOTES = {
+    "kmer": "algorithmic bytes 17 B per text character (1 B text, 8 B slot + arrival number written, 8 B for the two L2 atomics' operands); "
+            "bound by the latency of dependent L2 atomics (64-bit CAS on the key, atomicAdd arrival number, atomicMin smallest member), "
+            "not by HBM streaming",
     "tile_sort": "algorithmic HBM bytes are 25 B per tied suffix per round (read lp,lr,r2; write lp,lr,cls; 4 B rank scatter); ncu DRAM "
                  "traffic is 1.05x that (no re-reads).  The kernel is bound by instruction issue (61-72 % of the issue slots busy: head "
                  "scans, prefix counts and the shared-memory sorting network of each bucket's minority), not by HBM "
@@ -323,6 +329,8 @@ def run_ours(args):
             "ms_per_step": 1000.0 * t_dev_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u8/u32", "data": "synthetic",
             "config": config_dict(name, c, {"blocks": int(nb), "score": int(score), "text_len": int(st["text_len"]), "sa_rounds": int(st["sa_rounds"]),
+                                            "index": ("sufficient index: K1 stopped at depth %d (all tied buckets column-pure)%s" % (
+                                                st["index_depth"], ", f(x) from the sorted k-mer list" if st["index_virtual"] else "")) if st["index_depth"] else "full SA / ISA / LCP",
                                             "step": "MSA -> xGFA bytes (K0..K5)", "xgfa_bytes": int(last_info[0]["n_bytes"]),
                                             "nodes": int(last_info[0]["n_nodes"]), "edges": int(last_info[0]["n_edges"]),
                                             "parallelism": "1 MSA per GPU, independent" if world > 1 else "single GPU"}),

@@ -45,7 +45,7 @@ class FbgStats(C.Structure):
     _fields_ = [("m", C.c_uint64), ("n", C.c_uint64), ("text_len", C.c_uint64), ("gaps", C.c_uint64), ("to_ignore", C.c_uint64),
                 ("sa_rounds", C.c_uint64), ("arena_peak_bytes", C.c_uint64),
                 ("kernel_ms", C.c_double * N_KERNELS), ("kernel_bytes", C.c_double * N_KERNELS), ("kernel_launches", C.c_uint64 * N_KERNELS),
-                ("dp_passes", C.c_int64), ("kmer_dict", C.c_int64), ("index_depth", C.c_int64)]
+                ("dp_passes", C.c_int64), ("kmer_dict", C.c_int64), ("index_depth", C.c_int64), ("index_virtual", C.c_int64)]
 
 
 # every symbol include/fbg_cuda.h declares (checked by tests/test_cabi.py)
@@ -342,7 +342,7 @@ class Context:
         self._check(self.lib.fbg_get_stats(self.h, C.byref(st)))
         names = kernel_names()
         return dict(m=st.m, n=st.n, text_len=st.text_len, gaps=st.gaps, to_ignore=st.to_ignore, sa_rounds=st.sa_rounds,
-                    arena_peak_bytes=st.arena_peak_bytes, dp_passes=int(st.dp_passes), kmer_dict=int(st.kmer_dict), index_depth=int(st.index_depth),
+                    arena_peak_bytes=st.arena_peak_bytes, dp_passes=int(st.dp_passes), kmer_dict=int(st.kmer_dict), index_depth=int(st.index_depth), index_virtual=int(st.index_virtual),
                     kernels={names[i]: dict(ms=st.kernel_ms[i], bytes=st.kernel_bytes[i], launches=st.kernel_launches[i]) for i in range(N_KERNELS)})
 
     def reset_stats(self):

@@ -46,6 +46,7 @@ void Pipeline::free_all() {
 	dev.pers_top = 0;
 	have_msa = have_index = have_f = have_seg = have_xgfa = false;
 	want_full_index = index_lazy = false; lazy_depth = 0;
+	index_virtual = force_arrays = false; dict_col = dict_lcp = nullptr; dict_nd = 0;
 }
 
 } // namespace fbg
@@ -114,6 +115,8 @@ int fbg_set_options(fbg_ctx *ctx, int elastic, int64_t gap_limit, const uint8_t 
 	if (!ctx) return FBG_ERR_ARG;
 	if (gap_limit < 0) { ctx->err = "Gap limit needs to be non-negative."; return FBG_ERR_ARG; }
 	Options &o = ctx->p.opt;
+	u32 old_bits[8];
+	for (int q = 0; q < 8; q++) old_bits[q] = o.ignore_bits[q];
 	o.elastic = elastic != 0; o.gap_limit = gap_limit; o.disable_tricks = disable_tricks != 0;
 	for (int q = 0; q < 8; q++) o.ignore_bits[q] = 0;
 	o.n_ignore = 0;
@@ -121,6 +124,8 @@ int fbg_set_options(fbg_ctx *ctx, int elastic, int64_t gap_limit, const uint8_t 
 	if (elastic && ignore_chars)
 		for (size_t i = 0; i < n_ignore; i++) { u8 c = ignore_chars[i]; o.ignore_bits[c >> 5] |= 1u << (c & 31); o.n_ignore++; }
 	ctx->p.have_f = ctx->p.have_seg = ctx->p.have_xgfa = false;
+	// the ignore bitmaps and the "characters to ignore" count are made by K0: pack again when the set changed
+	for (int q = 0; q < 8; q++) if (old_bits[q] != o.ignore_bits[q]) ctx->p.have_index = false;
 	return FBG_OK;
 }
 
@@ -140,13 +145,14 @@ int fbg_upload_msa_device(fbg_ctx *ctx, const void *rows, uint64_t m, uint64_t n
 
 // full = the true SA / ISA / LCP are wanted (explicit fbg_build_index, read-backs); otherwise K1 may
 // stop at the sufficient index (suffix.cu).  A sufficient index is replaced when the full one is asked for.
-static int build_index_impl(fbg_ctx *ctx, bool full) {
+static int build_index_impl(fbg_ctx *ctx, bool full, bool need_arrays = true) {
 	if (!ctx || !ctx->p.have_msa) { if (ctx) ctx->err = "no MSA uploaded"; return FBG_ERR_ARG; }
 	FBG_TRY(ctx)
 	Pipeline &p = ctx->p;
 	FBG_CUDA(cudaSetDevice(p.dev.device));
-	if (p.have_index && !(full && p.index_lazy)) return FBG_OK;
+	if (p.have_index && !(full && p.index_lazy) && !(need_arrays && p.index_virtual)) return FBG_OK;
 	if (full) p.want_full_index = true;
+	p.force_arrays = need_arrays; // need_arrays: a consumer that reads SA / ISA / PLCP follows
 	if (!p.have_index) k0_pack(p);
 	p.have_index = false;
 	k1_suffix_array(p);
@@ -160,7 +166,8 @@ int fbg_build_index(fbg_ctx *ctx) { return build_index_impl(ctx, true); }
 
 int fbg_compute_f(fbg_ctx *ctx) {
 	if (!ctx) return FBG_ERR_ARG;
-	int rc = build_index_impl(ctx, false);
+	// K2 reads the per-position arrays unless the k-mer table alone will do (fcol.cu k2_from_dict)
+	int rc = build_index_impl(ctx, false, ctx && ctx->p.opt.n_ignore > 0);
 	if (rc) return rc;
 	FBG_TRY(ctx)
 	Pipeline &p = ctx->p;
@@ -423,6 +430,7 @@ int fbg_get_stats(fbg_ctx *ctx, fbg_stats *out) {
 	out->m = p.m; out->n = p.n; out->text_len = p.N; out->gaps = p.gaps; out->to_ignore = p.toignore;
 	out->sa_rounds = p.sa_rounds; out->arena_peak_bytes = p.dev.arena_peak; out->dp_passes = p.dp_passes; out->kmer_dict = p.kmer_dict;
 	out->index_depth = p.index_lazy ? (int64_t) p.lazy_depth : 0;
+	out->index_virtual = p.index_virtual ? 1 : 0;
 	for (int k = 0; k < K_COUNT; k++) {
 		out->kernel_ms[k] = p.dev.stats[k].ms; out->kernel_bytes[k] = p.dev.stats[k].bytes; out->kernel_launches[k] = p.dev.stats[k].launches;
 	}

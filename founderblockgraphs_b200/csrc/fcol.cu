@@ -199,9 +199,79 @@ __global__ void __launch_bounds__(1024) k2_fcol_kernel(FcolArgs a) {
 	}
 }
 
+// ---- f(x) from the k-mer list of a "virtual" index (gapless MSA, every k-mer bucket in one
+// column, no ignore characters; suffix.cu).  Buckets in rank order: column c[t], LCP h[t] to the
+// bucket before (h[nd] = 0).  A run of the reference's coloured leaves is a maximal stretch of
+// neighbouring buckets of one column, and every row of bucket t gets the same
+//   g = 1 + max( min h[s..t], min h[t+1..e+1] )          (run [s, e]; fbg.cpp:1644-1656)
+// because LCP values inside a bucket exceed every h.  Rows are gapless, so rank_i(x) = x,
+// rowlen = n, lastcol = n - 1 and col(p + g - 1) = x + g - 1: fi depends on the bucket only
+// (fbg.cpp:1657-1666).  Segmented minima by max-scans of (run id, ~h): the run id grows along
+// the scan, so the maximum only ever compares values of the current run.
+__global__ void k2d_runs_kernel(const u32 *__restrict__ dcol, u32 nd, u32 *__restrict__ seg) {
+	u32 t = blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= nd) return;
+	seg[t] = (t > 0 && dcol[t - 1] != dcol[t]) ? t : 0u; // inclusive max-scan: first bucket of the run
+}
+__global__ void k2d_keys_kernel(const u32 *__restrict__ seg, const u32 *__restrict__ dlcp, u32 nd, u64 *__restrict__ fw, u64 *__restrict__ bw) {
+	u32 t = blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= nd) return;
+	fw[t] = ((u64) seg[t] << 32) | (u64) (~dlcp[t]);
+	bw[nd - 1 - t] = ((u64) (nd - seg[t]) << 32) | (u64) (~dlcp[t + 1]); // backwards the run id must grow too
+}
+__global__ void k2d_init_kernel(u32 *__restrict__ f, u64 n) {
+	u64 x = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (x < n) f[x] = (u32) x; // fbg.cpp:1618
+}
+__global__ void k2d_f_kernel(const u32 *__restrict__ dcol, const u64 *__restrict__ fw, const u64 *__restrict__ bw, u32 nd, u64 n, int tricks_off, u32 *__restrict__ f) {
+	u32 t = blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= nd) return;
+	const u64 c = dcol[t];
+	if (c >= n || (!tricks_off && c == 0)) return; // '#' and sentinel; rows without a character before x (fbg.cpp:1605-1608)
+	const u32 l = ~(u32) fw[t], r = ~(u32) bw[nd - 1 - t];
+	const u64 g = (u64) (l > r ? l : r) + 1;
+	const u64 gg = c + g;
+	const u32 fi = gg > n ? (tricks_off ? (u32) n : (u32) n - 1u) : (u32) (gg - 1);
+	atomicMax(&f[c], fi);
+}
+
+static void k2_from_dict(Pipeline &p) {
+	Dev &d = p.dev;
+	const u32 nd = (u32) p.dict_nd;
+	d.ensure((u64) nd * 20 + ((u64) nd / SCAN_TILE + 2) * 24 + (1u << 20));
+	u64 mk = d.mark();
+	u32 *seg = d.alloc<u32>(nd);
+	u64 *fw = d.alloc<u64>(nd), *bw = d.alloc<u64>(nd);
+	const u32 g = div_up(nd, 256);
+	d.begin(K_FCOL);
+	k2d_init_kernel<<<div_up(p.n, 256), 256, 0, d.stream>>>(p.f, p.n);
+	k2d_runs_kernel<<<g, 256, 0, d.stream>>>(p.dict_col, nd, seg);
+	FBG_LAUNCH_CHECK();
+	d.end((double) nd * 8.0 + (double) p.n * 4.0);
+	d.note_launches(K_FCOL, 1);
+	device_scan<OpMaxU32, false>(d, seg, seg, nd);
+	d.begin(K_FCOL);
+	k2d_keys_kernel<<<g, 256, 0, d.stream>>>(seg, p.dict_lcp, nd, fw, bw);
+	FBG_LAUNCH_CHECK();
+	d.end((double) nd * 28.0);
+	device_scan<OpMaxU64, false>(d, fw, fw, nd);
+	device_scan<OpMaxU64, false>(d, bw, bw, nd);
+	d.begin(K_FCOL);
+	k2d_f_kernel<<<g, 256, 0, d.stream>>>(p.dict_col, fw, bw, nd, p.n, p.opt.disable_tricks ? 1 : 0, p.f);
+	FBG_LAUNCH_CHECK();
+	d.end((double) nd * 24.0);
+	d.release(mk);
+	p.have_f = true;
+}
+
 void k2_compute_f(Pipeline &p) {
 	Dev &d = p.dev;
 	if (!p.f) p.f = p.dev.palloc<u32>(p.n + 1);
+	if (p.index_virtual) {
+		if (p.opt.n_ignore > 0) throw cuda_error("internal: f(x) from the k-mer list with ignore characters set");
+		k2_from_dict(p);
+		return;
+	}
 	FcolCfg gc = fcol_cfg(p.m);
 	u32 mpad = gc.mpad;
 	if (mpad > 8192) throw cuda_error("more than 8192 rows per column group is not supported by the shared-memory f(x) kernel yet");

@@ -156,6 +156,28 @@ __global__ void __launch_bounds__(256) k0_text_kernel(const u8 *__restrict__ msa
 	}
 }
 
+// gapless MSA: the text is the rows themselves with a '#' after each, position p = i (n + 1) + x.
+// One thread per four text positions, coalesced on both sides.
+__global__ void __launch_bounds__(256) k0_text_gapless_kernel(const u8 *__restrict__ msa, u64 pitch, u64 m, u64 n, u8 *__restrict__ T, u32 *__restrict__ col, u64 N) {
+	const u64 p0 = ((u64) blockIdx.x * blockDim.x + threadIdx.x) * 4;
+	if (p0 >= N) return;
+	u64 i = p0 / (n + 1), x = p0 % (n + 1);
+	u32 tv = 0, cv[4];
+#pragma unroll
+	for (int q = 0; q < 4; q++) {
+		u32 c = 0, cl = (u32) n + 1; // past the end / the final sentinel
+		if (p0 + q < N - 1) {
+			if (x < n) { c = msa[i * pitch + x]; cl = (u32) x; x++; }
+			else { c = (u32) '#'; cl = (u32) n; x = 0; i++; }
+		}
+		tv |= c << (8 * q);
+		cv[q] = cl;
+	}
+	// T and col are 256-byte aligned and hold at least N + 4 entries
+	*reinterpret_cast<u32 *>(T + p0) = tv;
+	*reinterpret_cast<uint4 *>(col + p0) = make_uint4(cv[0], cv[1], cv[2], cv[3]);
+}
+
 static void alloc_msa(Pipeline &p, u64 m, u64 n) {
 	p.free_all();
 	p.m = m; p.n = n; p.pitch = round_up(n, 32); p.W = p.pitch / 32;
@@ -183,9 +205,11 @@ void k0_pack(Pipeline &p) {
 	Dev &d = p.dev;
 	const u64 m = p.m, n = p.n, W = p.W;
 	const u64 NC = (W + CH - 1) / CH;
-	p.NG = p.dev.palloc<u32>(W * m); p.IG = p.dev.palloc<u32>(W * m);
-	p.RK = p.dev.palloc<u32>(W * m); p.NIA = p.dev.palloc<u32>(W * m);
-	p.start = p.dev.palloc<u32>(m + 1); p.rowlen = p.dev.palloc<u32>(m); p.lastcol = p.dev.palloc<u32>(m);
+	if (!p.NG) { // (packing the same MSA again, e.g. after the ignore characters changed, re-uses the arrays)
+		p.NG = p.dev.palloc<u32>(W * m); p.IG = p.dev.palloc<u32>(W * m);
+		p.RK = p.dev.palloc<u32>(W * m); p.NIA = p.dev.palloc<u32>(W * m);
+		p.start = p.dev.palloc<u32>(m + 1); p.rowlen = p.dev.palloc<u32>(m); p.lastcol = p.dev.palloc<u32>(m);
+	}
 	IgnoreSet ign;
 	for (int q = 0; q < 8; q++) ign.bits[q] = p.opt.ignore_bits[q];
 
@@ -209,11 +233,11 @@ void k0_pack(Pipeline &p) {
 	p.N = p.h_scalars[2];
 	if (p.N >= 0xFFFFFFF0ull)
 		throw cuda_error("text length " + std::to_string(p.N) + " needs 64-bit suffix indices: shard the MSA across GPUs (not in this build)");
-	p.T = p.dev.palloc<u8>(p.N + 64);
-	p.col = p.dev.palloc<u32>(p.N + 1);
+	if (!p.T) { p.T = p.dev.palloc<u8>(p.N + 64); p.col = p.dev.palloc<u32>(p.N + 8); }
 	FBG_CUDA(cudaMemsetAsync(p.T + p.N, 0, 64, d.stream)); // zero tail so k-mer windows can over-read
 	u64 wb = div_up(W, 256);
-	k0_text_kernel<<<(u32) (wb * m), 256, 0, d.stream>>>(p.msa, p.pitch, m, n, W, wb, p.RK, p.start, p.rowlen, p.T, p.col, p.N);
+	if (p.gaps == 0) k0_text_gapless_kernel<<<div_up((p.N + 3) / 4, 256), 256, 0, d.stream>>>(p.msa, p.pitch, m, n, p.T, p.col, p.N);
+	else k0_text_kernel<<<(u32) (wb * m), 256, 0, d.stream>>>(p.msa, p.pitch, m, n, W, wb, p.RK, p.start, p.rowlen, p.T, p.col, p.N);
 	FBG_LAUNCH_CHECK();
 	d.end((double) m * n * 2.0 + (double) p.N * 5.0 + (double) W * m * 4.0 * 6.0);
 	d.note_launches(K_PACK, 5);

@@ -137,6 +137,12 @@ struct Pipeline {
 	// and the read-back calls set want_full_index and get the true arrays.
 	bool want_full_index = false, index_lazy = false;
 	u64 lazy_depth = 0;
+	// ... and when the k-mer round itself is column-pure (and no ignore characters are set) K2 needs
+	// no per-position array at all: the sorted list of DISTINCT k-mers with their column and the
+	// LCP to the k-mer before is the whole index ("virtual"; fcol.cu k2_from_dict)
+	bool index_virtual = false, force_arrays = false;
+	u32 *dict_col = nullptr, *dict_lcp = nullptr; // [dict_nd], [dict_nd + 1] in rank order
+	u64 dict_nd = 0;
 	// K5: formatted xGFA bytes (own allocation, grown on demand, kept across builds)
 	u8 *xgfa = nullptr;
 	u64 xgfa_cap = 0, xgfa_len = 0;
@@ -162,7 +168,7 @@ u64 k5_scratch_need(u64 m, u64 nb, bool paths, u64 id_bytes);
 // bytes of the persistent arena one m x n MSA can need (N <= m*n + m + 1)
 static inline u64 persistent_need(u64 m, u64 n) {
 	u64 pitch = round_up(n, 32), W = pitch / 32, N = m * n + m + 1;
-	return m * pitch + 16 * W * m + 12 * (m + 1) + (N + 64) + 4 * 4 * (N + 1) + 6 * 4 * (n + 2) + 64 * 256;
+	return m * pitch + 16 * W * m + 12 * (m + 1) + (N + 64) + 4 * 4 * (N + 1) + 6 * 4 * (n + 2) + 64 * 256 + N + (1u << 19) + 64;
 }
 
 } // namespace fbg

@@ -111,6 +111,7 @@ struct Dev {
 // ------------------------------------------------------------------- scans
 struct OpSumU32 { typedef u32 T; __host__ __device__ static T id() { return 0; } __host__ __device__ static T f(T a, T b) { return a + b; } };
 struct OpSumU64 { typedef u64 T; __host__ __device__ static T id() { return 0; } __host__ __device__ static T f(T a, T b) { return a + b; } };
+struct OpMaxU64 { typedef u64 T; __host__ __device__ static T id() { return 0; } __host__ __device__ static T f(T a, T b) { return a > b ? a : b; } };
 struct OpMaxU32 { typedef u32 T; __host__ __device__ static T id() { return 0; } __host__ __device__ static T f(T a, T b) { return a > b ? a : b; } };
 // two independent 32-bit max-scans packed in one 64-bit word
 struct OpMax2x32 {

@@ -48,7 +48,12 @@ struct KmerShard { u32 bin_lo, bin_hi; int hshift; const u64 *block_off; u32 *hi
 // (slot, arrival number inside the k-mer's bucket).
 constexpr u64 KD_EMPTY = ~0ull;
 constexpr u32 KD_MAX_PROBES = 4096;
-struct KmerDict { u64 *key; u32 *cnt, *first; u32 mask; u32 *slot_of, *ord_of; u32 *overflow; };
+struct KmerDict { u64 *key; u32 *cnt, *first; u32 mask; u32 *slot_of, *ord_of; u32 *overflow; u32 *slotcol; const u32 *col; u32 *impure; };
+// MODE 5: the light form of MODE 4 for the "virtual" index of a gapless MSA (below): a position
+// only makes sure its k-mer is in the table and that the bucket lies in ONE column (the first
+// arrival leaves its column in slotcol, everybody else compares) -- in the steady state two L2
+// reads per position and no atomic.  No arrival numbers, no smallest member, nothing per position.
+constexpr u32 KD_NOCOL = 0xFFFFFFFFu;
 __device__ __forceinline__ u32 kd_hash(u64 k) {
 	k ^= k >> 33; k *= 0xff51afd7ed558ccdull; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ull; k ^= k >> 33;
 	return (u32) k;
@@ -60,9 +65,9 @@ template <int MODE> __global__ void __launch_bounds__(KM_THREADS) k1_kmer_kernel
 	__shared__ u8 stab[256];
 	__shared__ u32 ssum[32];
 	stab[threadIdx.x] = tab.code[threadIdx.x];
-	if (MODE == 4 && threadIdx.x == 0) ssum[0] = *reinterpret_cast<volatile u32 *>(dk.overflow);
+	if ((MODE == 4 || MODE == 5) && threadIdx.x == 0) ssum[0] = *reinterpret_cast<volatile u32 *>(dk.overflow) | (MODE == 5 ? *reinterpret_cast<volatile u32 *>(dk.impure) : 0u);
 	__syncthreads();
-	if (MODE == 4 && ssum[0]) return; // the table overflowed: the caller falls back to the sort
+	if ((MODE == 4 || MODE == 5) && ssum[0]) return; // the table overflowed (or, MODE 5, a bucket spans two columns): the caller falls back
 	const u64 base = (u64) blockIdx.x * KM_TILE;
 	for (u32 i = threadIdx.x; i < KM_TILE + 64; i += KM_THREADS) {
 		u64 g = base + i;
@@ -80,7 +85,7 @@ template <int MODE> __global__ void __launch_bounds__(KM_THREADS) k1_kmer_kernel
 		u64 g = base + o + it;
 		kk[it] = key;
 		if (MODE == 0) { if (g < N) { keys[g] = key; vals[g] = (u32) g; } }
-		else if (MODE == 4) {
+		else if (MODE == 4 || MODE == 5) {
 			// entered below, all items of the thread together
 		} else {
 			u32 bin = (u32) (key >> sh.hshift);
@@ -89,7 +94,7 @@ template <int MODE> __global__ void __launch_bounds__(KM_THREADS) k1_kmer_kernel
 		}
 		key = ((key << b) | sc[o + it + K]) & kmask;
 	}
-	if (MODE == 4) {
+	if (MODE == 4 || MODE == 5) {
 		// The eight table accesses of a thread are independent: first probes, arrival counters and
 		// results each go out as a batch, so a thread waits for L2 three times, not 8 x 3 times.
 		const u64 g0 = base + o;
@@ -119,6 +124,24 @@ template <int MODE> __global__ void __launch_bounds__(KM_THREADS) k1_kmer_kernel
 				}
 				sl[it] = s;
 			}
+		}
+		if (MODE == 5) {
+			u32 cc[KM_ITEMS], sv[KM_ITEMS];
+#pragma unroll
+			for (int it = 0; it < KM_ITEMS; it++) {
+				const bool ok = g0 + it < N && sl[it] != U32_MAX;
+				cc[it] = ok ? dk.col[g0 + it] : 0u;
+				sv[it] = ok ? __ldcg(dk.slotcol + sl[it]) : cc[it];
+			}
+#pragma unroll
+			for (int it = 0; it < KM_ITEMS; it++) {
+				if (g0 + it < N && sl[it] != U32_MAX) {
+					u32 v = sv[it];
+					if (v == KD_NOCOL) { v = atomicCAS(dk.slotcol + sl[it], KD_NOCOL, cc[it]); if (v == KD_NOCOL) v = cc[it]; }
+					if (v != cc[it]) *dk.impure = 1u;
+				}
+			}
+			return;
 		}
 		bool full = g0 + KM_ITEMS <= N;
 #pragma unroll
@@ -751,6 +774,22 @@ __global__ void k1_lazy_lcp_kernel(const u8 *__restrict__ T, const u32 *__restri
 	PLCP[p] = len;
 }
 
+// The "virtual" index: the distinct k-mers in rank order with the column of their bucket and the
+// LCP (in characters) to the k-mer before -- the keys hold K order-preserving b-bit codes, first
+// character in the top bits, so the LCP of two buckets is read off the XOR of their keys.
+__global__ void k1_dict_virtual_kernel(const u64 *__restrict__ skey, const u32 *__restrict__ lv, const u32 *__restrict__ slotcol,
+                                       u32 nd, int K, int b, u32 *__restrict__ dcol, u32 *__restrict__ dlcp) {
+	u32 t = blockIdx.x * blockDim.x + threadIdx.x;
+	if (t > nd) return;
+	if (t == nd) { dlcp[t] = 0; return; } // nothing follows the last bucket
+	dcol[t] = slotcol[lv[t]];
+	u32 l = 0;
+	if (t > 0) {
+		const u64 x = skey[t] ^ skey[t - 1];
+		l = (u32) ((__clzll((long long) x) - (64 - K * b)) / b);
+	}
+	dlcp[t] = l;
+}
 // Round 0 through the dictionary, speculating that every k-mer bucket is column-pure (the usual
 // case for a gapless MSA): final ranks (bucket rank + arrival number), SA entries and PLCP marks
 // straight from the table, in text order, and no S / B lists.  *impure is raised when a bucket
@@ -857,6 +896,55 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	lb.v[0] = d.alloc<u32>(ndmax); lb.v[1] = d.alloc<u32>(ndmax);
 	lb.cur = 0;
 	u32 *call = d.alloc<u32>(ndmax), *cbig = d.alloc<u32>(ndmax);
+	const u32 gc = div_up(cap, 256);
+	bool known_impure = false;
+	if (try_pure && !p.force_arrays && p.opt.n_ignore == 0) {
+		// "virtual" index: a light pass enters the k-mers and checks that every bucket lies in one
+		// column; if so, the sorted list of distinct k-mers is all K2 needs (fcol.cu k2_from_dict)
+		u32 *impure = reinterpret_cast<u32 *>(p.scalars + 12);
+		u32 *h_impure = reinterpret_cast<u32 *>(p.h_scalars + 12);
+		dk.slotcol = dk.cnt; dk.col = p.col; dk.impure = impure;
+		FBG_CUDA(cudaMemsetAsync(p.scalars + 48, 0, 4 * sizeof(u64), d.stream));
+		FBG_CUDA(cudaMemsetAsync(impure, 0, sizeof(u64), d.stream));
+		d.begin(K_KMER);
+		FBG_CUDA(cudaMemsetAsync(dk.key, 0xFF, (u64) cap * sizeof(u64), d.stream));
+		FBG_CUDA(cudaMemsetAsync(dk.slotcol, 0xFF, (u64) cap * sizeof(u32), d.stream));
+		KmerShard sh0;
+		sh0.bin_lo = 0; sh0.bin_hi = 0; sh0.hshift = 0; sh0.block_off = nullptr; sh0.hist = nullptr; sh0.block_cnt = nullptr;
+		k1_kmer_kernel<5><<<km_grid, KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, sh0, nullptr, nullptr, dk);
+		FBG_LAUNCH_CHECK();
+		d.end((double) N * (1.0 + 4.0 + 8.0 + 4.0));
+		d.begin(K_DOUBLING_AUX);
+		k1_dict_flag_kernel<<<gc, 256, 0, d.stream>>>(dk.key, cap, pos);
+		FBG_LAUNCH_CHECK();
+		d.end((double) cap * 12.0);
+		device_scan<OpSumU32, true>(d, pos, pos, cap, sc);
+		FBG_CUDA(cudaMemcpyAsync(h_sc, sc, 2 * sizeof(u32), cudaMemcpyDeviceToHost, d.stream));
+		FBG_CUDA(cudaMemcpyAsync(h_impure, impure, sizeof(u32), cudaMemcpyDeviceToHost, d.stream));
+		FBG_CUDA(cudaStreamSynchronize(d.stream));
+		const u32 ndv = h_sc[0];
+		if (h_sc[1] || ndv > ndmax) { d.release(mk); return false; }
+		if (*h_impure == 0) {
+			if (!p.dict_col) { p.dict_col = p.dev.palloc<u32>(ndmax); p.dict_lcp = p.dev.palloc<u32>((u64) ndmax + 1); }
+			d.begin(K_DOUBLING_AUX);
+			k1_dict_list_kernel<<<gc, 256, 0, d.stream>>>(dk.key, pos, cap, (u64 *) lb.k[0], lb.v[0]);
+			FBG_LAUNCH_CHECK();
+			d.end((double) cap * 12.0 + (double) ndv * 12.0);
+			const int curv = radix_sort<u64, true>(d, lb, ndv, 0, key_bits0);
+			d.begin(K_DOUBLING_AUX);
+			k1_dict_virtual_kernel<<<div_up((u64) ndv + 1, 256), 256, 0, d.stream>>>((const u64 *) lb.k[curv], lb.v[curv], dk.slotcol, ndv, K, b, p.dict_col, p.dict_lcp);
+			FBG_LAUNCH_CHECK();
+			d.end((double) ndv * 28.0);
+			FBG_CUDA(cudaStreamSynchronize(d.stream)); // the scratch is released below
+			p.index_lazy = true; p.lazy_depth = (u64) K;
+			p.index_virtual = true; p.dict_nd = ndv;
+			*nS = 0; *nB = 0; *maxb = 0;
+			d.release(mk);
+			return true;
+		}
+		known_impure = true; // the full insert below starts from an empty table
+		lb.cur = 0;
+	}
 	FBG_CUDA(cudaMemsetAsync(p.scalars + 48, 0, 4 * sizeof(u64), d.stream));
 	d.begin(K_KMER);
 	FBG_CUDA(cudaMemsetAsync(dk.key, 0xFF, (u64) cap * sizeof(u64), d.stream));
@@ -867,7 +955,6 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	k1_kmer_kernel<4><<<km_grid, KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, sh, nullptr, nullptr, dk);
 	FBG_LAUNCH_CHECK();
 	d.end((double) N * (1.0 + 8.0 + 8.0));
-	const u32 gc = div_up(cap, 256);
 	d.begin(K_DOUBLING_AUX);
 	k1_dict_flag_kernel<<<gc, 256, 0, d.stream>>>(dk.key, cap, pos);
 	FBG_LAUNCH_CHECK();
@@ -895,7 +982,7 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	k1_dict_assign_kernel<<<gn, 256, 0, d.stream>>>(lv, dk.cnt, dk.first, call, cbig, nd, 0u, info, rank_of_slot, A, sc + 4);
 	FBG_LAUNCH_CHECK();
 	d.end((double) nd * 40.0 + (double) N * 4.0);
-	if (try_pure) {
+	if (try_pure && !known_impure) {
 		// sufficient index (above k1_suffix_array): if no bucket spans two columns this is all of K1
 		u32 *impure = reinterpret_cast<u32 *>(p.scalars + 12);
 		u32 *h_impure = reinterpret_cast<u32 *>(p.h_scalars + 12);
@@ -935,7 +1022,7 @@ void k1_suffix_array(Pipeline &p) {
 	if (!p.ISA) p.ISA = p.dev.palloc<u32>(N + 1); // (a full index built after a sufficient one re-uses the arrays)
 	if (!p.SA) p.SA = p.dev.palloc<u32>(N + 1);
 	if (!p.PLCP) p.PLCP = p.dev.palloc<u32>(N + 1);
-	p.index_lazy = false; p.lazy_depth = 0;
+	p.index_lazy = false; p.lazy_depth = 0; p.index_virtual = false; p.dict_nd = 0;
 	// the sufficient index (above): gapless rows, one GPU, unless the full index was asked for
 	const bool lazy_ok = !sharded && p.gaps == 0 && !p.want_full_index && !getenv("FBG_FULL_INDEX");
 	d.ensure((sharded ? 1u : 0u) * (u64) (4u << KM_HBITS) + (1u << 20));
@@ -1251,6 +1338,7 @@ void k1_lcp(Pipeline &p) {
 	Dev &d = p.dev;
 	const u64 N = p.N;
 	if (!p.PLCP) p.PLCP = p.dev.palloc<u32>(N + 1);
+	if (p.index_virtual) return; // K2 works from the k-mer list
 	if (p.index_lazy) {
 		d.begin(K_LCP);
 		k1_lazy_lcp_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(p.T, p.SA, p.ISA, N, p.PLCP);

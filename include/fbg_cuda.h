@@ -66,6 +66,7 @@ typedef struct fbg_stats {
 	int64_t dp_passes;            /* K3: verify passes of the chunked DP (0 = one chunk, < 0 = that many passes were spent and the whole-range wavefront was needed) */
 	int64_t kmer_dict;            /* K1 round 0: 1 = through the k-mer dictionary, 0 = by sorting all suffixes (multi-GPU build, too many distinct k-mers, 64-bit k-mers) */
 	int64_t index_depth;          /* 0 = the full index; D > 0 = K1 stopped at depth D, where every bucket still tied lay in one column of a gapless MSA (the "sufficient index": same f, segmentation and graph) */
+	int64_t index_virtual;        /* 1 = that stop came straight after the k-mer round with no ignore characters set: no SA / ISA / LCP array was written at all, f(x) was computed from the sorted list of distinct k-mers (fcol.cu k2_from_dict) */
 } fbg_stats;
 
 /* index -> name for the arrays above ("pack", "kmer", "radix_hist", ...) */

@@ -523,8 +523,11 @@ def test_sufficient_index_matches_full_index(gpu_ctx, name, monkeypatch):
             ctx.set_options(elastic=elastic, gap_limit=1, ignore_chars=ign, disable_tricks=toff)
             ctx.upload(msa)
             f = ctx.compute_f()
-            depth = ctx.stats()["index_depth"]
+            st = ctx.stats()
+            depth = st["index_depth"]
             assert (depth == 0) if full else True
+            # the k-mer list alone serves K2 exactly when round 0 is pure and no ignore characters are set
+            assert st["index_virtual"] == int(depth > 0 and st["sa_rounds"] == 1 and not ign)
             try:
                 b, score = ctx.segment()
             except pkg.NoSegmentation:
@@ -553,7 +556,10 @@ def test_sufficient_index_then_full_index_on_request(gpu_ctx):
     ctx.set_options(elastic=True)
     ctx.upload(msa)
     f = ctx.compute_f()
-    assert ctx.stats()["index_depth"] == 21
+    assert ctx.stats()["index_depth"] == 21 and ctx.stats()["index_virtual"] == 1
+    # ignore characters set afterwards: K2 needs the per-position arrays, K1 is run again for them
+    ctx.set_options(elastic=True, ignore_chars=b"N")
+    assert np.array_equal(ctx.compute_f(), f) and ctx.stats()["index_virtual"] == 0 and ctx.stats()["index_depth"] == 21
     T, _, _, _ = O.text(msa)
     SA, ISA, LCP = O.sa_lcp(T)
     assert np.array_equal(ctx.sa(), SA.astype(np.uint64))
