@@ -41,8 +41,14 @@ DOMINANT_NAMES = {
     "kmer": "k1_kmer_kernel<4> (every text position enters its k-mer into the open-addressing table, K1 round 0)",
     "graph": "k4_hash / k4_group / k4_verify / k4_edges (label hash, per-block dedup, edges, K4)",
     "pack": "k0_mask / k0_chunk_* / k0_text (bitmaps, rank tables, gap-free text, K0)",
+    "dp": "k3_* (chunked guess-and-verify segmentation DP + parallel backtrack, K3)",
+    "scan": "scan_lookback_kernel (single-pass prefix scans)",
 }
 ROOFLINE_NOTES = {
+    "graph": "a group of six short kernels (label hash from the text, per-block shared-memory sort of (hash, row), byte-wise verification, "
+             "node ids, per-block edge sort/unique, gather): algorithmic bytes 2 B per text character + 60 B per (row, block) record; at "
+             "cfg2 (2.6 M records) every one of them runs for tens of microseconds, i.e. at launch / latency scale, not at HBM scale",
+    "pack": "algorithmic bytes 2 B per cell + 5 B per text character + 24 B per (row, 32-column tile)",
     "kmer": "algorithmic bytes 17 B per text character (1 B text, 8 B slot + arrival number written, 8 B for the two L2 atomics' operands); "
             "bound by the latency of dependent L2 atomics (64-bit CAS on the key, atomicAdd arrival number, atomicMin smallest member), "
             "not by HBM streaming",

@@ -1031,7 +1031,7 @@ void k1_suffix_array(Pipeline &p) {
 	// alphabet: dense order-preserving codes (sentinel 0 is always present)
 	u32 *present = d.alloc<u32>(256);
 	FBG_CUDA(cudaMemsetAsync(present, 0, 256 * sizeof(u32), d.stream));
-	d.begin(K_KMER);
+	d.begin(K_PACK); // alphabet scan: accounted with the text preparation, K_KMER is the k-mer pass alone
 	k1_presence_kernel<<<NUM_SMS * 4, 256, 0, d.stream>>>(p.T, N, present);
 	FBG_LAUNCH_CHECK();
 	d.end((double) N);
