@@ -22,7 +22,7 @@ CLI_PATH = os.path.join(_PKG, "founderblockgraph")
 
 FBG_OK, FBG_ERR_CUDA, FBG_ERR_ARG, FBG_ERR_NOSEG, FBG_ERR_UNSUPPORTED = 0, -1, -2, -3, -4
 FBG_NO_NODE = 0xFFFFFFFF
-N_KERNELS = 13
+N_KERNELS = 14
 
 _u8p = C.POINTER(C.c_uint8)
 _u32p = C.POINTER(C.c_uint32)

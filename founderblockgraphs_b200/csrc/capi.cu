@@ -51,7 +51,7 @@ void Pipeline::free_all() {
 
 } // namespace fbg
 
-static const char *KNAMES[K_COUNT] = {"pack", "kmer", "radix_hist", "radix_scatter", "scan", "doubling_aux", "lcp", "fcol", "dp", "graph", "tile_sort", "comm", "emit"};
+static const char *KNAMES[K_COUNT] = {"pack", "kmer", "radix_hist", "radix_scatter", "scan", "doubling_aux", "lcp", "fcol", "dp", "graph", "tile_sort", "comm", "emit", "edges"};
 
 #define FBG_TRY(ctx) try {
 #define FBG_CATCH(ctx)                                                         \

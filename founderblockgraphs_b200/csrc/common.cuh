@@ -50,6 +50,7 @@ enum KernelId {
 	K_TILE_SORT,     // K1: bucket-local shared-memory sort of tied suffixes
 	K_COMM,          // NCCL collectives of a multi-GPU build (rank replicas, f)
 	K_EMIT,          // K5: xGFA formatting (item lengths, offsets, byte writes)
+	K_EDGES,         // K4: node ids, per-block edge sort / unique, gather (K_GRAPH keeps hash, dedup, verification)
 	K_COUNT
 };
 

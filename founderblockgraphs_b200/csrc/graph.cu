@@ -267,14 +267,14 @@ void k4_graph(Pipeline &p, Graph *gp, bool want_node_of, XgfaJob *x) {
 	}
 	device_scan<OpSumU32, true>(d, HEAD, NIDX, R, tot_nodes);
 	FBG_CUDA(cudaMemsetAsync(EC, 0, (nb + 1) * sizeof(u32), d.stream));
-	d.begin(K_GRAPH);
+	d.begin(K_EDGES);
 	k4_nodes_kernel<<<gR, 256, 0, d.stream>>>(m, nb, REP, HEAD, NIDX, LEN, node_of, node_block, node_row, label_total);
 	if (nb > 1) k4_edges_kernel<<<grid, gc.threads, smem, d.stream>>>(m, nb, gc.mpad, gc.tpg, gc.groups, node_of, PAIRS, EC);
 	FBG_LAUNCH_CHECK();
 	d.end((double) R * 40.0);
-	d.note_launches(K_GRAPH, 1);
+	d.note_launches(K_EDGES, 1);
 	device_scan<OpSumU32, true>(d, EC, EOFF, nb, tot_edges);
-	d.begin(K_GRAPH);
+	d.begin(K_EDGES);
 	k4_edge_gather_kernel<<<gR, 256, 0, d.stream>>>(m, nb, PAIRS, EC, EOFF, es, ed);
 	FBG_LAUNCH_CHECK();
 	d.end((double) R * 12.0);

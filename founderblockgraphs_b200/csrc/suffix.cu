@@ -48,7 +48,7 @@ struct KmerShard { u32 bin_lo, bin_hi; int hshift; const u64 *block_off; u32 *hi
 // (slot, arrival number inside the k-mer's bucket).
 constexpr u64 KD_EMPTY = ~0ull;
 constexpr u32 KD_MAX_PROBES = 4096;
-struct KmerDict { u64 *key; u32 *cnt, *first; u32 mask; u32 *slot_of, *ord_of; u32 *overflow; u32 *slotcol; const u32 *col; u32 *impure; };
+struct KmerDict { u64 *key; u32 *cnt, *first; u32 mask; u32 *slot_of, *ord_of; u32 *overflow; u32 *slotcol; const u32 *col; u32 *impure; u32 ncol1; };
 // MODE 5: the light form of MODE 4 for the "virtual" index of a gapless MSA (below): a position
 // only makes sure its k-mer is in the table and that the bucket lies in ONE column (the first
 // arrival leaves its column in slotcol, everybody else compares) -- in the steady state two L2
@@ -126,11 +126,15 @@ template <int MODE> __global__ void __launch_bounds__(KM_THREADS) k1_kmer_kernel
 			}
 		}
 		if (MODE == 5) {
+			// gapless rows: text position p = i (n + 1) + x, so the column needs no look-up
+			// (ncol1 = n + 1; '#' -> n like the col array; the final sentinel -> n + 1)
 			u32 cc[KM_ITEMS], sv[KM_ITEMS];
+			u32 xc = (u32) (g0 % dk.ncol1);
 #pragma unroll
 			for (int it = 0; it < KM_ITEMS; it++) {
 				const bool ok = g0 + it < N && sl[it] != U32_MAX;
-				cc[it] = ok ? dk.col[g0 + it] : 0u;
+				cc[it] = g0 + it == N - 1 ? dk.ncol1 : xc;
+				xc = xc + 1 == dk.ncol1 ? 0u : xc + 1;
 				sv[it] = ok ? __ldcg(dk.slotcol + sl[it]) : cc[it];
 			}
 #pragma unroll
@@ -903,7 +907,7 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 		// column; if so, the sorted list of distinct k-mers is all K2 needs (fcol.cu k2_from_dict)
 		u32 *impure = reinterpret_cast<u32 *>(p.scalars + 12);
 		u32 *h_impure = reinterpret_cast<u32 *>(p.h_scalars + 12);
-		dk.slotcol = dk.cnt; dk.col = p.col; dk.impure = impure;
+		dk.slotcol = dk.cnt; dk.col = p.col; dk.impure = impure; dk.ncol1 = (u32) p.n + 1u;
 		FBG_CUDA(cudaMemsetAsync(p.scalars + 48, 0, 4 * sizeof(u64), d.stream));
 		FBG_CUDA(cudaMemsetAsync(impure, 0, sizeof(u64), d.stream));
 		d.begin(K_KMER);
@@ -913,7 +917,7 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 		sh0.bin_lo = 0; sh0.bin_hi = 0; sh0.hshift = 0; sh0.block_off = nullptr; sh0.hist = nullptr; sh0.block_cnt = nullptr;
 		k1_kmer_kernel<5><<<km_grid, KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, sh0, nullptr, nullptr, dk);
 		FBG_LAUNCH_CHECK();
-		d.end((double) N * (1.0 + 4.0 + 8.0 + 4.0));
+		d.end((double) N * (1.0 + 8.0 + 4.0));
 		d.begin(K_DOUBLING_AUX);
 		k1_dict_flag_kernel<<<gc, 256, 0, d.stream>>>(dk.key, cap, pos);
 		FBG_LAUNCH_CHECK();

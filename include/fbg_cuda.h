@@ -54,7 +54,7 @@ typedef struct fbg_graph {
 
 /* Per-kernel accounting for the roofline: accumulated CUDA-event milliseconds,
  * algorithmic bytes (DESIGN.md states the per-unit figures) and launch counts. */
-#define FBG_N_KERNELS 13
+#define FBG_N_KERNELS 14
 typedef struct fbg_stats {
 	uint64_t m, n, text_len;      /* N = non-gap cells + m + 1 */
 	uint64_t gaps, to_ignore;     /* fbg.cpp:1858-1859 */
