@@ -38,7 +38,8 @@ DOMINANT_NAMES = {
     "radix_scatter": "rs_scatter_kernel (radix scatter passes of K1)",
     "doubling_aux": "k1_cls_write_kernel + k1_dict_emit_kernel (list compaction / round-0 emission with fused rank look-up, K1)",
     "fcol": "k2_fcol_kernel (per-column f(x))",
-    "kmer": "k1_kmer_kernel<4> (every text position enters its k-mer into the open-addressing table, K1 round 0)",
+    "kmer": "k1_kmer_kernel<5> (virtual index: every text position looks its k-mer up in / enters it into the open-addressing table "
+            "and checks the slot's column, K1 round 0; <4>, the full insert, when per-position ranks are needed)",
     "graph": "k4_hash / k4_group / k4_verify (label hash, per-block dedup, byte-wise verification, K4)",
     "edges": "k4_nodes / k4_edges / k4_edge_gather (node ids, per-block edge sort/unique, K4)",
     "pack": "k0_mask / k0_chunk_* / k0_text (bitmaps, rank tables, gap-free text, K0)",
@@ -52,8 +53,10 @@ ROOFLINE_NOTES = {
     "pack": "algorithmic bytes 2 B per cell + 5 B per text character + 24 B per (row, 32-column tile)",
     "kmer": "algorithmic bytes 17 B per text character (1 B text, 8 B slot + arrival number written, 8 B for the two L2 atomics' operands); "
             "with the virtual index (gapless MSA, cfg2) the light form <5> runs: 13 B per text character (1 B text, the 8 B key word and the "
-            "4 B column word of its table slot); ncu: DRAM 6 % of peak, L2 42 %, issue slots 21 % busy, 37 % achieved occupancy - the kernel waits "
-            "for random L2 sectors of the 4 M-slot table (long-scoreboard stalls), not for HBM; the full form <4> adds three L2 atomics per position",
+            "4 B column word of its table slot, requested from L2); ncu: 79 MB of DRAM traffic per launch against 390 MB requested - the 50 MB "
+            "table stays in the 126 MB L2, only the text streams from HBM - DRAM 2 % of peak, L2 41 %, issue slots 22 % busy, 37 % achieved "
+            "occupancy (58 registers): the kernel waits for random L2 sectors of the 4 M-slot table (long-scoreboard stalls), not for HBM; "
+            "the full form <4> adds three L2 atomics per position",
     "tile_sort": "algorithmic HBM bytes are 25 B per tied suffix per round (read lp,lr,r2; write lp,lr,cls; 4 B rank scatter); ncu DRAM "
                  "traffic is 1.05x that (no re-reads).  The kernel is bound by instruction issue (61-72 % of the issue slots busy: head "
                  "scans, prefix counts and the shared-memory sorting network of each bucket's minority), not by HBM "
