@@ -211,6 +211,12 @@ def run_reference_arm(args):
 
 
 def run_ours(args):
+    # rank 0 prints ONE JSON line on stdout: everything else that writes to file descriptor 1 (NCCL's
+    # "NCCL version ..." banner when NCCL_DEBUG is set, library chatter) is sent to stderr, and the
+    # line goes out through a saved copy of the original descriptor
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     import torch
     import torch.distributed as dist
     import founderblockgraphs_b200 as pkg
@@ -367,7 +373,7 @@ def run_ours(args):
         }
         if sharded:
             line["sharded_single_msa"] = sharded
-        print(json.dumps(line))
+        os.write(real_stdout, (json.dumps(line) + "\n").encode())
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
