@@ -12,6 +12,11 @@
 // start indices, so the new rank of a suffix is its old rank plus the offset of
 // its sub-bucket.  LCP is computed at irreducible positions only (BWT[k] !=
 // BWT[k-1]) by direct comparison and filled with PLCP[p] = max_{q<=p,irr}(PLCP[q]+q) - p.
+//
+// On a gapless MSA the later stages need less than that: prefix doubling stops as soon as every
+// tied bucket lies in one column ("sufficient index"), and when the k-mer round itself is
+// column-pure no per-position array is written at all ("virtual index"; see the block above
+// k1_round0_dict and fcol.cu k2_from_dict).  fbg_build_index and the read-backs build the full arrays.
 #include "pipeline.cuh"
 #include "tilesort.cuh"
 #include "dist.cuh"
