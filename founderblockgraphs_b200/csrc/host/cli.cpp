@@ -187,10 +187,12 @@ int main(int argc, char **argv) {
 	if (fbg_set_options(ctx, a.elastic, a.gap_limit, (const uint8_t *) a.ignore.data(), a.ignore.size(), a.tricks_off) != FBG_OK) return fail_cuda(ctx, "options");
 	if (fbg_upload_msa(ctx, msa.rows, msa.m, msa.n) != FBG_OK) return fail_cuda(ctx, "MSA upload");
 	fprintf(stderr, "Building the MSA index (suffix array, LCP) on the GPU.\n");
-	if (fbg_build_index(ctx) != FBG_OK) return fail_cuda(ctx, "index construction");
+	// index + f(x) in one call: the library then builds only as much of the index as f(x) can
+	// depend on (on gapless input far less than the full SA / ISA / LCP an explicit fbg_build_index gives)
+	if (fbg_compute_f(ctx) != FBG_OK) return fail_cuda(ctx, "index construction");
 	fbg_stats st;
 	fbg_get_stats(ctx, &st);
-	lap("upload + index");
+	lap("upload + index + f");
 	fprintf(stderr, "MSA index construction complete, index requires %g MiB.\n", (double) st.text_len * 17.0 / (1024.0 * 1024.0));
 
 	uint64_t nb = 0, score = 0;
@@ -216,7 +218,7 @@ int main(int argc, char **argv) {
 	}
 	bnd.resize(nb);
 	if (fbg_get_boundaries(ctx, bnd.data()) != FBG_OK) return fail_cuda(ctx, "boundaries");
-	lap("f + segmentation");
+	lap("segmentation");
 	// Graph and xGFA bytes: formatted on the device and streamed to the file (K5, default), or --
 	// FBG_HOST_WRITER=1 -- graph arrays copied out and formatted by the host writer.  Same bytes.
 	const bool host_writer = getenv("FBG_HOST_WRITER") != nullptr;
