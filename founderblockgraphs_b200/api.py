@@ -513,4 +513,8 @@ def main(argv, **kw):
     """Runs the compiled drop-in CLI (same flags as the reference executable)."""
     if not os.path.exists(CLI_PATH):
         raise ImportError(CLI_PATH + " is missing: build with make -C founderblockgraphs_b200/csrc")
+    # the executable is a build artefact (not tracked): refuse one that predates its sources or the ABI header
+    for src in (os.path.join(_PKG, "csrc", "host", "cli.cpp"), os.path.join(os.path.dirname(_PKG), "include", "fbg_cuda.h")):
+        if os.path.exists(src) and os.path.getmtime(src) > os.path.getmtime(CLI_PATH):
+            raise ImportError(CLI_PATH + " is older than " + src + ": rebuild with make -C founderblockgraphs_b200/csrc")
     return subprocess.run([CLI_PATH] + list(argv), **kw)

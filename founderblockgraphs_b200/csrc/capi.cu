@@ -56,6 +56,7 @@ static const char *KNAMES[K_COUNT] = {"pack", "kmer", "radix_hist", "radix_scatt
 #define FBG_TRY(ctx) try {
 #define FBG_CATCH(ctx)                                                         \
 	}                                                                          \
+	catch (const fbg::unsupported_error &e) { (ctx)->err = e.what(); return FBG_ERR_UNSUPPORTED; } \
 	catch (const fbg::cuda_error &e) { (ctx)->err = e.what(); cudaGetLastError(); return FBG_ERR_CUDA; } \
 	catch (const std::exception &e) { (ctx)->err = e.what(); return FBG_ERR_CUDA; }
 
@@ -131,7 +132,9 @@ int fbg_set_options(fbg_ctx *ctx, int elastic, int64_t gap_limit, const uint8_t 
 
 static int upload_common(fbg_ctx *ctx, const void *rows, uint64_t m, uint64_t n, bool device) {
 	if (!ctx || !rows || m == 0 || n == 0) { if (ctx) ctx->err = "empty MSA"; return FBG_ERR_ARG; }
-	if (m >= (1u << 24)) { ctx->err = "more than 2^24 rows"; return FBG_ERR_UNSUPPORTED; }
+	// limits of this build, reported before any work is done (DESIGN.md "Limits")
+	if (m > FBG_MAX_ROWS) { ctx->err = "more than " + std::to_string(FBG_MAX_ROWS) + " rows: the per-column sorts of K2 / K4 run in shared memory"; return FBG_ERR_UNSUPPORTED; }
+	if (n >= 0xFFFFFFF0ull) { ctx->err = "more than 2^32 - 16 columns"; return FBG_ERR_UNSUPPORTED; }
 	FBG_TRY(ctx)
 	FBG_CUDA(cudaSetDevice(ctx->p.dev.device));
 	ctx->p.have_xgfa = false;
@@ -151,7 +154,7 @@ static int build_index_impl(fbg_ctx *ctx, bool full, bool need_arrays = true) {
 	Pipeline &p = ctx->p;
 	FBG_CUDA(cudaSetDevice(p.dev.device));
 	if (p.have_index && !(full && p.index_lazy) && !(need_arrays && p.index_virtual)) return FBG_OK;
-	if (full) p.want_full_index = true;
+	p.want_full_index = full; // per call: a later rebuild on this MSA (new ignore set) may take the sufficient index again
 	p.force_arrays = need_arrays; // need_arrays: a consumer that reads SA / ISA / PLCP follows
 	if (!p.have_index) k0_pack(p);
 	p.have_index = false;
@@ -174,10 +177,9 @@ int fbg_compute_f(fbg_ctx *ctx) {
 	if (p.have_f) return FBG_OK;
 	// non-elastic: v[j] is defined through f without the row-end tricks and without
 	// ignore characters (fbg.cpp:552-611 has neither)
-	bool saved = p.opt.disable_tricks;
+	struct Restore { bool &ref, val; ~Restore() { ref = val; } } restore{p.opt.disable_tricks, p.opt.disable_tricks}; // also when K2 throws
 	if (!p.opt.elastic) p.opt.disable_tricks = true;
 	k2_compute_f(p);
-	p.opt.disable_tricks = saved;
 	FBG_CATCH(ctx)
 	return FBG_OK;
 }
@@ -228,6 +230,8 @@ int fbg_build_graph(fbg_ctx *ctx, int want_paths, fbg_graph *out) {
 	GraphHolder *h = new GraphHolder();
 	try {
 		k4_graph(ctx->p, &h->g, want_paths != 0);
+	} catch (const fbg::unsupported_error &e) {
+		ctx->err = e.what(); delete h; return FBG_ERR_UNSUPPORTED;
 	} catch (const std::exception &e) {
 		ctx->err = e.what(); cudaGetLastError(); delete h; return FBG_ERR_CUDA;
 	}
@@ -428,7 +432,7 @@ int fbg_get_stats(fbg_ctx *ctx, fbg_stats *out) {
 	p.dev.resolve();
 	std::memset(out, 0, sizeof *out);
 	out->m = p.m; out->n = p.n; out->text_len = p.N; out->gaps = p.gaps; out->to_ignore = p.toignore;
-	out->sa_rounds = p.sa_rounds; out->arena_peak_bytes = p.dev.arena_peak; out->dp_passes = p.dp_passes; out->kmer_dict = p.kmer_dict;
+	out->sa_rounds = p.sa_rounds; out->arena_peak_bytes = p.dev.arena_peak + p.dev.pers_top; out->dp_passes = p.dp_passes; out->kmer_dict = p.kmer_dict;
 	out->index_depth = p.index_lazy ? (int64_t) p.lazy_depth : 0;
 	out->index_virtual = p.index_virtual ? 1 : 0;
 	for (int k = 0; k < K_COUNT; k++) {

@@ -19,6 +19,11 @@ struct cuda_error : std::runtime_error {
 	explicit cuda_error(const std::string &s) : std::runtime_error(s) {}
 };
 
+// a size or shape this build does not handle (reported as FBG_ERR_UNSUPPORTED, not as a CUDA failure)
+struct unsupported_error : std::runtime_error {
+	explicit unsupported_error(const std::string &s) : std::runtime_error(s) {}
+};
+
 #define FBG_CUDA(expr)                                                                       \
 	do {                                                                                     \
 		cudaError_t e__ = (expr);                                                            \

@@ -274,7 +274,7 @@ void k2_compute_f(Pipeline &p) {
 	}
 	FcolCfg gc = fcol_cfg(p.m);
 	u32 mpad = gc.mpad;
-	if (mpad > 8192) throw cuda_error("more than 8192 rows per column group is not supported by the shared-memory f(x) kernel yet");
+	if (mpad > 8192) throw unsupported_error("more than 8192 rows is not supported by the shared-memory f(x) kernel");
 	FcolArgs a;
 	a.NG = p.NG; a.IG = p.IG; a.RK = p.RK; a.NIA = p.NIA; a.start = p.start; a.rowlen = p.rowlen; a.lastcol = p.lastcol;
 	a.col = p.col; a.ISA = p.ISA; a.SA = p.SA; a.PLCP = p.PLCP; a.f = p.f;

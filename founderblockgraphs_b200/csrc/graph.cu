@@ -221,9 +221,9 @@ static void d2h(u64 *dst, const u32 *src, u64 count, u64 *wide, cudaStream_t s) 
 void k4_graph(Pipeline &p, Graph *gp, bool want_node_of, XgfaJob *x) {
 	Dev &d = p.dev;
 	const u64 m = p.m, nb = p.nb, R = m * nb;
-	if (R >= 0xFFFFFFF0ull) throw cuda_error("more than 2^32 (row,block) records");
+	if (R >= 0xFFFFFFF0ull) throw unsupported_error("more than 2^32 (row,block) records");
 	GroupCfg gc = group_cfg(m);
-	if (gc.mpad > 8192) throw cuda_error("more than 8192 rows is not supported by the shared-memory dedup kernel yet");
+	if (gc.mpad > 8192) throw unsupported_error("more than 8192 rows is not supported by the shared-memory dedup kernel");
 	u64 id_bytes = 0;
 	if (x && x->paths) for (u64 i = 0; i < m; i++) id_bytes += strlen(x->ids[i]);
 	d.ensure(R * 72 + (nb + 1) * 12 + (R / SCAN_TILE + 2) * 24 + (4u << 20) + (x ? k5_scratch_need(m, nb, x->paths, id_bytes) : 0));

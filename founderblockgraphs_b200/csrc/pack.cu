@@ -232,7 +232,8 @@ void k0_pack(Pipeline &p) {
 	p.gaps = m * n - nongap;
 	p.N = p.h_scalars[2];
 	if (p.N >= 0xFFFFFFF0ull)
-		throw cuda_error("text length " + std::to_string(p.N) + " needs 64-bit suffix indices: shard the MSA across GPUs (not in this build)");
+		throw unsupported_error("text length " + std::to_string(p.N) + " needs suffix indices wider than 32 bits, which this build does not have (single-GPU and sharded alike); "
+		                        "--heuristic-subset=ROWNUM builds the graph from row chunks that fit");
 	if (!p.T) { p.T = p.dev.palloc<u8>(p.N + 64); p.col = p.dev.palloc<u32>(p.N + 8); }
 	FBG_CUDA(cudaMemsetAsync(p.T + p.N, 0, 64, d.stream)); // zero tail so k-mer windows can over-read
 	u64 wb = div_up(W, 256);

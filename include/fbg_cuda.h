@@ -29,7 +29,13 @@ extern "C" {
 #define FBG_ERR_CUDA (-1)       /* CUDA runtime / device failure */
 #define FBG_ERR_ARG (-2)        /* bad argument or call order */
 #define FBG_ERR_NOSEG (-3)      /* "No proper segmentation exists." / "No valid segmentation found!" */
-#define FBG_ERR_UNSUPPORTED (-4)
+#define FBG_ERR_UNSUPPORTED (-4)  /* a size this build does not handle; fbg_last_error() says which */
+
+/* Limits of this build, checked by fbg_upload_msa before any work is done (FBG_ERR_UNSUPPORTED):
+ * rows (the per-column sorts of K2 / K4 run in shared memory; the reference has no row limit,
+ * fbg.cpp:1610-1693), and text length N = non-gap cells + rows + 1 < 2^32 - 16 (32-bit suffix
+ * indices; the reference switches to divsufsort64, construct_sa.hpp:183-190). */
+#define FBG_MAX_ROWS 8192
 
 #define FBG_NO_NODE UINT32_MAX  /* node_of[] entry of a row whose label in that block is empty */
 
@@ -59,7 +65,7 @@ typedef struct fbg_stats {
 	uint64_t m, n, text_len;      /* N = non-gap cells + m + 1 */
 	uint64_t gaps, to_ignore;     /* fbg.cpp:1858-1859 */
 	uint64_t sa_rounds;           /* prefix-doubling rounds incl. the k-mer round */
-	uint64_t arena_peak_bytes;
+	uint64_t arena_peak_bytes;    /* device bytes in use: per-MSA arrays + peak of the scratch arena */
 	double kernel_ms[FBG_N_KERNELS];
 	double kernel_bytes[FBG_N_KERNELS];
 	uint64_t kernel_launches[FBG_N_KERNELS];

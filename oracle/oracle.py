@@ -238,7 +238,7 @@ def run_reference(fasta_path: str, args, timeout: float = 600.0):
         inp = os.path.join(td, "in.fasta")
         out = os.path.join(td, "out.xgfa")
         shutil.copyfile(fasta_path, inp)
-        pr = subprocess.run([REF_BIN, "--input", inp, "--output", out] + list(args), capture_output=True, timeout=timeout)
+        pr = subprocess.run([REF_BIN, "--input", inp, "--output", out] + list(args), capture_output=True, timeout=timeout, cwd=td)  # sdsl drops its cache files in the cwd
         data = open(out, "rb").read() if os.path.exists(out) else None
         return pr.returncode, data, pr.stderr.decode("utf8", "replace")
 
@@ -252,7 +252,7 @@ def run_harness(fasta_path: str, mode: str, args=(), timeout: float = 600.0, wan
         cmd = [HARNESS_BIN, "--mode", mode, "--input", inp] + list(args)
         if want_output:
             cmd += ["--output", out]
-        pr = subprocess.run(cmd, capture_output=True, timeout=timeout)
+        pr = subprocess.run(cmd, capture_output=True, timeout=timeout, cwd=td)  # sdsl drops its cache files in the cwd
         res = {"returncode": pr.returncode}
         for line in pr.stdout.decode().splitlines():
             parts = line.split()
