@@ -199,8 +199,12 @@ template <int MODE> __global__ void __launch_bounds__(KM_THREADS) k1_kmer_kernel
 // rank plus its offset inside the (sorted) bucket.  All rank look-ups R[p+h] of a
 // round are done by the compaction kernel of the round before, i.e. before any
 // rank of the round changes.
-constexpr u32 BSMALL = 8192;     // largest bucket the tile path takes (CAP_max / 2)
-constexpr u32 CLS_DROP = 0, CLS_SMALL = 1, CLS_BIG = 2;
+constexpr u32 BSMALL = 8192;     // largest bucket the shared-memory paths take (CAP_max / 2)
+// ... and, when the M list is in use, the S list only keeps buckets below MID_MIN: buckets of
+// MID_MIN .. BSMALL suffixes go to the M list (same record format), where one CTA streams one
+// bucket (k1_bucket_sort_kernel) instead of sorting a window of whole buckets in shared memory
+constexpr u32 MID_MIN = 1024;
+constexpr u32 CLS_DROP = 0, CLS_SMALL = 1, CLS_BIG = 2, CLS_MID = 3, CLS_NONE = 0xFF;
 
 // HH[t] = (bucket head index << 32) | sub-bucket head index, 0 where not a head;
 // HR[na-1-t] = na - t at sub-bucket heads (a max-scan of HR gives the next head)
@@ -217,7 +221,7 @@ __global__ void k1_heads_kernel(const u64 *__restrict__ keys, u64 na, int hi_shi
 
 // new rank = bucket rank + (sub-head index - bucket-head index); class by sub-bucket size
 __global__ void __launch_bounds__(256) k1_update_kernel(const u64 *__restrict__ keys, const u32 *__restrict__ vals, const u64 *__restrict__ HH, const u32 *__restrict__ HR,
-                                                        u64 na, int hi_shift, u32 rank_off, u32 *__restrict__ R, u32 *__restrict__ SA, u32 *__restrict__ newr, u8 *__restrict__ cls, u32 *__restrict__ maxb) {
+                                                        u64 na, int hi_shift, u32 rank_off, u32 mid_min, u32 *__restrict__ R, u32 *__restrict__ SA, u32 *__restrict__ newr, u8 *__restrict__ cls, u32 *__restrict__ maxb) {
 	__shared__ u32 smax[8];
 	u64 t = (u64) blockIdx.x * blockDim.x + threadIdx.x;
 	u32 small_size = 0;
@@ -229,7 +233,7 @@ __global__ void __launch_bounds__(256) k1_update_kernel(const u64 *__restrict__ 
 		u32 nr = base + (hs - hb);
 		u32 nh = (t + 1 < na) ? (u32) na - HR[na - 2 - t] : (u32) na; // HR scanned: 0 = no head after t
 		u32 size = nh - hs;
-		u32 c = size == 1 ? CLS_DROP : (size <= BSMALL ? CLS_SMALL : CLS_BIG);
+		u32 c = size == 1 ? CLS_DROP : (size < mid_min ? CLS_SMALL : (size <= BSMALL ? CLS_MID : CLS_BIG)); // mid_min = BSMALL + 1: no M list
 		const u32 pv = vals[t];
 		R[pv] = nr;
 		if (c == CLS_DROP) SA[nr] = pv; // a suffix alone in its bucket has its final rank: the SA entry is written as it leaves
@@ -278,63 +282,68 @@ __global__ void k1_ordered_write_kernel(const u64 *__restrict__ HH, const u32 *_
 	Slp[q] = p; Slr[q] = newr[t]; Sr2[q] = pn < N ? R[pn] : 0u;
 }
 
-__device__ __forceinline__ u64 cls_count16(uint4 v) {
-	// bytes equal to 1 -> low word, equal to 2 -> high word
-	u32 w[4] = {v.x, v.y, v.z, v.w};
-	u32 s = 0, b = 0;
-#pragma unroll
-	for (int q = 0; q < 4; q++) {
-		u32 one = w[q] & 0x01010101u, two = (w[q] >> 1) & 0x01010101u;
-		s += __popc(one & ~two);
-		b += __popc(two & ~one);
-	}
-	return ((u64) b << 32) | s;
+// number of bytes of w equal to v (v < 128 or CLS_NONE)
+__device__ __forceinline__ u32 bytes_equal(u32 w, u32 v) {
+	const u32 x = w ^ (v * 0x01010101u);
+	return (u32) __popc(~(((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x) & 0x80808080u);
+}
+__device__ __forceinline__ u64 cls_count16(uint4 v, u32 ca, u32 cb) {
+	// bytes equal to class ca -> low word, equal to class cb -> high word
+	const u32 a = bytes_equal(v.x, ca) + bytes_equal(v.y, ca) + bytes_equal(v.z, ca) + bytes_equal(v.w, ca);
+	const u32 b = bytes_equal(v.x, cb) + bytes_equal(v.y, cb) + bytes_equal(v.z, cb) + bytes_equal(v.w, cb);
+	return ((u64) b << 32) | a;
 }
 
-__global__ void __launch_bounds__(CP_THREADS) k1_cls_count_kernel(const u8 *__restrict__ cls, u64 na, int skip_small, u64 *__restrict__ partial) {
+// One compaction moves the survivors of two classes (ca, cb; CLS_NONE = unused) of one sorted list into
+// the next round's lists.
+__global__ void __launch_bounds__(CP_THREADS) k1_cls_count_kernel(const u8 *__restrict__ cls, u64 na, u32 ca, u32 cb, u64 *__restrict__ partial) {
 	__shared__ u64 sm[32];
 	u64 base = (u64) blockIdx.x * CP_TILE + (u64) threadIdx.x * CP_ITEMS;
 	u64 c = 0;
-	if (base + CP_ITEMS <= na) c = cls_count16(*reinterpret_cast<const uint4 *>(cls + base));
-	else for (u64 i = base; i < na; i++) { u8 v = cls[i]; c += v == CLS_SMALL ? 1ull : (v == CLS_BIG ? (1ull << 32) : 0ull); }
-	if (skip_small) c &= 0xFFFFFFFF00000000ull;
+	if (base + CP_ITEMS <= na) c = cls_count16(*reinterpret_cast<const uint4 *>(cls + base), ca, cb);
+	else for (u64 i = base; i < na; i++) { u8 v = cls[i]; c += v == ca ? 1ull : (v == cb ? (1ull << 32) : 0ull); }
 	u64 tot;
 	block_excl_scan<OpSumU64>(c, sm, &tot);
 	if (threadIdx.x == 0) partial[blockIdx.x] = tot;
 }
 
+constexpr int TGT_S = 0, TGT_M = 1, TGT_B = 2;
 struct CompactOut {
 	u32 *Slp, *Slr, *Sr2;  // next S list
+	u32 *Mlp, *Mlr, *Mr2;  // next M list (same records)
 	u64 *Bkey; u32 *Bval;  // next B list
 };
 
-// partial: exclusive-scanned per-tile (small | big << 32) counts; base: device word with
-// the offsets this call appends at (same packing), or null for 0.  A warp owns 512
+// partial: exclusive-scanned per-tile (class a | class b << 32) counts; base_a / base_b: device words with
+// the offsets this call appends at in its two target lists (null = 0).  A warp owns 512
 // consecutive entries and walks them 32 at a time: coalesced reads, ballot/popc ranks,
 // compacted (hence nearly coalesced) writes.
 __global__ void __launch_bounds__(CP_THREADS, CP_MINB) k1_cls_write_kernel(const u8 *__restrict__ cls, const u32 *__restrict__ lp, const u32 *__restrict__ lr, u64 na,
-                                                                  const u64 *__restrict__ partial, const u64 *__restrict__ base, int skip_small,
+                                                                  const u64 *__restrict__ partial, const u64 *__restrict__ base_a, const u64 *__restrict__ base_b,
+                                                                  u32 ca, u32 cb, int tgt_a, int tgt_b,
                                                                   const u32 *__restrict__ R, u64 hnext, u64 N, int nbits, CompactOut o) {
 	__shared__ u64 wtot[CP_THREADS / 32];
 	const u32 w = threadIdx.x >> 5, l = threadIdx.x & 31;
 	const u64 w0 = (u64) blockIdx.x * CP_TILE + (u64) w * (32 * CP_ITEMS);
 	// pass 1: this warp's counts
-	u32 cs = 0, cb = 0;
+	u32 cs = 0, cbn = 0;
 	u8 c[CP_ITEMS];
 #pragma unroll
 	for (int i = 0; i < CP_ITEMS; i++) {
 		u64 t = w0 + (u64) i * 32 + l;
 		u8 v = t < na ? cls[t] : (u8) CLS_DROP;
-		if (skip_small && v == CLS_SMALL) v = (u8) CLS_DROP;
+		v = v == ca ? (u8) 1 : (v == cb ? (u8) 2 : (u8) 0); // 1 -> target a, 2 -> target b, 0 -> not moved by this call
 		c[i] = v;
-		cs += __popc(__ballot_sync(0xffffffffu, v == CLS_SMALL));
-		cb += __popc(__ballot_sync(0xffffffffu, v == CLS_BIG));
+		cs += __popc(__ballot_sync(0xffffffffu, v == 1));
+		cbn += __popc(__ballot_sync(0xffffffffu, v == 2));
 	}
-	if (l == 0) wtot[w] = ((u64) cb << 32) | cs;
+	if (l == 0) wtot[w] = ((u64) cbn << 32) | cs;
 	__syncthreads();
-	u64 ex = partial[blockIdx.x] + (base ? *base : 0ull);
+	u64 ex = partial[blockIdx.x];
 	for (u32 ww = 0; ww < w; ww++) ex += wtot[ww];
-	u32 qs = (u32) ex, qb = (u32) (ex >> 32);
+	u32 qa = (u32) ex + (base_a ? (u32) *base_a : 0u), qb = (u32) (ex >> 32) + (base_b ? (u32) *base_b : 0u);
+	u32 *alp = tgt_a == TGT_S ? o.Slp : o.Mlp, *alr = tgt_a == TGT_S ? o.Slr : o.Mlr, *ar2 = tgt_a == TGT_S ? o.Sr2 : o.Mr2;
+	u32 *blp = tgt_b == TGT_S ? o.Slp : o.Mlp, *blr = tgt_b == TGT_S ? o.Slr : o.Mlr, *br2 = tgt_b == TGT_S ? o.Sr2 : o.Mr2;
 	// pass 2, CP_CHUNK items at a time: their loads, then their rank look-ups, then the writes, each as
 	// one batch (the output arrays may alias the inputs as far as the compiler knows, so it would
 	// not reorder an item's loads over the stores of the item before)
@@ -345,22 +354,33 @@ __global__ void __launch_bounds__(CP_THREADS, CP_MINB) k1_cls_write_kernel(const
 		for (int k = 0; k < CP_CHUNK; k++) {
 			const u64 t = w0 + (u64) (i0 + k) * 32 + l;
 			pp[k] = 0; rr[k] = 0;
-			if (c[i0 + k] != CLS_DROP) { pp[k] = lp[t]; rr[k] = lr[t]; }
+			if (c[i0 + k]) { pp[k] = lp[t]; rr[k] = lr[t]; }
 		}
 #pragma unroll
 		for (int k = 0; k < CP_CHUNK; k++) {
 			const u64 q = (u64) pp[k] + hnext;
-			r2[k] = (c[i0 + k] != CLS_DROP && q < N) ? R[q] : 0u;
+			r2[k] = (c[i0 + k] && q < N) ? R[q] : 0u;
 		}
 #pragma unroll
 		for (int k = 0; k < CP_CHUNK; k++) {
 			const int i = i0 + k;
-			const u32 ms = __ballot_sync(0xffffffffu, c[i] == CLS_SMALL), mb = __ballot_sync(0xffffffffu, c[i] == CLS_BIG);
-			if (c[i] == CLS_SMALL) { const u32 d = qs + __popc(ms & lanemask_lt()); o.Slp[d] = pp[k]; o.Slr[d] = rr[k]; o.Sr2[d] = r2[k]; }
-			else if (c[i] == CLS_BIG) { const u32 d = qb + __popc(mb & lanemask_lt()); o.Bkey[d] = ((u64) rr[k] << nbits) | r2[k]; o.Bval[d] = pp[k]; }
-			qs += __popc(ms); qb += __popc(mb);
+			const u32 ma = __ballot_sync(0xffffffffu, c[i] == 1), mb = __ballot_sync(0xffffffffu, c[i] == 2);
+			if (c[i] == 1) { const u32 d = qa + __popc(ma & lanemask_lt()); alp[d] = pp[k]; alr[d] = rr[k]; ar2[d] = r2[k]; }
+			else if (c[i] == 2) {
+				const u32 d = qb + __popc(mb & lanemask_lt());
+				if (tgt_b == TGT_B) { o.Bkey[d] = ((u64) rr[k] << nbits) | r2[k]; o.Bval[d] = pp[k]; }
+				else { blp[d] = pp[k]; blr[d] = rr[k]; br2[d] = r2[k]; }
+			}
+			qa += __popc(ma); qb += __popc(mb);
 		}
 	}
+}
+
+// the totals of one compaction call are added to the fill counts of its two target lists
+__global__ void k1_add_totals_kernel(const u64 *tot, u64 *cnt_a, u64 *cnt_b) {
+	const u64 t = *tot;
+	if (cnt_a) *cnt_a += t & 0xFFFFFFFFull;
+	if (cnt_b) *cnt_b += t >> 32;
 }
 
 // ---- bucket-local sort of the S list
@@ -697,28 +717,215 @@ template <int CAP> static void launch_tile_sort(Dev &d, const u32 *lp, const u32
 	FBG_LAUNCH_CHECK();
 }
 
-// Appends the survivors of one sorted list to the next S / B lists.  *total_out receives
-// this call's (small | big << 32) counts; base (device word, same packing) = where to append.
-static void compact_lists(Dev &d, const u8 *cls, const u32 *lp, const u32 *lr, u64 na, const u64 *base, u64 *total_out, bool skip_small,
+// Appends the survivors of classes ca / cb of one sorted list to the next round's lists tgt_a / tgt_b.
+// cnt_a / cnt_b: device words with the fill counts of those lists: read as the append offsets, then
+// raised by this call's totals (null for an unused class).  tot: a scratch device word.
+static void compact_lists(Dev &d, const u8 *cls, const u32 *lp, const u32 *lr, u64 na, u32 ca, int tgt_a, u64 *cnt_a, u32 cb, int tgt_b, u64 *cnt_b, u64 *tot,
                           const u32 *R, u64 hnext, u64 N, int nbits, CompactOut o) {
-	if (na == 0) { FBG_CUDA(cudaMemsetAsync(total_out, 0, sizeof(u64), d.stream)); return; }
+	if (na == 0) return;
 	u32 nt = div_up(na, CP_TILE);
 	u64 mk = d.mark();
 	u64 *partial = d.alloc<u64>(nt);
 	d.begin(K_DOUBLING_AUX);
-	k1_cls_count_kernel<<<nt, CP_THREADS, 0, d.stream>>>(cls, na, skip_small ? 1 : 0, partial);
-	scan_partials_kernel<OpSumU64><<<1, 1024, 0, d.stream>>>(partial, nt, total_out);
-	k1_cls_write_kernel<<<nt, CP_THREADS, 0, d.stream>>>(cls, lp, lr, na, partial, base, skip_small ? 1 : 0, R, hnext, N, nbits, o);
+	k1_cls_count_kernel<<<nt, CP_THREADS, 0, d.stream>>>(cls, na, ca, cb, partial);
+	scan_partials_kernel<OpSumU64><<<1, 1024, 0, d.stream>>>(partial, nt, tot);
+	k1_cls_write_kernel<<<nt, CP_THREADS, 0, d.stream>>>(cls, lp, lr, na, partial, cnt_a, cnt_b, ca, cb, tgt_a, tgt_b, R, hnext, N, nbits, o);
+	k1_add_totals_kernel<<<1, 1, 0, d.stream>>>(tot, cnt_a, cnt_b);
 	FBG_LAUNCH_CHECK();
 	d.end((double) na * (2.0 + 8.0 + 4.0 + 12.0));
-	d.note_launches(K_DOUBLING_AUX, 2);
+	d.note_launches(K_DOUBLING_AUX, 3);
 	d.release(mk);
 }
 
-__global__ void k1_active_total_kernel(const u64 *sc64, u64 *tot) {
-	// (small | big << 32) survivor words of the S and B compaction -> one count
-	u64 a = sc64[0], b = sc64[1];
-	*tot = (a & 0xFFFFFFFFull) + (a >> 32) + (b & 0xFFFFFFFFull) + (b >> 32);
+__global__ void k1_active_total_kernel(const u64 *cnt, u64 *tot) {
+	*tot = cnt[0] + cnt[1] + cnt[2]; // next S, M, B lists
+}
+
+// ---- bucket-streaming sort of the M list (buckets of MID_MIN .. BSMALL suffixes)
+// Same job as k1_tile_sort_kernel -- order every bucket by r2, new rank = old rank + offset of the
+// sub-bucket, class of every element, rank scatter, SA entries of single suffixes -- for buckets too
+// large to sort several of per shared-memory window.  CTA b owns the buckets whose head lies in list slots
+// [b * BS_TILE, (b + 1) * BS_TILE) and STREAMS each of them twice instead of holding it in shared memory:
+//   pass A  finds the end of the bucket (lr changes) and counts the elements below / above the pivot
+//           (the majority value of three probes; any value is correct, a bad one only sends more
+//           keys through the network);
+//   pass B  writes the elements equal to the pivot straight to their final slots (block-wide ballot
+//           scan: they keep their order, which is text order) and collects the others -- the
+//           minority -- as 64-bit keys (above-pivot | r2 | index in bucket) in shared memory;
+//   then    the swizzled bitonic network (tilesort.cuh), sized to the minority, sub-bucket heads by
+//           ballots, ranks / classes / outputs of the minority.
+// Per element: 8 B (lr, r2) + 8 B (r2 again, mostly from L2, lp) read, 9 B written, 4 B rank scatter, and
+// about a tenth of the instructions of the window kernel.
+constexpr int BS_THREADS = 512;
+constexpr int BS_TILE = 2048;
+constexpr int BS_CH = BS_THREADS * 4;   // elements per streaming step
+constexpr int BS_MAXHEADS = 32;         // bucket heads per BS_TILE slots (2 when every bucket has >= MID_MIN elements)
+constexpr size_t BS_SMEM = (size_t) BSMALL * 8 + ((size_t) BSMALL / 32 + 1) * 4;
+
+__global__ void __launch_bounds__(BS_THREADS, 3)
+k1_bucket_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, const u32 *__restrict__ r2, u64 na, u32 mid_min,
+                      u32 *__restrict__ R, u32 *__restrict__ SA, u32 *__restrict__ lp_out, u32 *__restrict__ lr_out, u8 *__restrict__ cls_out, u32 *__restrict__ scal) {
+	extern __shared__ __align__(16) unsigned char bs_raw[];
+	u64 *key = reinterpret_cast<u64 *>(bs_raw);
+	u32 *bal = reinterpret_cast<u32 *>(bs_raw + (size_t) BSMALL * 8);
+	__shared__ u32 s_heads[BS_MAXHEADS], s_nheads, s_red[3][BS_THREADS / 32], s_cnt[4 * (BS_THREADS / 32)], s_pre[4 * (BS_THREADS / 32)], s_tot;
+	constexpr u32 NW = BS_THREADS / 32;
+	const u32 tid = threadIdx.x, w = tid >> 5, l = tid & 31;
+	const u64 w0 = (u64) blockIdx.x * BS_TILE;
+	if (tid == 0) s_nheads = 0;
+	__syncthreads();
+#pragma unroll
+	for (int j = 0; j < BS_TILE / BS_THREADS; j++) {
+		const u64 t = w0 + (u64) j * BS_THREADS + tid;
+		if (t < na) {
+			const u32 v = lr[t];
+			if (t == 0 || lr[t - 1] != v) { const u32 q = atomicAdd(&s_nheads, 1u); if (q < BS_MAXHEADS) s_heads[q] = (u32) (t - w0); }
+		}
+	}
+	__syncthreads();
+	const u32 nh = s_nheads;
+	if (nh == 0) return;
+	if (nh > BS_MAXHEADS) { if (tid == 0) scal[1] = 1u; return; } // smaller buckets than the host promised
+	u32 mx = 0;
+	for (u32 hi = 0; hi < nh; hi++) {
+		const u64 h = w0 + s_heads[hi];
+		const u32 lrh = lr[h];
+		u32 pv;
+		{
+			const u64 tb = h + mid_min / 3, tc = h + 2 * (mid_min / 3);
+			const u32 pa = r2[h], pb = tb < na ? r2[tb] : pa, pc = tc < na ? r2[tc] : pa;
+			pv = pb == pc ? pb : pa;
+		}
+		// pass A
+		u32 cnt = 0, nl = 0, ng = 0;
+		bool broken = false;
+		for (u32 c0 = 0;; c0 += BS_CH) {
+			u32 a[4], b[4];
+#pragma unroll
+			for (int j = 0; j < 4; j++) {
+				const u64 t = h + c0 + (u32) j * BS_THREADS + tid;
+				a[j] = ~lrh; b[j] = pv;
+				if (t < na) { a[j] = lr[t]; b[j] = r2[t]; }
+			}
+			bool all_in = true;
+#pragma unroll
+			for (int j = 0; j < 4; j++) {
+				const u64 t = h + c0 + (u32) j * BS_THREADS + tid;
+				const bool in = t < na && a[j] == lrh;
+				cnt += in ? 1u : 0u; nl += (in && b[j] < pv) ? 1u : 0u; ng += (in && b[j] > pv) ? 1u : 0u;
+				all_in = all_in && in;
+			}
+			if (!__syncthreads_and(all_in ? 1 : 0)) break;
+			if (c0 + BS_CH > BSMALL) { broken = true; break; } // a bucket above BSMALL: host contract broken
+		}
+		if (broken) { if (tid == 0) scal[1] = 1u; return; }
+		cnt = warp_reduce_sum(cnt); nl = warp_reduce_sum(nl); ng = warp_reduce_sum(ng);
+		if (l == 0) { s_red[0][w] = cnt; s_red[1][w] = nl; s_red[2][w] = ng; }
+		__syncthreads();
+		u32 size = 0, nless = 0, ngr = 0;
+#pragma unroll
+		for (u32 ww = 0; ww < NW; ww++) { size += s_red[0][ww]; nless += s_red[1][ww]; ngr += s_red[2][ww]; }
+		if (size > BSMALL) { if (tid == 0) scal[1] = 1u; return; }
+		const u32 nmin = nless + ngr, neq = size - nmin;
+		const u32 cls_eq = neq == 1 ? CLS_DROP : (neq < mid_min ? CLS_SMALL : CLS_MID);
+		const u32 req = lrh + nless; // rank of the elements equal to the pivot
+		if (cls_eq == CLS_SMALL) mx = neq > mx ? neq : mx;
+		// pass B
+		u32 eq_run = 0, mn_run = 0;
+		for (u32 c0 = 0; c0 < size; c0 += BS_CH) {
+			u32 rv[4], pp[4];
+#pragma unroll
+			for (int j = 0; j < 4; j++) {
+				const u32 q = c0 + (u32) j * BS_THREADS + tid;
+				rv[j] = pv; pp[j] = 0;
+				if (q < size) { rv[j] = r2[h + q]; pp[j] = lp[h + q]; }
+			}
+			u32 be[4], bm[4];
+#pragma unroll
+			for (int j = 0; j < 4; j++) {
+				const u32 q = c0 + (u32) j * BS_THREADS + tid;
+				const bool in = q < size;
+				be[j] = __ballot_sync(0xffffffffu, in && rv[j] == pv);
+				bm[j] = __ballot_sync(0xffffffffu, in && rv[j] != pv);
+				if (l == 0) s_cnt[j * NW + w] = (u32) __popc(be[j]) | ((u32) __popc(bm[j]) << 16);
+			}
+			__syncthreads();
+			if (w == 0) { // exclusive scan of the 4 * NW slab counts (two per lane)
+				const u32 x = s_cnt[2 * l], y = s_cnt[2 * l + 1];
+				const u32 inc = warp_incl_sum(x + y);
+				s_pre[2 * l] = inc - x - y; s_pre[2 * l + 1] = inc - y;
+				if (l == 31) s_tot = inc;
+			}
+			__syncthreads();
+#pragma unroll
+			for (int j = 0; j < 4; j++) {
+				const u32 q = c0 + (u32) j * BS_THREADS + tid;
+				if (q < size) {
+					const u32 pre = s_pre[j * NW + w];
+					if (rv[j] == pv) {
+						const u64 out = h + nless + eq_run + (pre & 0xFFFFu) + (u32) __popc(be[j] & lanemask_lt());
+						lp_out[out] = pp[j]; lr_out[out] = req; cls_out[out] = (u8) cls_eq;
+						if (nless) R[pp[j]] = req;
+						if (neq == 1) SA[req] = pp[j];
+					} else {
+						const u32 mp = mn_run + (pre >> 16) + (u32) __popc(bm[j] & lanemask_lt());
+						key[ts_sw(mp)] = ((u64) (rv[j] > pv ? 1u : 0u) << 45) | ((u64) rv[j] << 13) | (u64) q;
+					}
+				}
+			}
+			const u32 tot = s_tot;
+			eq_run += tot & 0xFFFFu; mn_run += tot >> 16;
+		}
+		if (nmin) {
+			u32 net = 32;
+			while (net < nmin) net <<= 1;
+			for (u32 slot = nmin + tid; slot < net; slot += BS_THREADS) key[ts_sw(slot)] = ~0ull;
+			__syncthreads();
+			tile_bitonic_sort_rt<BS_THREADS>(key, net);
+			// sub-bucket heads of the sorted minority, one ballot word per 32 slots
+			for (u32 s0 = 0; s0 < nmin; s0 += BS_THREADS) {
+				const u32 sx = s0 + tid;
+				const bool hd = sx < nmin && (sx == 0 || (key[ts_sw(sx)] >> 13) != (key[ts_sw(sx - 1)] >> 13));
+				const u32 bw = __ballot_sync(0xffffffffu, hd);
+				if (l == 0 && sx < nmin) bal[sx >> 5] = bw;
+			}
+			__syncthreads();
+			const u32 ngrp = (nmin + 31) >> 5;
+			for (u32 s0 = 0; s0 < nmin; s0 += BS_THREADS) {
+				const u32 sx = s0 + tid;
+				if (sx < nmin) {
+					const u64 k = key[ts_sw(sx)];
+					const u32 g = sx >> 5, bi = sx & 31;
+					u32 m1 = bal[g] & (0xFFFFFFFFu >> (31 - bi)), g1 = g;
+					while (m1 == 0) m1 = bal[--g1];                 // slot 0 is a head
+					const u32 hs = g1 * 32 + 31 - (u32) __clz(m1);  // head of my sub-bucket
+					u32 m2 = bi == 31 ? 0u : (bal[g] & (0xFFFFFFFFu << (bi + 1))), g2 = g;
+					while (m2 == 0 && ++g2 < ngrp) m2 = bal[g2];
+					const u32 he = m2 ? g2 * 32 + (u32) __ffs(m2) - 1 : nmin; // head of the next one
+					const u32 sz = he - hs;
+					const bool gt = (k >> 45) & 1ull;
+					const u32 p = lp[h + ((u32) k & (BSMALL - 1))];
+					const u64 out = h + (gt ? neq : 0u) + sx;
+					const u32 nr = lrh + (gt ? neq : 0u) + hs;
+					const u32 c = sz == 1 ? CLS_DROP : (sz < mid_min ? CLS_SMALL : CLS_MID);
+					if (nr != lrh) R[p] = nr;
+					if (sz == 1) SA[nr] = p;
+					lp_out[out] = p; lr_out[out] = nr; cls_out[out] = (u8) c;
+					if (c == CLS_SMALL && sx == hs) mx = sz > mx ? sz : mx;
+				}
+			}
+		}
+		__syncthreads(); // key, bal and the counters are used again by the next bucket
+	}
+	mx = warp_reduce_max(mx);
+	if (l == 0 && mx > *reinterpret_cast<volatile u32 *>(scal)) atomicMax(&scal[0], mx);
+}
+
+static void launch_bucket_sort(Dev &d, const u32 *lp, const u32 *lr, const u32 *r2, u64 na, u32 mid_min,
+                               u32 *R, u32 *SA, u32 *lp_out, u32 *lr_out, u8 *cls_out, u32 *scal) {
+	FBG_CUDA(cudaFuncSetAttribute(k1_bucket_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) BS_SMEM));
+	k1_bucket_sort_kernel<<<div_up(na, BS_TILE), BS_THREADS, BS_SMEM, d.stream>>>(lp, lr, r2, na, mid_min, R, SA, lp_out, lr_out, cls_out, scal);
+	FBG_LAUNCH_CHECK();
 }
 
 // ---- sufficient index for gapless MSAs: stop as soon as every tied bucket is COLUMN-PURE
@@ -834,33 +1041,50 @@ __global__ void k1_dict_counts_kernel(const u32 *__restrict__ lv, const u32 *__r
 	u32 c = cnt[lv[t]];
 	call[t] = c; cbig[t] = c > BSMALL ? c : 0u;
 }
-// info[slot] = (rank, start of the bucket in its list, size, smallest member); A = directory of the small buckets by text position
+// info[slot] = (rank, start of the bucket in its list, size, smallest member); the start of a B bucket is set here
+// (B list in k-mer order), that of an S / M bucket by k1_dict_place_kernel
 __global__ void k1_dict_assign_kernel(const u32 *__restrict__ lv, const u32 *__restrict__ cnt, const u32 *__restrict__ first, const u32 *__restrict__ rk, const u32 *__restrict__ bs,
-                                      u32 nd, u32 rank_off, uint4 *__restrict__ info, u32 *__restrict__ rank_of_slot, u32 *__restrict__ A, u32 *__restrict__ maxb) {
+                                      u32 nd, u32 rank_off, u32 mid_min, uint4 *__restrict__ info, u32 *__restrict__ rank_of_slot, u32 *__restrict__ maxb) {
 	u32 t = blockIdx.x * blockDim.x + threadIdx.x;
 	u32 small = 0;
 	if (t < nd) {
 		u32 s = lv[t], c = cnt[s], f = first[s], start = 0;
 		if (c > BSMALL) start = bs[t];
-		else if (c > 1) { A[f] = c; small = c; }
+		else if (c > 1 && c < mid_min) small = c;
 		info[s] = make_uint4(rank_off + rk[t], start, c, f);
 		rank_of_slot[s] = rank_off + rk[t];
 	}
 	small = warp_reduce_max(small);
 	if (lane_id() == 0 && small) atomicMax(maxb, small);
 }
-__global__ void k1_dict_fold_kernel(const u32 *__restrict__ lv, u32 nd, uint4 *__restrict__ info, const u32 *__restrict__ A) {
+// The S and M lists are laid out by text position: buckets ordered by their smallest member, so
+// neighbouring tiles hold neighbouring MSA columns (see k1_bucket_size_kernel).  The distinct k-mers
+// are sorted by that position (a few passes over nd keys, not a directory of N words): ok = key, ov = t
+__global__ void k1_dict_firstkeys_kernel(const u32 *__restrict__ lv, const u32 *__restrict__ first, u32 nd, u64 *__restrict__ ok, u32 *__restrict__ ov) {
 	u32 t = blockIdx.x * blockDim.x + threadIdx.x;
 	if (t >= nd) return;
-	u32 s = lv[t];
+	ok[t] = first[lv[t]]; ov[t] = t;
+}
+// in that order: sizes of the S-class and of the M-class buckets (their exclusive scans = the list offsets)
+__global__ void k1_dict_sizes_kernel(const u32 *__restrict__ ov, const u32 *__restrict__ lv, const u32 *__restrict__ cnt, u32 nd, u32 mid_min, u32 *__restrict__ zs, u32 *__restrict__ zm) {
+	u32 j = blockIdx.x * blockDim.x + threadIdx.x;
+	if (j >= nd) return;
+	const u32 c = cnt[lv[ov[j]]];
+	zs[j] = (c > 1 && c < mid_min) ? c : 0u;
+	zm[j] = (c >= mid_min && c <= BSMALL) ? c : 0u;
+}
+__global__ void k1_dict_place_kernel(const u32 *__restrict__ ov, const u32 *__restrict__ lv, u32 nd, u32 mid_min, const u32 *__restrict__ zs, const u32 *__restrict__ zm, uint4 *__restrict__ info) {
+	u32 j = blockIdx.x * blockDim.x + threadIdx.x;
+	if (j >= nd) return;
+	const u32 s = lv[ov[j]];
 	uint4 v = info[s];
-	if (v.z > 1 && v.z <= BSMALL) { v.y = A[v.w]; info[s] = v; }
+	if (v.z > 1 && v.z <= BSMALL) { v.y = v.z < mid_min ? zs[j] : zm[j]; info[s] = v; }
 }
 // what the sort-based round 0 leaves behind: ranks, SA entries of the suffixes alone in their
-// bucket, the S and B lists of the next round with R[p+h] looked up (through the table: no
+// bucket, the S, M and B lists of the next round with R[p+h] looked up (through the table: no
 // rank has to be visible yet)
 __global__ void __launch_bounds__(256) k1_dict_emit_kernel(const u32 *__restrict__ slot_of, const u32 *__restrict__ ord_of, const uint4 *__restrict__ info, const u32 *__restrict__ rank_of_slot,
-                                                           u64 N, u64 hnext, int nbits, u32 *__restrict__ R, u32 *__restrict__ SA, CompactOut o) {
+                                                           u64 N, u64 hnext, int nbits, u32 mid_min, u32 *__restrict__ R, u32 *__restrict__ SA, CompactOut o) {
 	u64 p = (u64) blockIdx.x * blockDim.x + threadIdx.x;
 	if (p >= N) return;
 	const uint4 v = __ldg(info + slot_of[p]);
@@ -869,7 +1093,8 @@ __global__ void __launch_bounds__(256) k1_dict_emit_kernel(const u32 *__restrict
 	const u64 pn = p + hnext;
 	const u32 r2 = pn < N ? __ldg(rank_of_slot + slot_of[pn]) : 0u; // 4-byte entries: a quarter of the L2 traffic of info[]
 	const u32 q = v.y + ord_of[p];
-	if (v.z <= BSMALL) { o.Slp[q] = (u32) p; o.Slr[q] = v.x; o.Sr2[q] = r2; }
+	if (v.z < mid_min) { o.Slp[q] = (u32) p; o.Slr[q] = v.x; o.Sr2[q] = r2; }
+	else if (v.z <= BSMALL) { o.Mlp[q] = (u32) p; o.Mlr[q] = v.x; o.Mr2[q] = r2; }
 	else { o.Bkey[q] = ((u64) v.x << nbits) | r2; o.Bval[q] = (u32) p; }
 }
 
@@ -880,13 +1105,13 @@ static u32 dict_capacity(u64 N) {
 }
 static u64 dict_scratch_bytes(u64 N) {
 	u64 cap = dict_capacity(N);
-	return cap * (8 + 4 + 4 + 16 + 4) + (cap / 2) * (16 + 8 + 8) + (cap / SCAN_TILE + 2) * 24 + (1u << 16);
+	return cap * (8 + 4 + 4 + 16 + 4) + (cap / 2) * (16 + 8 + 8 + 16 + 8) + (cap / SCAN_TILE + 2) * 24 + (cap / 2 / RS_TILE + 2) * RS_BINS * 12 + (1u << 16);
 }
 
 // Returns false (nothing written that matters) when the text has too many distinct k-mers for
 // the table: the caller then sorts all suffixes as before.
-static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int key_bits0, u32 km_grid, u32 *slot_of, u32 *ord_of, u32 *A,
-                           u64 hnext, int nbits, CompactOut o, u64 *nS, u64 *nB, u32 *maxb, bool try_pure) {
+static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int key_bits0, u32 km_grid, u32 *slot_of, u32 *ord_of, u32 mid_min,
+                           u64 hnext, int nbits, CompactOut o, u64 *nS, u64 *nM, u64 *nB, u32 *maxb, bool try_pure) {
 	Dev &d = p.dev;
 	const u64 N = p.N;
 	const u32 cap = dict_capacity(N), ndmax = cap / 2;
@@ -894,7 +1119,7 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	KmerDict dk;
 	dk.key = d.alloc<u64>(cap); dk.cnt = d.alloc<u32>(cap); dk.first = d.alloc<u32>(cap);
 	dk.mask = cap - 1; dk.slot_of = slot_of; dk.ord_of = ord_of;
-	u32 *sc = reinterpret_cast<u32 *>(p.scalars + 48); // [0] distinct, [1] overflow, [2] nS, [3] nB, [4] maxb
+	u32 *sc = reinterpret_cast<u32 *>(p.scalars + 48); // [0] distinct, [1] overflow, [2] nS, [3] nB, [4] maxb, [5] nM
 	u32 *h_sc = reinterpret_cast<u32 *>(p.h_scalars + 48);
 	dk.overflow = sc + 1;
 	uint4 *info = d.alloc<uint4>(cap);
@@ -905,6 +1130,10 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	lb.v[0] = d.alloc<u32>(ndmax); lb.v[1] = d.alloc<u32>(ndmax);
 	lb.cur = 0;
 	u32 *call = d.alloc<u32>(ndmax), *cbig = d.alloc<u32>(ndmax);
+	RadixBuffers ob; // the distinct k-mers by smallest member (layout of the S and M lists)
+	ob.k[0] = d.alloc<u64>(ndmax); ob.k[1] = d.alloc<u64>(ndmax);
+	ob.v[0] = d.alloc<u32>(ndmax); ob.v[1] = d.alloc<u32>(ndmax);
+	ob.cur = 0;
 	const u32 gc = div_up(cap, 256);
 	bool known_impure = false;
 	if (try_pure && !p.force_arrays && p.opt.n_ignore == 0) {
@@ -947,7 +1176,7 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 			FBG_CUDA(cudaStreamSynchronize(d.stream)); // the scratch is released below
 			p.index_lazy = true; p.lazy_depth = (u64) K;
 			p.index_virtual = true; p.dict_nd = ndv;
-			*nS = 0; *nB = 0; *maxb = 0;
+			*nS = 0; *nM = 0; *nB = 0; *maxb = 0;
 			d.release(mk);
 			return true;
 		}
@@ -987,10 +1216,9 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	device_scan<OpSumU32, true>(d, call, call, nd);
 	device_scan<OpSumU32, true>(d, cbig, cbig, nd, sc + 3);
 	d.begin(K_DOUBLING_AUX);
-	FBG_CUDA(cudaMemsetAsync(A, 0, N * sizeof(u32), d.stream));
-	k1_dict_assign_kernel<<<gn, 256, 0, d.stream>>>(lv, dk.cnt, dk.first, call, cbig, nd, 0u, info, rank_of_slot, A, sc + 4);
+	k1_dict_assign_kernel<<<gn, 256, 0, d.stream>>>(lv, dk.cnt, dk.first, call, cbig, nd, 0u, mid_min, info, rank_of_slot, sc + 4);
 	FBG_LAUNCH_CHECK();
-	d.end((double) nd * 40.0 + (double) N * 4.0);
+	d.end((double) nd * 40.0);
 	if (try_pure && !known_impure) {
 		// sufficient index (above k1_suffix_array): if no bucket spans two columns this is all of K1
 		u32 *impure = reinterpret_cast<u32 *>(p.scalars + 12);
@@ -1004,21 +1232,34 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 		FBG_CUDA(cudaStreamSynchronize(d.stream));
 		if (*h_impure == 0) {
 			p.index_lazy = true; p.lazy_depth = (u64) K;
-			*nS = 0; *nB = 0; *maxb = 0;
+			*nS = 0; *nM = 0; *nB = 0; *maxb = 0;
 			d.release(mk);
 			return true;
 		}
 	}
-	device_scan<OpSumU32, true>(d, A, A, N, sc + 2);
+	// offsets of the S and M buckets in their lists, in the order of their smallest members
 	d.begin(K_DOUBLING_AUX);
-	k1_dict_fold_kernel<<<gn, 256, 0, d.stream>>>(lv, nd, info, A);
-	k1_dict_emit_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, p.ISA, p.SA, o);
+	k1_dict_firstkeys_kernel<<<gn, 256, 0, d.stream>>>(lv, dk.first, nd, (u64 *) ob.k[0], ob.v[0]);
 	FBG_LAUNCH_CHECK();
-	d.end((double) N * (8.0 + 4.0 + 4.0 + 12.0) + (double) nd * 24.0);
+	d.end((double) nd * 20.0);
+	const int oc = radix_sort<u64, true>(d, ob, nd, 0, nbits);
+	const u32 *ov = ob.v[oc];
+	u32 *zs = call, *zm = cbig; // both scans were consumed by k1_dict_assign_kernel
+	d.begin(K_DOUBLING_AUX);
+	k1_dict_sizes_kernel<<<gn, 256, 0, d.stream>>>(ov, lv, dk.cnt, nd, mid_min, zs, zm);
+	FBG_LAUNCH_CHECK();
+	d.end((double) nd * 20.0);
+	device_scan<OpSumU32, true>(d, zs, zs, nd, sc + 2);
+	device_scan<OpSumU32, true>(d, zm, zm, nd, sc + 5);
+	d.begin(K_DOUBLING_AUX);
+	k1_dict_place_kernel<<<gn, 256, 0, d.stream>>>(ov, lv, nd, mid_min, zs, zm, info);
+	k1_dict_emit_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, p.SA, o);
+	FBG_LAUNCH_CHECK();
+	d.end((double) N * (8.0 + 4.0 + 4.0 + 12.0) + (double) nd * 40.0);
 	d.note_launches(K_DOUBLING_AUX, 1);
-	FBG_CUDA(cudaMemcpyAsync(h_sc, sc, 5 * sizeof(u32), cudaMemcpyDeviceToHost, d.stream));
+	FBG_CUDA(cudaMemcpyAsync(h_sc, sc, 6 * sizeof(u32), cudaMemcpyDeviceToHost, d.stream));
 	FBG_CUDA(cudaStreamSynchronize(d.stream));
-	*nS = h_sc[2]; *nB = h_sc[3]; *maxb = h_sc[4];
+	*nS = h_sc[2]; *nB = h_sc[3]; *maxb = h_sc[4]; *nM = h_sc[5];
 	d.release(mk);
 	return true;
 }
@@ -1087,10 +1328,10 @@ void k1_suffix_array(Pipeline &p) {
 		d.release(mk2);
 	}
 	const u64 cap = nloc ? nloc : 1;
-	// scratch of this phase: 74 B per suffix sorted here (sort ping-pong 24, heads 16, classes 2,
-	// S lists 24, tile outputs 8) + radix count matrices + (sharded) the N-word bucket directory
+	// scratch of this phase: 98 B per suffix sorted here (sort ping-pong 24, heads 16, classes 2,
+	// S lists 24, M lists 24, sorter outputs 8) + radix count matrices + (sharded) the N-word bucket directory
 	d.release(mk);
-	d.ensure(cap * 76 + (cap / RS_TILE + 2) * RS_BINS * 12 + (u64) km_grid * 8 + (sharded ? N * 4 + (N / SCAN_TILE + 2) * 24 : dict_scratch_bytes(N)) + (16u << 20));
+	d.ensure(cap * 100 + (cap / RS_TILE + 2) * RS_BINS * 12 + (u64) km_grid * 8 + (sharded ? N * 4 + (N / SCAN_TILE + 2) * 24 : dict_scratch_bytes(N)) + (16u << 20));
 	mk = d.mark();
 
 	RadixBuffers rb;
@@ -1100,27 +1341,37 @@ void k1_suffix_array(Pipeline &p) {
 	u64 *HH = d.alloc<u64>(cap);
 	u32 *HR = d.alloc<u32>(cap), *newr = d.alloc<u32>(cap);
 	u8 *clsB = d.alloc<u8>(cap + 16), *clsS = d.alloc<u8>(cap + 16);
-	u32 *Slp[2], *Slr[2], *Sr2[2];
+	u32 *Slp[2], *Slr[2], *Sr2[2], *Mlp[2], *Mlr[2], *Mr2[2];
 	for (int q = 0; q < 2; q++) { Slp[q] = d.alloc<u32>(cap); Slr[q] = d.alloc<u32>(cap); Sr2[q] = d.alloc<u32>(cap); }
+	for (int q = 0; q < 2; q++) { Mlp[q] = d.alloc<u32>(cap); Mlr[q] = d.alloc<u32>(cap); Mr2[q] = d.alloc<u32>(cap); }
+	// outputs of the two bucket-local sorters: S list in [0, nS), M list in [nS, nS + nM)
 	u32 *lp_out = d.alloc<u32>(cap), *lr_out = d.alloc<u32>(cap);
-	u32 *sc32 = reinterpret_cast<u32 *>(p.scalars + 8);  // [0] maxb, [1] err
-	u64 *sc64 = p.scalars + 9;                          // (small | big << 32) survivor counts of the [0] S path, [1] B path
-	u64 *gtot = p.scalars + 11;                         // suffixes still tied, over all GPUs
-	u64 *h_sc = p.h_scalars + 8;                        // mirror of scalars[8..11]
+	u32 *sc32 = reinterpret_cast<u32 *>(p.scalars + 56);  // [0] maxb, [1] err
+	u64 *cnt = p.scalars + 57;                           // fill counts of the next S, M, B lists
+	u64 *ctot = p.scalars + 60;                          // scratch word of the compactions
+	u64 *gtot = p.scalars + 61;                          // suffixes still tied, over all GPUs
+	u64 *h_sc = p.h_scalars + 56;                        // mirror of scalars[56..61]
 
 	int nbits = 1;
 	while ((1ull << nbits) < N) nbits++;
-	u64 nS = 0, nB = nloc; // round 0: every suffix goes through the device-wide sort ...
+	u64 nS = 0, nM = 0, nB = nloc; // round 0: every suffix goes through the device-wide sort ...
 	u32 maxb = 0;
-	int sc = 0;           // current S list
+	int sc = 0;           // current S / M lists
 	// ... unless the k-mer dictionary takes it: no sort, ranks written in text order
 	bool by_dict = false;
+	u32 mid_want = MID_MIN; // FBG_MID_MIN: test hook (64 ..: small inputs through the M path; above BSMALL: no M list)
+	if (const char *e = getenv("FBG_MID_MIN")) { long v = atol(e); mid_want = v > (long) BSMALL ? BSMALL + 1 : (v < 64 ? 64u : (u32) v); }
 	if (!sharded && key_bits0 < 64 && !getenv("FBG_NO_KMER_DICT")) {
 		CompactOut o;
 		o.Slp = Slp[1]; o.Slr = Slr[1]; o.Sr2 = Sr2[1];
+		o.Mlp = Mlp[1]; o.Mlr = Mlr[1]; o.Mr2 = Mr2[1];
 		o.Bkey = (u64 *) rb.k[1]; o.Bval = rb.v[1];
-		by_dict = k1_round0_dict(p, tab, K, b, key_bits0, km_grid, HR, newr, lp_out, (u64) K, nbits, o, &nS, &nB, &maxb, lazy_ok && (u64) K <= LAZY_MAX_DEPTH);
+		by_dict = k1_round0_dict(p, tab, K, b, key_bits0, km_grid, HR, newr, mid_want, (u64) K, nbits, o, &nS, &nM, &nB, &maxb,
+		                         lazy_ok && (u64) K <= LAZY_MAX_DEPTH);
 	}
+	// the M list (buckets of MID_MIN .. BSMALL suffixes streamed one per CTA) needs the text-ordered layout the
+	// dictionary's round 0 gives it; builds whose round 0 sorts all suffixes keep everything up to BSMALL in the S list
+	const u32 mid_min = by_dict ? mid_want : BSMALL + 1;
 	if (!by_dict) d.begin(K_KMER);
 	if (by_dict) {
 	} else if (!sharded) {
@@ -1158,8 +1409,8 @@ void k1_suffix_array(Pipeline &p) {
 		h *= 2;
 	}
 	for (;;) {
-		if (by_dict && nS + nB == 0) break; // every k-mer was unique
-		if (lazy_ok && p.sa_rounds >= 1 && h / 2 <= LAZY_MAX_DEPTH && nS + nB) {
+		if (by_dict && nS + nM + nB == 0) break; // every k-mer was unique
+		if (lazy_ok && p.sa_rounds >= 1 && h / 2 <= LAZY_MAX_DEPTH && nS + nM + nB) {
 			// ranks are exact to depth h / 2: are all buckets still tied column-pure?
 			u32 *impure = reinterpret_cast<u32 *>(p.scalars + 12);
 			u32 *h_impure = reinterpret_cast<u32 *>(p.h_scalars + 12);
@@ -1168,25 +1419,29 @@ void k1_suffix_array(Pipeline &p) {
 			FBG_CUDA(cudaMemsetAsync(impure, 0, sizeof(u64), d.stream));
 			d.begin(K_DOUBLING_AUX);
 			if (nS) k1_pure_check_kernel<false><<<div_up(nS, 256), 256, 0, d.stream>>>(Slp[sc], Slr[sc], nullptr, nbits, nS, p.col, impure);
+			if (nM) k1_pure_check_kernel<false><<<div_up(nM, 256), 256, 0, d.stream>>>(Mlp[sc], Mlr[sc], nullptr, nbits, nM, p.col, impure);
 			if (nB) k1_pure_check_kernel<true><<<div_up(nB, 256), 256, 0, d.stream>>>(bv, nullptr, bk, nbits, nB, p.col, impure);
 			FBG_LAUNCH_CHECK();
-			d.end((double) nS * 12.0 + (double) nB * 16.0);
+			d.end((double) (nS + nM) * 12.0 + (double) nB * 16.0);
 			FBG_CUDA(cudaMemcpyAsync(h_impure, impure, sizeof(u32), cudaMemcpyDeviceToHost, d.stream));
 			FBG_CUDA(cudaStreamSynchronize(d.stream));
 			if (debug) fprintf(stderr, "[fbg] K1 depth %llu: tied buckets %s\n", (unsigned long long) (h / 2), *h_impure ? "span several columns" : "are all column-pure: stop");
 			if (*h_impure == 0) {
 				const u32 depth = (u32) (h / 2);
 				FBG_CUDA(cudaMemsetAsync(p.PLCP, 0xFF, N * sizeof(u32), d.stream)); // PLCP_TODO everywhere
-				if (nS) {
+				for (int li = 0; li < 2; li++) { // S list, then M list (same records)
+					const u64 nl = li ? nM : nS;
+					const u32 *llp = li ? Mlp[sc] : Slp[sc], *llr = li ? Mlr[sc] : Slr[sc];
+					if (!nl) continue;
 					d.begin(K_DOUBLING_AUX);
-					k1_pure_heads_kernel<false><<<div_up(nS, 256), 256, 0, d.stream>>>(Slr[sc], nullptr, nbits, nS, lp_out);
+					k1_pure_heads_kernel<false><<<div_up(nl, 256), 256, 0, d.stream>>>(llr, nullptr, nbits, nl, lp_out);
 					FBG_LAUNCH_CHECK();
-					d.end((double) nS * 8.0);
-					device_scan<OpMaxU32, false>(d, lp_out, lp_out, nS);
+					d.end((double) nl * 8.0);
+					device_scan<OpMaxU32, false>(d, lp_out, lp_out, nl);
 					d.begin(K_DOUBLING_AUX);
-					k1_pure_final_kernel<false><<<div_up(nS, 256), 256, 0, d.stream>>>(Slp[sc], Slr[sc], nullptr, nbits, nS, lp_out, depth, p.ISA, p.SA, p.PLCP);
+					k1_pure_final_kernel<false><<<div_up(nl, 256), 256, 0, d.stream>>>(llp, llr, nullptr, nbits, nl, lp_out, depth, p.ISA, p.SA, p.PLCP);
 					FBG_LAUNCH_CHECK();
-					d.end((double) nS * 24.0);
+					d.end((double) nl * 24.0);
 				}
 				if (nB) {
 					d.begin(K_DOUBLING_AUX);
@@ -1203,10 +1458,10 @@ void k1_suffix_array(Pipeline &p) {
 				break;
 			}
 		}
-		if (debug) fprintf(stderr, "[fbg] rank %d K1 round %d: depth %llu, S list %llu (largest bucket %u), B list %llu\n", dist.rank, p.sa_rounds,
-		                   (unsigned long long) (p.sa_rounds ? h / 2 : 0), (unsigned long long) nS, maxb, (unsigned long long) nB);
-		FBG_CUDA(cudaMemsetAsync(p.scalars + 8, 0, 4 * sizeof(u64), d.stream));
-		// ---- S path
+		if (debug) fprintf(stderr, "[fbg] rank %d K1 round %d: depth %llu, S list %llu (largest bucket %u), M list %llu, B list %llu\n", dist.rank, p.sa_rounds,
+		                   (unsigned long long) (p.sa_rounds ? h / 2 : 0), (unsigned long long) nS, maxb, (unsigned long long) nM, (unsigned long long) nB);
+		FBG_CUDA(cudaMemsetAsync(p.scalars + 56, 0, 6 * sizeof(u64), d.stream));
+		// ---- S path: windows of whole small buckets sorted in shared memory
 		if (nS) {
 			d.begin(K_TILE_SORT);
 			if (2 * maxb <= 2048) launch_tile_sort<2048>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
@@ -1214,6 +1469,12 @@ void k1_suffix_array(Pipeline &p) {
 			else if (2 * maxb <= 8192) launch_tile_sort<8192>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
 			else launch_tile_sort<16384>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
 			d.end((double) nS * (12.0 + 4.0 + 9.0));
+		}
+		// ---- M path: one CTA streams one bucket
+		if (nM) {
+			d.begin(K_TILE_SORT);
+			launch_bucket_sort(d, Mlp[sc], Mlr[sc], Mr2[sc], nM, mid_min, p.ISA, p.SA, lp_out + nS, lr_out + nS, clsS + nS, sc32);
+			d.end((double) nM * (12.0 + 4.0 + 9.0));
 		}
 		// ---- B path
 		const u32 *sv = nullptr;
@@ -1229,7 +1490,7 @@ void k1_suffix_array(Pipeline &p) {
 			device_scan<OpMax2x32, false>(d, HH, HH, nB);
 			device_scan<OpMaxU32, false>(d, HR, HR, nB);
 			d.begin(K_DOUBLING_AUX);
-			k1_update_kernel<<<g, 256, 0, d.stream>>>(sk, sv, HH, HR, nB, hi_shift, rank_off, p.ISA, p.SA, newr, clsB, sc32);
+			k1_update_kernel<<<g, 256, 0, d.stream>>>(sk, sv, HH, HR, nB, hi_shift, rank_off, mid_min, p.ISA, p.SA, newr, clsB, sc32);
 			FBG_LAUNCH_CHECK();
 			d.end((double) nB * (8.0 + 4.0 + 8.0 + 4.0 + 4.0 + 4.0 + 1.0));
 		}
@@ -1243,8 +1504,9 @@ void k1_suffix_array(Pipeline &p) {
 		u64 hnext = h;
 		CompactOut o;
 		o.Slp = Slp[sc ^ 1]; o.Slr = Slr[sc ^ 1]; o.Sr2 = Sr2[sc ^ 1];
+		o.Mlp = Mlp[sc ^ 1]; o.Mlr = Mlr[sc ^ 1]; o.Mr2 = Mr2[sc ^ 1];
 		o.Bkey = (u64 *) rb.k[rb.cur ^ 1]; o.Bval = rb.v[rb.cur ^ 1];
-		const bool ordered = p.sa_rounds == 0; // round 0: S list in text order (k1_bucket_size_kernel)
+		const bool ordered = p.sa_rounds == 0; // round 0 by sort: S list in text order (k1_bucket_size_kernel); no M list in such a build
 		if (ordered) {
 			u64 mk2 = d.mark();
 			u32 *A = sharded ? d.alloc<u32>(N) : lp_out; // lp_out is free in round 0 (no S path yet) and holds N words on one GPU
@@ -1256,7 +1518,7 @@ void k1_suffix_array(Pipeline &p) {
 				FBG_LAUNCH_CHECK();
 				d.end((double) nB * 9.0 + (double) N * 4.0);
 			}
-			device_scan<OpSumU32, true>(d, A, A, N, reinterpret_cast<u32 *>(sc64));
+			device_scan<OpSumU32, true>(d, A, A, N, reinterpret_cast<u32 *>(cnt)); // cnt[0] = next nS (the high half of the word is zero)
 			if (nB) {
 				u32 g = div_up(nB, 256);
 				d.begin(K_DOUBLING_AUX);
@@ -1266,23 +1528,25 @@ void k1_suffix_array(Pipeline &p) {
 			}
 			if (sharded) FBG_CUDA(cudaStreamSynchronize(d.stream)); // A is released below
 			d.release(mk2);
+			compact_lists(d, clsB, sv, newr, nB, CLS_NONE, TGT_S, nullptr, CLS_BIG, TGT_B, cnt + 2, ctot, p.ISA, hnext, N, nbits, o);
 		} else {
-			compact_lists(d, clsS, lp_out, lr_out, nS, nullptr, sc64, false, p.ISA, hnext, N, nbits, o);
+			// the sorted S and M lists lie back to back in the sorter outputs: one pass moves both
+			compact_lists(d, clsS, lp_out, lr_out, nS + nM, CLS_SMALL, TGT_S, cnt, CLS_MID, TGT_M, cnt + 1, ctot, p.ISA, hnext, N, nbits, o);
+			compact_lists(d, clsB, sv, newr, nB, CLS_SMALL, TGT_S, cnt, CLS_BIG, TGT_B, cnt + 2, ctot, p.ISA, hnext, N, nbits, o);
+			if (mid_min <= BSMALL) compact_lists(d, clsB, sv, newr, nB, CLS_MID, TGT_M, cnt + 1, CLS_NONE, TGT_B, nullptr, ctot, p.ISA, hnext, N, nbits, o);
 		}
-		compact_lists(d, clsB, sv, newr, nB, sc64, sc64 + 1, ordered, p.ISA, hnext, N, nbits, o);
-		k1_active_total_kernel<<<1, 1, 0, d.stream>>>(sc64, gtot);
+		k1_active_total_kernel<<<1, 1, 0, d.stream>>>(cnt, gtot);
 		if (sharded) dist.allreduce_sum_u64(gtot, 1, d.stream);
-		FBG_CUDA(cudaMemcpyAsync(h_sc, p.scalars + 8, 4 * sizeof(u64), cudaMemcpyDeviceToHost, d.stream));
+		FBG_CUDA(cudaMemcpyAsync(h_sc, p.scalars + 56, 6 * sizeof(u64), cudaMemcpyDeviceToHost, d.stream));
 		FBG_CUDA(cudaStreamSynchronize(d.stream));
 		p.sa_rounds++;
 		const u32 *h32 = reinterpret_cast<const u32 *>(h_sc);
 		if (h32[1]) throw cuda_error("bucket-local suffix sort met a bucket larger than its tile");
 		maxb = h32[0];
-		nS = (u64) (u32) h_sc[1] + (u64) (u32) h_sc[2];
-		nB = h_sc[2] >> 32;
+		nS = h_sc[1]; nM = h_sc[2]; nB = h_sc[3];
 		if (nB) rb.cur ^= 1; // the compaction wrote the next B list into the other ping-pong half
 		sc ^= 1;
-		if (h_sc[3] == 0) break; // nothing tied on any GPU
+		if (h_sc[5] == 0) break; // nothing tied on any GPU
 		if (h >= N) throw cuda_error("prefix doubling did not converge");
 		hi_shift = nbits;
 		key_bits = 2 * nbits;

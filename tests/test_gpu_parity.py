@@ -465,7 +465,7 @@ def test_backtrack_across_many_segments(gpu_ctx):
 
 def test_randomised_shapes(gpu_ctx):
     """A fixed slice of tools/fuzz_gpu.py (which ran 4197 drawn cases without a mismatch in round 1):
-    MSA-like, few founders, periodic, identical, unrelated, tiny, many-rows and long inputs."""
+    MSA-like, few founders, periodic, identical, unrelated, tiny, many-rows, clades and long inputs."""
     import importlib.util
     spec = importlib.util.spec_from_file_location("fuzz_gpu", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools", "fuzz_gpu.py"))
     fz = importlib.util.module_from_spec(spec)
@@ -480,7 +480,7 @@ def test_randomised_shapes(gpu_ctx):
             _check_elastic(gpu_ctx, msa)
         else:
             _check_nonelastic(gpu_ctx, msa, 1)
-    assert len(kinds) == 8
+    assert len(kinds) == 9
 
 
 

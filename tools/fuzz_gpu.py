@@ -23,7 +23,7 @@ import test_gpu_parity as T
 
 
 def draw(rng):
-    kind = int(rng.integers(0, 8))
+    kind = int(rng.integers(0, 9))
     alpha = bytes(rng.choice([b"ACGT", b"ACGT", b"AC", b"ACGTN", b"ACDEFGHIKLMNPQRSTVWY"]))
     if kind == 0:  # MSA-like: one ancestor, sparse SNPs, many rows
         m, n = int(rng.integers(2, 400)), int(rng.integers(50, 4000))
@@ -55,6 +55,24 @@ def draw(rng):
         mut = rng.random((m, n)) < float(rng.choice([0.0005, 0.003, 0.02]))
         a[mut] = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, size=int(mut.sum()))]
         return a, "many-rows"
+    if kind == 8:  # clades: many rows copied from a few founders with sparse mutations and gap runs -- buckets of 1000+ rows
+        # whose minorities are large buckets themselves (the M list of the suffix sorter)
+        m, n = int(rng.integers(1100, 5000)), int(rng.integers(40, 400))
+        nf = int(rng.integers(1, 5))
+        founders = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, size=(nf, n))]
+        if nf > 1 and rng.random() < 0.7:  # founders that differ in a few columns only
+            founders[1:] = founders[0]
+            for q in range(1, nf):
+                cols = rng.integers(0, n, size=int(rng.integers(1, 6)))
+                founders[q, cols] = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, size=len(cols))]
+        a = founders[rng.integers(0, nf, size=m)].copy()
+        mut = rng.random((m, n)) < float(rng.choice([0.0, 0.0003, 0.002, 0.01]))
+        a[mut] = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, size=int(mut.sum()))]
+        if rng.random() < 0.5:
+            for i in rng.integers(0, m, size=int(rng.integers(1, 40))):
+                x = int(rng.integers(0, n))
+                a[i, x:x + int(rng.integers(1, 12))] = 0x2D
+        return a, "clades"
     m, n = int(rng.integers(2, 25)), int(rng.integers(200, 20000))  # long, few rows: many DP chunks / backtrack segments
     return synth.make_msa(m, n, snp=float(rng.choice([0.005, 0.03])), gap_div=int(rng.choice([0, 300])), seed=int(rng.integers(1 << 30))), "long"
 
