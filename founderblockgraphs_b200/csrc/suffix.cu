@@ -789,6 +789,17 @@ k1_bucket_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, co
 	u32 mx = 0;
 	for (u32 hi = 0; hi < nh; hi++) {
 		const u64 h = w0 + s_heads[hi];
+		// the bucket is walked in steps of BS_CH elements, each step waiting for its loads: pull everything the
+		// two passes will read into L2 now (the end of the bucket is not known yet; what lies behind it is
+		// the next bucket, which its own CTA is about to ask for)
+		for (u32 q = tid; q < 3 * (BSMALL / 32); q += BS_THREADS) {
+			const u32 arr = q / (BSMALL / 32);
+			const u64 e = h + BS_CH * (arr < 2 ? 1u : 0u) + (u64) (q % (BSMALL / 32)) * 32;
+			if (e < na && e < h + BSMALL) {
+				const u32 *a = (arr == 0 ? lr : arr == 1 ? r2 : lp) + e;
+				asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
+			}
+		}
 		const u32 lrh = lr[h];
 		u32 pv;
 		{
