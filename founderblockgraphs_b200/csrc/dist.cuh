@@ -16,6 +16,7 @@
 #pragma once
 #include "common.cuh"
 #include <dlfcn.h>
+#include <cstring>
 #include <string>
 
 namespace fbg {
@@ -28,6 +29,7 @@ struct NcclApi {
 	int (*CommInitRank)(void **, int, NcclUniqueId, int) = nullptr;
 	int (*CommDestroy)(void *) = nullptr;
 	int (*AllReduce)(const void *, void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+	int (*AllGather)(const void *, void *, size_t, int, void *, cudaStream_t) = nullptr;
 	const char *(*GetErrorString)(int) = nullptr;
 
 	bool load(std::string &err) {
@@ -41,13 +43,28 @@ struct NcclApi {
 		CommInitRank = (decltype(CommInitRank)) dlsym(lib, "ncclCommInitRank");
 		CommDestroy = (decltype(CommDestroy)) dlsym(lib, "ncclCommDestroy");
 		AllReduce = (decltype(AllReduce)) dlsym(lib, "ncclAllReduce");
+		AllGather = (decltype(AllGather)) dlsym(lib, "ncclAllGather");
 		GetErrorString = (decltype(GetErrorString)) dlsym(lib, "ncclGetErrorString");
-		if (!GetUniqueId || !CommInitRank || !CommDestroy || !AllReduce || !GetErrorString) { err = "NCCL library lacks an expected symbol"; return false; }
+		if (!GetUniqueId || !CommInitRank || !CommDestroy || !AllReduce || !AllGather || !GetErrorString) { err = "NCCL library lacks an expected symbol"; return false; }
 		return true;
 	}
 };
 
-constexpr int NCCL_UINT32 = 3, NCCL_UINT64 = 5, NCCL_SUM = 0, NCCL_MAX = 2;
+constexpr int NCCL_UINT8 = 1, NCCL_UINT32 = 3, NCCL_UINT64 = 5, NCCL_SUM = 0, NCCL_MAX = 2;
+constexpr int MAX_PEERS = 16; // GPUs of one box
+
+// What a kernel of a peer-mode build needs to find the authoritative copy of a rank: rank array of every GPU
+// (its own included; the others mapped through CUDA IPC over NVLink) and the column ranges the GPUs own.
+struct PeerView {
+	u32 *R[MAX_PEERS];
+	u32 xb[MAX_PEERS + 1]; // GPU g owns the text positions of columns [xb[g], xb[g+1]); '#' and the sentinel (column >= n) go to the last
+	int me, world;
+	__host__ __device__ int owner(u32 c) const {
+		int g = 0;
+		while (g + 1 < world && c >= xb[g + 1]) g++;
+		return g;
+	}
+};
 
 struct Dist {
 	int rank = 0, world = 1;
@@ -63,6 +80,35 @@ struct Dist {
 	}
 	void allreduce_sum_u64(u64 *buf, u64 count, cudaStream_t s) const {
 		if (world > 1 && count) check(api.AllReduce(buf, buf, count, NCCL_UINT64, NCCL_SUM, comm, s), "ncclAllReduce(sum,u64)");
+	}
+
+	// ---- peer memory (one process per GPU: CUDA IPC; the mappings live for one index build)
+	struct PeerMsg { cudaIpcMemHandle_t handle; u64 offset; u64 pad[7]; }; // 128 bytes
+	u8 *xchg = nullptr;                 // device staging of the all-gather
+	void *peer_map[MAX_PEERS] = {};     // mapped base of every peer's persistent arena
+	// Every rank publishes (arena base, offset of an array inside it); returns the array's address on every GPU.
+	void open_peers(void *arena_base, void *array, void **out /* [world] */, cudaStream_t s) {
+		if (world > MAX_PEERS) throw cuda_error("more GPUs than one box holds");
+		if (!xchg) FBG_CUDA(cudaMalloc(&xchg, sizeof(PeerMsg) * (MAX_PEERS + 1)));
+		PeerMsg mine;
+		memset(&mine, 0, sizeof mine);
+		FBG_CUDA(cudaIpcGetMemHandle(&mine.handle, arena_base));
+		mine.offset = (u64) ((char *) array - (char *) arena_base);
+		FBG_CUDA(cudaMemcpyAsync(xchg + sizeof(PeerMsg) * MAX_PEERS, &mine, sizeof mine, cudaMemcpyHostToDevice, s));
+		check(api.AllGather(xchg + sizeof(PeerMsg) * MAX_PEERS, xchg, sizeof(PeerMsg), NCCL_UINT8, comm, s), "ncclAllGather(ipc handles)");
+		PeerMsg all[MAX_PEERS];
+		FBG_CUDA(cudaMemcpyAsync(all, xchg, sizeof(PeerMsg) * world, cudaMemcpyDeviceToHost, s));
+		FBG_CUDA(cudaStreamSynchronize(s));
+		for (int g = 0; g < world; g++) {
+			if (g == rank) { out[g] = array; continue; }
+			if (!peer_map[g]) FBG_CUDA(cudaIpcOpenMemHandle(&peer_map[g], all[g].handle, cudaIpcMemLazyEnablePeerAccess));
+			out[g] = (char *) peer_map[g] + all[g].offset;
+		}
+	}
+	// after a barrier: nobody reads this GPU's arrays any more
+	void close_peers() {
+		for (int g = 0; g < MAX_PEERS; g++)
+			if (peer_map[g]) { cudaIpcCloseMemHandle(peer_map[g]); peer_map[g] = nullptr; }
 	}
 };
 

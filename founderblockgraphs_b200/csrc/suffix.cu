@@ -318,10 +318,12 @@ struct CompactOut {
 // the offsets this call appends at in its two target lists (null = 0).  A warp owns 512
 // consecutive entries and walks them 32 at a time: coalesced reads, ballot/popc ranks,
 // compacted (hence nearly coalesced) writes.
+// PEER (a multi-GPU build in peer mode, dist.cuh): the rank of position q is read from the GPU that owns q's column
+template <bool PEER>
 __global__ void __launch_bounds__(CP_THREADS, CP_MINB) k1_cls_write_kernel(const u8 *__restrict__ cls, const u32 *__restrict__ lp, const u32 *__restrict__ lr, u64 na,
                                                                   const u64 *__restrict__ partial, const u64 *__restrict__ base_a, const u64 *__restrict__ base_b,
                                                                   u32 ca, u32 cb, int tgt_a, int tgt_b,
-                                                                  const u32 *__restrict__ R, u64 hnext, u64 N, int nbits, CompactOut o) {
+                                                                  const u32 *__restrict__ R, u64 hnext, u64 N, int nbits, CompactOut o, const u32 *__restrict__ col, PeerView pv) {
 	__shared__ u64 wtot[CP_THREADS / 32];
 	const u32 w = threadIdx.x >> 5, l = threadIdx.x & 31;
 	const u64 w0 = (u64) blockIdx.x * CP_TILE + (u64) w * (32 * CP_ITEMS);
@@ -356,10 +358,24 @@ __global__ void __launch_bounds__(CP_THREADS, CP_MINB) k1_cls_write_kernel(const
 			pp[k] = 0; rr[k] = 0;
 			if (c[i0 + k]) { pp[k] = lp[t]; rr[k] = lr[t]; }
 		}
+		if (PEER) {
+			u32 cq[CP_CHUNK];
 #pragma unroll
-		for (int k = 0; k < CP_CHUNK; k++) {
-			const u64 q = (u64) pp[k] + hnext;
-			r2[k] = (c[i0 + k] && q < N) ? R[q] : 0u;
+			for (int k = 0; k < CP_CHUNK; k++) {
+				const u64 q = (u64) pp[k] + hnext;
+				cq[k] = (c[i0 + k] && q < N) ? col[q] : 0u;
+			}
+#pragma unroll
+			for (int k = 0; k < CP_CHUNK; k++) {
+				const u64 q = (u64) pp[k] + hnext;
+				r2[k] = (c[i0 + k] && q < N) ? __ldcg(pv.R[pv.owner(cq[k])] + q) : 0u; // never through L1: the owner rewrites it every round
+			}
+		} else {
+#pragma unroll
+			for (int k = 0; k < CP_CHUNK; k++) {
+				const u64 q = (u64) pp[k] + hnext;
+				r2[k] = (c[i0 + k] && q < N) ? R[q] : 0u;
+			}
 		}
 #pragma unroll
 		for (int k = 0; k < CP_CHUNK; k++) {
@@ -721,7 +737,7 @@ template <int CAP> static void launch_tile_sort(Dev &d, const u32 *lp, const u32
 // cnt_a / cnt_b: device words with the fill counts of those lists: read as the append offsets, then
 // raised by this call's totals (null for an unused class).  tot: a scratch device word.
 static void compact_lists(Dev &d, const u8 *cls, const u32 *lp, const u32 *lr, u64 na, u32 ca, int tgt_a, u64 *cnt_a, u32 cb, int tgt_b, u64 *cnt_b, u64 *tot,
-                          const u32 *R, u64 hnext, u64 N, int nbits, CompactOut o) {
+                          const u32 *R, u64 hnext, u64 N, int nbits, CompactOut o, const u32 *col = nullptr, const PeerView *pv = nullptr) {
 	if (na == 0) return;
 	u32 nt = div_up(na, CP_TILE);
 	u64 mk = d.mark();
@@ -729,7 +745,8 @@ static void compact_lists(Dev &d, const u8 *cls, const u32 *lp, const u32 *lr, u
 	d.begin(K_DOUBLING_AUX);
 	k1_cls_count_kernel<<<nt, CP_THREADS, 0, d.stream>>>(cls, na, ca, cb, partial);
 	scan_partials_kernel<OpSumU64><<<1, 1024, 0, d.stream>>>(partial, nt, tot);
-	k1_cls_write_kernel<<<nt, CP_THREADS, 0, d.stream>>>(cls, lp, lr, na, partial, cnt_a, cnt_b, ca, cb, tgt_a, tgt_b, R, hnext, N, nbits, o);
+	if (pv) k1_cls_write_kernel<true><<<nt, CP_THREADS, 0, d.stream>>>(cls, lp, lr, na, partial, cnt_a, cnt_b, ca, cb, tgt_a, tgt_b, R, hnext, N, nbits, o, col, *pv);
+	else k1_cls_write_kernel<false><<<nt, CP_THREADS, 0, d.stream>>>(cls, lp, lr, na, partial, cnt_a, cnt_b, ca, cb, tgt_a, tgt_b, R, hnext, N, nbits, o, nullptr, PeerView());
 	k1_add_totals_kernel<<<1, 1, 0, d.stream>>>(tot, cnt_a, cnt_b);
 	FBG_LAUNCH_CHECK();
 	d.end((double) na * (2.0 + 8.0 + 4.0 + 12.0));
@@ -1045,22 +1062,40 @@ __global__ void k1_dict_list_kernel(const u64 *__restrict__ key, const u32 *__re
 	u64 k = key[s];
 	if (k != KD_EMPTY) { u32 q = pos[s]; lk[q] = k; lv[q] = s; }
 }
-// bucket sizes in k-mer order: all of them (their exclusive scan = the ranks) and the big ones (B list offsets)
-__global__ void k1_dict_counts_kernel(const u32 *__restrict__ lv, const u32 *__restrict__ cnt, u32 nd, u32 *__restrict__ call, u32 *__restrict__ cbig) {
+// Peer mode (one MSA across several GPUs, dist.cuh): the dictionary is built by every GPU, the tied buckets are
+// dealt out by column.  A bucket whose members lie in one column belongs to the GPU that owns the column; a
+// bucket that spans columns (a repeat) is kept by EVERY GPU: each sorts it in full, identically, so whoever
+// owns a member's column holds that member's up-to-date rank without any rank crossing the wire.
+__global__ void k1_dict_spans_kernel(const u32 *__restrict__ slot_of, const u32 *__restrict__ first, const u32 *__restrict__ col, u64 N, u8 *__restrict__ spans) {
+	u64 p = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (p >= N) return;
+	const u32 s = slot_of[p];
+	if (col[p] != __ldg(col + first[s])) spans[s] = 1;
+}
+__global__ void k1_dict_mine_kernel(const u32 *__restrict__ lv, const u32 *__restrict__ first, const u32 *__restrict__ col, const u8 *__restrict__ spans, u32 nd, PeerView pv, u8 *__restrict__ mine) {
+	u32 t = blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= nd) return;
+	const u32 s = lv[t];
+	mine[t] = (spans[s] || pv.owner(col[first[s]]) == pv.me) ? 1 : 0;
+}
+// bucket sizes in k-mer order: all of them (their exclusive scan = the ranks) and the big ones (B list offsets);
+// mine: null, or which buckets this GPU sorts
+__global__ void k1_dict_counts_kernel(const u32 *__restrict__ lv, const u32 *__restrict__ cnt, const u8 *__restrict__ mine, u32 nd, u32 *__restrict__ call, u32 *__restrict__ cbig) {
 	u32 t = blockIdx.x * blockDim.x + threadIdx.x;
 	if (t >= nd) return;
 	u32 c = cnt[lv[t]];
-	call[t] = c; cbig[t] = c > BSMALL ? c : 0u;
+	call[t] = c; cbig[t] = (c > BSMALL && (!mine || mine[t])) ? c : 0u;
 }
 // info[slot] = (rank, start of the bucket in its list, size, smallest member); the start of a B bucket is set here
 // (B list in k-mer order), that of an S / M bucket by k1_dict_place_kernel
 __global__ void k1_dict_assign_kernel(const u32 *__restrict__ lv, const u32 *__restrict__ cnt, const u32 *__restrict__ first, const u32 *__restrict__ rk, const u32 *__restrict__ bs,
-                                      u32 nd, u32 rank_off, u32 mid_min, uint4 *__restrict__ info, u32 *__restrict__ rank_of_slot, u32 *__restrict__ maxb) {
+                                      const u8 *__restrict__ mine, u32 nd, u32 rank_off, u32 mid_min, uint4 *__restrict__ info, u32 *__restrict__ rank_of_slot, u32 *__restrict__ maxb) {
 	u32 t = blockIdx.x * blockDim.x + threadIdx.x;
 	u32 small = 0;
 	if (t < nd) {
 		u32 s = lv[t], c = cnt[s], f = first[s], start = 0;
-		if (c > BSMALL) start = bs[t];
+		if (mine && !mine[t]) start = U32_MAX; // sorted by another GPU: no list entry here
+		else if (c > BSMALL) start = bs[t];
 		else if (c > 1 && c < mid_min) small = c;
 		info[s] = make_uint4(rank_off + rk[t], start, c, f);
 		rank_of_slot[s] = rank_off + rk[t];
@@ -1077,10 +1112,11 @@ __global__ void k1_dict_firstkeys_kernel(const u32 *__restrict__ lv, const u32 *
 	ok[t] = first[lv[t]]; ov[t] = t;
 }
 // in that order: sizes of the S-class and of the M-class buckets (their exclusive scans = the list offsets)
-__global__ void k1_dict_sizes_kernel(const u32 *__restrict__ ov, const u32 *__restrict__ lv, const u32 *__restrict__ cnt, u32 nd, u32 mid_min, u32 *__restrict__ zs, u32 *__restrict__ zm) {
+__global__ void k1_dict_sizes_kernel(const u32 *__restrict__ ov, const u32 *__restrict__ lv, const u32 *__restrict__ cnt, const u8 *__restrict__ mine, u32 nd, u32 mid_min, u32 *__restrict__ zs, u32 *__restrict__ zm) {
 	u32 j = blockIdx.x * blockDim.x + threadIdx.x;
 	if (j >= nd) return;
-	const u32 c = cnt[lv[ov[j]]];
+	u32 c = cnt[lv[ov[j]]];
+	if (mine && !mine[ov[j]]) c = 0;
 	zs[j] = (c > 1 && c < mid_min) ? c : 0u;
 	zm[j] = (c >= mid_min && c <= BSMALL) ? c : 0u;
 }
@@ -1089,7 +1125,7 @@ __global__ void k1_dict_place_kernel(const u32 *__restrict__ ov, const u32 *__re
 	if (j >= nd) return;
 	const u32 s = lv[ov[j]];
 	uint4 v = info[s];
-	if (v.z > 1 && v.z <= BSMALL) { v.y = v.z < mid_min ? zs[j] : zm[j]; info[s] = v; }
+	if (v.z > 1 && v.z <= BSMALL && v.y != U32_MAX) { v.y = v.z < mid_min ? zs[j] : zm[j]; info[s] = v; }
 }
 // what the sort-based round 0 leaves behind: ranks, SA entries of the suffixes alone in their
 // bucket, the S, M and B lists of the next round with R[p+h] looked up (through the table: no
@@ -1101,6 +1137,7 @@ __global__ void __launch_bounds__(256) k1_dict_emit_kernel(const u32 *__restrict
 	const uint4 v = __ldg(info + slot_of[p]);
 	R[p] = v.x;
 	if (v.z == 1) { SA[v.x] = (u32) p; return; }
+	if (v.y == U32_MAX) return; // peer mode: another GPU sorts this bucket
 	const u64 pn = p + hnext;
 	const u32 r2 = pn < N ? __ldg(rank_of_slot + slot_of[pn]) : 0u; // 4-byte entries: a quarter of the L2 traffic of info[]
 	const u32 q = v.y + ord_of[p];
@@ -1116,13 +1153,14 @@ static u32 dict_capacity(u64 N) {
 }
 static u64 dict_scratch_bytes(u64 N) {
 	u64 cap = dict_capacity(N);
-	return cap * (8 + 4 + 4 + 16 + 4) + (cap / 2) * (16 + 8 + 8 + 16 + 8) + (cap / SCAN_TILE + 2) * 24 + (cap / 2 / RS_TILE + 2) * RS_BINS * 12 + (1u << 16);
+	return cap * (8 + 4 + 4 + 16 + 4 + 1) + (cap / 2) * (16 + 8 + 8 + 16 + 8 + 1) + (cap / SCAN_TILE + 2) * 24 + (cap / 2 / RS_TILE + 2) * RS_BINS * 12 + (1u << 16);
 }
 
 // Returns false (nothing written that matters) when the text has too many distinct k-mers for
 // the table: the caller then sorts all suffixes as before.
+// pv: null, or the column ranges of a peer-mode build (this GPU lists only the buckets it sorts; list_cap = room in its lists)
 static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int key_bits0, u32 km_grid, u32 *slot_of, u32 *ord_of, u32 mid_min,
-                           u64 hnext, int nbits, CompactOut o, u64 *nS, u64 *nM, u64 *nB, u32 *maxb, bool try_pure) {
+                           u64 hnext, int nbits, CompactOut o, u64 *nS, u64 *nM, u64 *nB, u32 *maxb, bool try_pure, const PeerView *pv = nullptr, u64 list_cap = 0) {
 	Dev &d = p.dev;
 	const u64 N = p.N;
 	const u32 cap = dict_capacity(N), ndmax = cap / 2;
@@ -1220,14 +1258,26 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	const int cur = radix_sort<u64, true>(d, lb, nd, 0, key_bits0);
 	const u32 *lv = lb.v[cur];
 	const u32 gn = div_up(nd, 256);
+	u8 *mine = nullptr;
+	if (pv) {
+		u8 *spans = d.alloc<u8>(cap);
+		mine = d.alloc<u8>(ndmax);
+		FBG_CUDA(cudaMemsetAsync(spans, 0, cap, d.stream));
+		d.begin(K_DOUBLING_AUX);
+		k1_dict_spans_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, dk.first, p.col, N, spans);
+		k1_dict_mine_kernel<<<gn, 256, 0, d.stream>>>(lv, dk.first, p.col, spans, nd, *pv, mine);
+		FBG_LAUNCH_CHECK();
+		d.end((double) N * 8.0 + (double) nd * 13.0);
+		d.note_launches(K_DOUBLING_AUX, 1);
+	}
 	d.begin(K_DOUBLING_AUX);
-	k1_dict_counts_kernel<<<gn, 256, 0, d.stream>>>(lv, dk.cnt, nd, call, cbig);
+	k1_dict_counts_kernel<<<gn, 256, 0, d.stream>>>(lv, dk.cnt, mine, nd, call, cbig);
 	FBG_LAUNCH_CHECK();
 	d.end((double) nd * 16.0);
 	device_scan<OpSumU32, true>(d, call, call, nd);
 	device_scan<OpSumU32, true>(d, cbig, cbig, nd, sc + 3);
 	d.begin(K_DOUBLING_AUX);
-	k1_dict_assign_kernel<<<gn, 256, 0, d.stream>>>(lv, dk.cnt, dk.first, call, cbig, nd, 0u, mid_min, info, rank_of_slot, sc + 4);
+	k1_dict_assign_kernel<<<gn, 256, 0, d.stream>>>(lv, dk.cnt, dk.first, call, cbig, mine, nd, 0u, mid_min, info, rank_of_slot, sc + 4);
 	FBG_LAUNCH_CHECK();
 	d.end((double) nd * 40.0);
 	if (try_pure && !known_impure) {
@@ -1257,11 +1307,23 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	const u32 *ov = ob.v[oc];
 	u32 *zs = call, *zm = cbig; // both scans were consumed by k1_dict_assign_kernel
 	d.begin(K_DOUBLING_AUX);
-	k1_dict_sizes_kernel<<<gn, 256, 0, d.stream>>>(ov, lv, dk.cnt, nd, mid_min, zs, zm);
+	k1_dict_sizes_kernel<<<gn, 256, 0, d.stream>>>(ov, lv, dk.cnt, mine, nd, mid_min, zs, zm);
 	FBG_LAUNCH_CHECK();
 	d.end((double) nd * 20.0);
 	device_scan<OpSumU32, true>(d, zs, zs, nd, sc + 2);
 	device_scan<OpSumU32, true>(d, zm, zm, nd, sc + 5);
+	if (pv) {
+		// the lists were sized for this GPU's share of the columns: check before anything is written into them
+		FBG_CUDA(cudaMemcpyAsync(h_sc, sc, 6 * sizeof(u32), cudaMemcpyDeviceToHost, d.stream));
+		FBG_CUDA(cudaStreamSynchronize(d.stream));
+		// (all GPUs decide alike: the build changes form if any of them is short of room)
+		p.h_scalars[63] = ((u64) h_sc[2] + h_sc[5] + h_sc[3] > list_cap) ? 1 : 0;
+		FBG_CUDA(cudaMemcpyAsync(p.scalars + 63, p.h_scalars + 63, sizeof(u64), cudaMemcpyHostToDevice, d.stream));
+		p.dist.allreduce_sum_u64(p.scalars + 63, 1, d.stream);
+		FBG_CUDA(cudaMemcpyAsync(p.h_scalars + 63, p.scalars + 63, sizeof(u64), cudaMemcpyDeviceToHost, d.stream));
+		FBG_CUDA(cudaStreamSynchronize(d.stream));
+		if (p.h_scalars[63]) { d.release(mk); return false; }
+	}
 	d.begin(K_DOUBLING_AUX);
 	k1_dict_place_kernel<<<gn, 256, 0, d.stream>>>(ov, lv, nd, mid_min, zs, zm, info);
 	k1_dict_emit_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, p.SA, o);
@@ -1277,13 +1339,13 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 
 void k1_suffix_array(Pipeline &p) {
 	Dev &d = p.dev;
-	const Dist &dist = p.dist;
+	Dist &dist = p.dist;
 	const bool sharded = dist.world > 1;
 	const u64 N = p.N;
 	if (!p.ISA) p.ISA = p.dev.palloc<u32>(N + 1); // (a full index built after a sufficient one re-uses the arrays)
 	if (!p.SA) p.SA = p.dev.palloc<u32>(N + 1);
 	if (!p.PLCP) p.PLCP = p.dev.palloc<u32>(N + 1);
-	p.index_lazy = false; p.lazy_depth = 0; p.index_virtual = false; p.dict_nd = 0;
+	p.index_lazy = false; p.lazy_depth = 0; p.index_virtual = false; p.dict_nd = 0; p.isa_partial = false;
 	// the sufficient index (above): gapless rows, one GPU, unless the full index was asked for
 	const bool lazy_ok = !sharded && p.gaps == 0 && !p.want_full_index && !getenv("FBG_FULL_INDEX");
 	d.ensure((sharded ? 1u : 0u) * (u64) (4u << KM_HBITS) + (1u << 20));
@@ -1317,7 +1379,14 @@ void k1_suffix_array(Pipeline &p) {
 	sh.block_off = nullptr; sh.hist = nullptr; sh.block_cnt = nullptr;
 	u64 nloc = N;      // suffixes sorted here
 	u32 rank_off = 0;  // global rank of the first of them
-	if (sharded) {
+	// Peer mode (several GPUs, the preferred form): every GPU builds the k-mer dictionary of round 0, the tied buckets
+	// are dealt out by COLUMN range, every GPU keeps the ranks of its own columns up to date and reads the ranks of
+	// other columns straight from their owner's memory over NVLink (CUDA IPC).  No rank array is ever all-reduced.
+	// The older form (k-mer key ranges, rank replicas merged by all-reduce(max) every round) remains for texts
+	// the dictionary does not take (p.no_peer: set for one build when the peer attempt had to be given up).
+	bool peer = sharded && key_bits0 < 64 && !p.no_peer && !getenv("FBG_NO_KMER_DICT") && !getenv("FBG_NO_PEER");
+	p.no_peer = false;
+	if (sharded && !peer) {
 		const u32 nbins = 1u << KM_HBITS;
 		u64 mk2 = d.mark();
 		u32 *hist = d.alloc<u32>(nbins);
@@ -1338,11 +1407,16 @@ void k1_suffix_array(Pipeline &p) {
 		nloc = mine; rank_off = (u32) before;
 		d.release(mk2);
 	}
-	const u64 cap = nloc ? nloc : 1;
+	u64 cap = nloc ? nloc : 1;
+	if (peer) { // this GPU's share of the columns, with room for uneven columns and for the buckets every GPU keeps
+		cap = N / (u64) dist.world + N / (2 * (u64) dist.world) + (8u << 20);
+		if (cap > N) cap = N;
+	}
+	const u64 capN = peer ? N : cap; // the dictionary's per-position arrays cover the whole text
 	// scratch of this phase: 98 B per suffix sorted here (sort ping-pong 24, heads 16, classes 2,
-	// S lists 24, M lists 24, sorter outputs 8) + radix count matrices + (sharded) the N-word bucket directory
+	// S lists 24, M lists 24, sorter outputs 8) + radix count matrices + (key-range form) the N-word bucket directory
 	d.release(mk);
-	d.ensure(cap * 100 + (cap / RS_TILE + 2) * RS_BINS * 12 + (u64) km_grid * 8 + (sharded ? N * 4 + (N / SCAN_TILE + 2) * 24 : dict_scratch_bytes(N)) + (16u << 20));
+	d.ensure(cap * 100 + (capN - cap) * 8 + (cap / RS_TILE + 2) * RS_BINS * 12 + (u64) km_grid * 8 + (sharded && !peer ? N * 4 + (N / SCAN_TILE + 2) * 24 : dict_scratch_bytes(N)) + (16u << 20));
 	mk = d.mark();
 
 	RadixBuffers rb;
@@ -1350,7 +1424,7 @@ void k1_suffix_array(Pipeline &p) {
 	rb.v[0] = d.alloc<u32>(cap); rb.v[1] = d.alloc<u32>(cap);
 	rb.cur = 0;
 	u64 *HH = d.alloc<u64>(cap);
-	u32 *HR = d.alloc<u32>(cap), *newr = d.alloc<u32>(cap);
+	u32 *HR = d.alloc<u32>(capN), *newr = d.alloc<u32>(capN);
 	u8 *clsB = d.alloc<u8>(cap + 16), *clsS = d.alloc<u8>(cap + 16);
 	u32 *Slp[2], *Slr[2], *Sr2[2], *Mlp[2], *Mlr[2], *Mr2[2];
 	for (int q = 0; q < 2; q++) { Slp[q] = d.alloc<u32>(cap); Slr[q] = d.alloc<u32>(cap); Sr2[q] = d.alloc<u32>(cap); }
@@ -1370,15 +1444,34 @@ void k1_suffix_array(Pipeline &p) {
 	int sc = 0;           // current S / M lists
 	// ... unless the k-mer dictionary takes it: no sort, ranks written in text order
 	bool by_dict = false;
+	PeerView pv;
+	memset(&pv, 0, sizeof pv);
+	if (peer) {
+		pv.me = dist.rank; pv.world = dist.world;
+		for (int g = 0; g < dist.world; g++) { u64 a, bq; plan_columns(p.n, dist.world, g, &a, &bq); pv.xb[g] = (u32) a; pv.xb[g + 1] = (u32) bq; }
+		void *rp[MAX_PEERS];
+		dist.open_peers(d.pers, p.ISA, rp, d.stream);
+		for (int g = 0; g < dist.world; g++) pv.R[g] = static_cast<u32 *>(rp[g]);
+		FBG_CUDA(cudaMemsetAsync(p.SA, 0, N * sizeof(u32), d.stream)); // every GPU writes the SA entries of the buckets it sorts; merged by max at the end
+	}
 	u32 mid_want = MID_MIN; // FBG_MID_MIN: test hook (64 ..: small inputs through the M path; above BSMALL: no M list)
 	if (const char *e = getenv("FBG_MID_MIN")) { long v = atol(e); mid_want = v > (long) BSMALL ? BSMALL + 1 : (v < 64 ? 64u : (u32) v); }
-	if (!sharded && key_bits0 < 64 && !getenv("FBG_NO_KMER_DICT")) {
+	if ((!sharded || peer) && key_bits0 < 64 && !getenv("FBG_NO_KMER_DICT")) {
 		CompactOut o;
 		o.Slp = Slp[1]; o.Slr = Slr[1]; o.Sr2 = Sr2[1];
 		o.Mlp = Mlp[1]; o.Mlr = Mlr[1]; o.Mr2 = Mr2[1];
 		o.Bkey = (u64 *) rb.k[1]; o.Bval = rb.v[1];
 		by_dict = k1_round0_dict(p, tab, K, b, key_bits0, km_grid, HR, newr, mid_want, (u64) K, nbits, o, &nS, &nM, &nB, &maxb,
-		                         lazy_ok && (u64) K <= LAZY_MAX_DEPTH);
+		                         lazy_ok && (u64) K <= LAZY_MAX_DEPTH, peer ? &pv : nullptr, cap);
+	}
+	if (peer && !by_dict) {
+		// the dictionary did not take this text (or a GPU's share outgrew its lists) -- on every GPU alike: key-range form
+		FBG_CUDA(cudaStreamSynchronize(d.stream));
+		dist.close_peers();
+		d.release(mk);
+		p.no_peer = true;
+		k1_suffix_array(p);
+		return;
 	}
 	// the M list (buckets of MID_MIN .. BSMALL suffixes streamed one per CTA) needs the text-ordered layout the
 	// dictionary's round 0 gives it; builds whose round 0 sorts all suffixes keep everything up to BSMALL in the S list
@@ -1505,11 +1598,13 @@ void k1_suffix_array(Pipeline &p) {
 			FBG_LAUNCH_CHECK();
 			d.end((double) nB * (8.0 + 4.0 + 8.0 + 4.0 + 4.0 + 4.0 + 1.0));
 		}
-		// ---- merge the rank replicas: every GPU raised only the ranks of its own suffixes
+		// ---- key-range form: merge the rank replicas (every GPU raised only the ranks of its own suffixes);
+		//      peer mode: only a barrier -- every GPU's rank updates of this round are done before anyone looks ranks up
 		if (sharded) {
 			d.begin(K_COMM);
-			dist.allreduce_max_u32(p.ISA, N, d.stream);
-			d.end((double) N * 8.0);
+			if (peer) dist.allreduce_sum_u64(p.scalars + 62, 1, d.stream);
+			else dist.allreduce_max_u32(p.ISA, N, d.stream);
+			d.end(peer ? 16.0 : (double) N * 8.0);
 		}
 		// ---- next lists (all rank updates of this round are enqueued before these look-ups)
 		u64 hnext = h;
@@ -1542,9 +1637,10 @@ void k1_suffix_array(Pipeline &p) {
 			compact_lists(d, clsB, sv, newr, nB, CLS_NONE, TGT_S, nullptr, CLS_BIG, TGT_B, cnt + 2, ctot, p.ISA, hnext, N, nbits, o);
 		} else {
 			// the sorted S and M lists lie back to back in the sorter outputs: one pass moves both
-			compact_lists(d, clsS, lp_out, lr_out, nS + nM, CLS_SMALL, TGT_S, cnt, CLS_MID, TGT_M, cnt + 1, ctot, p.ISA, hnext, N, nbits, o);
-			compact_lists(d, clsB, sv, newr, nB, CLS_SMALL, TGT_S, cnt, CLS_BIG, TGT_B, cnt + 2, ctot, p.ISA, hnext, N, nbits, o);
-			if (mid_min <= BSMALL) compact_lists(d, clsB, sv, newr, nB, CLS_MID, TGT_M, cnt + 1, CLS_NONE, TGT_B, nullptr, ctot, p.ISA, hnext, N, nbits, o);
+			const PeerView *pvp = peer ? &pv : nullptr;
+			compact_lists(d, clsS, lp_out, lr_out, nS + nM, CLS_SMALL, TGT_S, cnt, CLS_MID, TGT_M, cnt + 1, ctot, p.ISA, hnext, N, nbits, o, p.col, pvp);
+			compact_lists(d, clsB, sv, newr, nB, CLS_SMALL, TGT_S, cnt, CLS_BIG, TGT_B, cnt + 2, ctot, p.ISA, hnext, N, nbits, o, p.col, pvp);
+			if (mid_min <= BSMALL) compact_lists(d, clsB, sv, newr, nB, CLS_MID, TGT_M, cnt + 1, CLS_NONE, TGT_B, nullptr, ctot, p.ISA, hnext, N, nbits, o, p.col, pvp);
 		}
 		k1_active_total_kernel<<<1, 1, 0, d.stream>>>(cnt, gtot);
 		if (sharded) dist.allreduce_sum_u64(gtot, 1, d.stream);
@@ -1568,6 +1664,17 @@ void k1_suffix_array(Pipeline &p) {
 		d.begin(K_COMM);
 		dist.allreduce_max_u32(p.SA, N, d.stream);
 		d.end((double) N * 8.0);
+	}
+	if (peer) {
+		// Ranks: every GPU holds the final ranks of its own columns (what its share of K2 reads); the other
+		// entries are older, hence smaller, values.  The full inverse is only assembled when somebody asks for it.
+		if (p.want_full_index) {
+			d.begin(K_COMM);
+			dist.allreduce_max_u32(p.ISA, N, d.stream);
+			d.end((double) N * 8.0);
+		} else p.isa_partial = true;
+		FBG_CUDA(cudaStreamSynchronize(d.stream)); // past the SA all-reduce: no GPU reads another's ranks any more
+		dist.close_peers();
 	}
 	d.release(mk);
 }
