@@ -45,7 +45,7 @@ void Pipeline::free_all() {
 	col = ISA = SA = PLCP = f = bnd = dp_a = dp_b = dp_v = nullptr;
 	dev.pers_top = 0;
 	have_msa = have_index = have_f = have_seg = have_xgfa = false;
-	want_full_index = index_lazy = false; lazy_depth = 0; isa_partial = false;
+	want_full_index = index_lazy = false; lazy_depth = 0;
 	index_virtual = force_arrays = false; dict_col = dict_lcp = nullptr; dict_nd = 0;
 }
 
@@ -157,14 +157,6 @@ static int build_index_impl(fbg_ctx *ctx, bool full, bool need_arrays = true) {
 	FBG_TRY(ctx)
 	Pipeline &p = ctx->p;
 	FBG_CUDA(cudaSetDevice(p.dev.device));
-	if (p.have_index && full && p.isa_partial) {
-		// peer-mode build: assemble the full inverse from the GPUs' column shares (collective; all ranks make the same calls)
-		p.dev.begin(K_COMM);
-		p.dist.allreduce_max_u32(p.ISA, p.N, p.dev.stream);
-		p.dev.end((double) p.N * 8.0);
-		FBG_CUDA(cudaStreamSynchronize(p.dev.stream));
-		p.isa_partial = false;
-	}
 	if (p.have_index && !(full && p.index_lazy) && !(need_arrays && p.index_virtual)) return FBG_OK;
 	p.want_full_index = full; // per call: a later rebuild on this MSA (new ignore set) may take the sufficient index again
 	p.force_arrays = need_arrays; // need_arrays: a consumer that reads SA / ISA / PLCP follows

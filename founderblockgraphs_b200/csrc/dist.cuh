@@ -82,10 +82,11 @@ struct Dist {
 		if (world > 1 && count) check(api.AllReduce(buf, buf, count, NCCL_UINT64, NCCL_SUM, comm, s), "ncclAllReduce(sum,u64)");
 	}
 
-	// ---- peer memory (one process per GPU: CUDA IPC; the mappings live for one index build)
+	// ---- peer memory (one process per GPU: CUDA IPC)
 	struct PeerMsg { cudaIpcMemHandle_t handle; u64 offset; u64 pad[7]; }; // 128 bytes
 	u8 *xchg = nullptr;                 // device staging of the all-gather
 	void *peer_map[MAX_PEERS] = {};     // mapped base of every peer's persistent arena
+	cudaIpcMemHandle_t peer_handle[MAX_PEERS];
 	// Every rank publishes (arena base, offset of an array inside it); returns the array's address on every GPU.
 	void open_peers(void *arena_base, void *array, void **out /* [world] */, cudaStream_t s) {
 		if (world > MAX_PEERS) throw cuda_error("more GPUs than one box holds");
@@ -101,11 +102,16 @@ struct Dist {
 		FBG_CUDA(cudaStreamSynchronize(s));
 		for (int g = 0; g < world; g++) {
 			if (g == rank) { out[g] = array; continue; }
-			if (!peer_map[g]) FBG_CUDA(cudaIpcOpenMemHandle(&peer_map[g], all[g].handle, cudaIpcMemLazyEnablePeerAccess));
+			// mapping a peer's arena costs tens of milliseconds: kept across builds, renewed when the peer's arena moved
+			if (peer_map[g] && memcmp(&peer_handle[g], &all[g].handle, sizeof(cudaIpcMemHandle_t)) != 0) { cudaIpcCloseMemHandle(peer_map[g]); peer_map[g] = nullptr; }
+			if (!peer_map[g]) {
+				FBG_CUDA(cudaIpcOpenMemHandle(&peer_map[g], all[g].handle, cudaIpcMemLazyEnablePeerAccess));
+				peer_handle[g] = all[g].handle;
+			}
 			out[g] = (char *) peer_map[g] + all[g].offset;
 		}
 	}
-	// after a barrier: nobody reads this GPU's arrays any more
+	// (leaving the communicator, or giving the peer form up for a build)
 	void close_peers() {
 		for (int g = 0; g < MAX_PEERS; g++)
 			if (peer_map[g]) { cudaIpcCloseMemHandle(peer_map[g]); peer_map[g] = nullptr; }

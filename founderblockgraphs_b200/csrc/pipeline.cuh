@@ -141,8 +141,7 @@ struct Pipeline {
 	// no per-position array at all: the sorted list of DISTINCT k-mers with their column and the
 	// LCP to the k-mer before is the whole index ("virtual"; fcol.cu k2_from_dict)
 	bool index_virtual = false, force_arrays = false;
-	// multi-GPU build in peer mode (suffix.cu): ISA holds final ranks for this GPU's columns only until somebody asks for all
-	bool isa_partial = false, no_peer = false;
+	bool no_peer = false; // multi-GPU: the peer-mode attempt of this build was given up, use the key-range form (suffix.cu)
 	u32 *dict_col = nullptr, *dict_lcp = nullptr; // [dict_nd], [dict_nd + 1] in rank order
 	u64 dict_nd = 0;
 	// K5: formatted xGFA bytes (own allocation, grown on demand, kept across builds)

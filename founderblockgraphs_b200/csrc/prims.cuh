@@ -2,6 +2,8 @@
 // per-kernel event accounting, three-phase tiled scans and the LSD radix sort
 // (warp match/ballot ranking + shared-memory staged bucket histograms).
 #pragma once
+#include <cstdlib>
+#include <cstdio>
 #include "common.cuh"
 #include <vector>
 
@@ -88,9 +90,11 @@ struct Dev {
 	void note_launches(int id, u64 extra) { if (timing) stats[id].launches += extra; }
 	// call after a stream synchronize
 	void resolve() {
+		static const bool trace = getenv("FBG_TRACE") != nullptr; // every timed launch group, in launch order, on stderr
 		for (auto &r : recs) {
 			float ms = 0.f;
 			FBG_CUDA(cudaEventElapsedTime(&ms, r.a, r.b));
+			if (trace) fprintf(stderr, "[fbg-trace] dev %d group %2d %9.3f ms %12.0f B\n", device, r.id, ms, r.bytes);
 			stats[r.id].ms += ms; stats[r.id].bytes += r.bytes;
 			pool.push_back(r.a); pool.push_back(r.b);
 		}

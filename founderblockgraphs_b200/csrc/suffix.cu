@@ -323,8 +323,13 @@ template <bool PEER>
 __global__ void __launch_bounds__(CP_THREADS, CP_MINB) k1_cls_write_kernel(const u8 *__restrict__ cls, const u32 *__restrict__ lp, const u32 *__restrict__ lr, u64 na,
                                                                   const u64 *__restrict__ partial, const u64 *__restrict__ base_a, const u64 *__restrict__ base_b,
                                                                   u32 ca, u32 cb, int tgt_a, int tgt_b,
-                                                                  const u32 *__restrict__ R, u64 hnext, u64 N, int nbits, CompactOut o, const u32 *__restrict__ col, PeerView pv) {
+                                                                  const u32 *__restrict__ R, u64 hnext, u64 N, int nbits, CompactOut o, const u32 *__restrict__ col, const PeerView *__restrict__ pvp) {
 	__shared__ u64 wtot[CP_THREADS / 32];
+	__shared__ PeerView pv; // (dynamic indexing of a by-value kernel parameter would put a copy into every thread's local memory)
+	if (PEER) {
+		for (u32 q = threadIdx.x; q < sizeof(PeerView) / 4; q += CP_THREADS) reinterpret_cast<u32 *>(&pv)[q] = reinterpret_cast<const u32 *>(pvp)[q];
+		// wtot's barrier below also publishes pv
+	}
 	const u32 w = threadIdx.x >> 5, l = threadIdx.x & 31;
 	const u64 w0 = (u64) blockIdx.x * CP_TILE + (u64) w * (32 * CP_ITEMS);
 	// pass 1: this warp's counts
@@ -745,8 +750,8 @@ static void compact_lists(Dev &d, const u8 *cls, const u32 *lp, const u32 *lr, u
 	d.begin(K_DOUBLING_AUX);
 	k1_cls_count_kernel<<<nt, CP_THREADS, 0, d.stream>>>(cls, na, ca, cb, partial);
 	scan_partials_kernel<OpSumU64><<<1, 1024, 0, d.stream>>>(partial, nt, tot);
-	if (pv) k1_cls_write_kernel<true><<<nt, CP_THREADS, 0, d.stream>>>(cls, lp, lr, na, partial, cnt_a, cnt_b, ca, cb, tgt_a, tgt_b, R, hnext, N, nbits, o, col, *pv);
-	else k1_cls_write_kernel<false><<<nt, CP_THREADS, 0, d.stream>>>(cls, lp, lr, na, partial, cnt_a, cnt_b, ca, cb, tgt_a, tgt_b, R, hnext, N, nbits, o, nullptr, PeerView());
+	if (pv) k1_cls_write_kernel<true><<<nt, CP_THREADS, 0, d.stream>>>(cls, lp, lr, na, partial, cnt_a, cnt_b, ca, cb, tgt_a, tgt_b, R, hnext, N, nbits, o, col, pv);
+	else k1_cls_write_kernel<false><<<nt, CP_THREADS, 0, d.stream>>>(cls, lp, lr, na, partial, cnt_a, cnt_b, ca, cb, tgt_a, tgt_b, R, hnext, N, nbits, o, nullptr, nullptr);
 	k1_add_totals_kernel<<<1, 1, 0, d.stream>>>(tot, cnt_a, cnt_b);
 	FBG_LAUNCH_CHECK();
 	d.end((double) na * (2.0 + 8.0 + 4.0 + 12.0));
@@ -1063,14 +1068,17 @@ __global__ void k1_dict_list_kernel(const u64 *__restrict__ key, const u32 *__re
 	if (k != KD_EMPTY) { u32 q = pos[s]; lk[q] = k; lv[q] = s; }
 }
 // Peer mode (one MSA across several GPUs, dist.cuh): the dictionary is built by every GPU, the tied buckets are
-// dealt out by column.  A bucket whose members lie in one column belongs to the GPU that owns the column; a
-// bucket that spans columns (a repeat) is kept by EVERY GPU: each sorts it in full, identically, so whoever
+// dealt out by column range.  A bucket whose members all lie in the columns of one GPU belongs to that GPU
+// (the usual case: one column, or a few neighbouring ones -- the character before a gap run often shares
+// its k-mer with the column the run ends in).  A bucket that spans the ranges of several GPUs (a gap run
+// across a range boundary, a repeat) is kept by EVERY GPU: each sorts it in full, identically, so whoever
 // owns a member's column holds that member's up-to-date rank without any rank crossing the wire.
-__global__ void k1_dict_spans_kernel(const u32 *__restrict__ slot_of, const u32 *__restrict__ first, const u32 *__restrict__ col, u64 N, u8 *__restrict__ spans) {
+__global__ void k1_dict_spans_kernel(const u32 *__restrict__ slot_of, const u32 *__restrict__ first, const u32 *__restrict__ col, u64 N, PeerView pv, u8 *__restrict__ spans) {
 	u64 p = (u64) blockIdx.x * blockDim.x + threadIdx.x;
 	if (p >= N) return;
 	const u32 s = slot_of[p];
-	if (col[p] != __ldg(col + first[s])) spans[s] = 1;
+	const u32 ca = col[p], cb = __ldg(col + first[s]);
+	if (ca != cb && pv.owner(ca) != pv.owner(cb)) spans[s] = 1;
 }
 __global__ void k1_dict_mine_kernel(const u32 *__restrict__ lv, const u32 *__restrict__ first, const u32 *__restrict__ col, const u8 *__restrict__ spans, u32 nd, PeerView pv, u8 *__restrict__ mine) {
 	u32 t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1264,7 +1272,7 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 		mine = d.alloc<u8>(ndmax);
 		FBG_CUDA(cudaMemsetAsync(spans, 0, cap, d.stream));
 		d.begin(K_DOUBLING_AUX);
-		k1_dict_spans_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, dk.first, p.col, N, spans);
+		k1_dict_spans_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, dk.first, p.col, N, *pv, spans);
 		k1_dict_mine_kernel<<<gn, 256, 0, d.stream>>>(lv, dk.first, p.col, spans, nd, *pv, mine);
 		FBG_LAUNCH_CHECK();
 		d.end((double) N * 8.0 + (double) nd * 13.0);
@@ -1345,7 +1353,7 @@ void k1_suffix_array(Pipeline &p) {
 	if (!p.ISA) p.ISA = p.dev.palloc<u32>(N + 1); // (a full index built after a sufficient one re-uses the arrays)
 	if (!p.SA) p.SA = p.dev.palloc<u32>(N + 1);
 	if (!p.PLCP) p.PLCP = p.dev.palloc<u32>(N + 1);
-	p.index_lazy = false; p.lazy_depth = 0; p.index_virtual = false; p.dict_nd = 0; p.isa_partial = false;
+	p.index_lazy = false; p.lazy_depth = 0; p.index_virtual = false; p.dict_nd = 0;
 	// the sufficient index (above): gapless rows, one GPU, unless the full index was asked for
 	const bool lazy_ok = !sharded && p.gaps == 0 && !p.want_full_index && !getenv("FBG_FULL_INDEX");
 	d.ensure((sharded ? 1u : 0u) * (u64) (4u << KM_HBITS) + (1u << 20));
@@ -1444,7 +1452,7 @@ void k1_suffix_array(Pipeline &p) {
 	int sc = 0;           // current S / M lists
 	// ... unless the k-mer dictionary takes it: no sort, ranks written in text order
 	bool by_dict = false;
-	PeerView pv;
+	PeerView pv, *pv_dev = nullptr;
 	memset(&pv, 0, sizeof pv);
 	if (peer) {
 		pv.me = dist.rank; pv.world = dist.world;
@@ -1452,6 +1460,9 @@ void k1_suffix_array(Pipeline &p) {
 		void *rp[MAX_PEERS];
 		dist.open_peers(d.pers, p.ISA, rp, d.stream);
 		for (int g = 0; g < dist.world; g++) pv.R[g] = static_cast<u32 *>(rp[g]);
+		pv_dev = d.alloc<PeerView>(1);
+		FBG_CUDA(cudaMemcpyAsync(pv_dev, &pv, sizeof pv, cudaMemcpyHostToDevice, d.stream));
+		FBG_CUDA(cudaStreamSynchronize(d.stream)); // pv lives on this function's stack
 		FBG_CUDA(cudaMemsetAsync(p.SA, 0, N * sizeof(u32), d.stream)); // every GPU writes the SA entries of the buckets it sorts; merged by max at the end
 	}
 	u32 mid_want = MID_MIN; // FBG_MID_MIN: test hook (64 ..: small inputs through the M path; above BSMALL: no M list)
@@ -1467,7 +1478,6 @@ void k1_suffix_array(Pipeline &p) {
 	if (peer && !by_dict) {
 		// the dictionary did not take this text (or a GPU's share outgrew its lists) -- on every GPU alike: key-range form
 		FBG_CUDA(cudaStreamSynchronize(d.stream));
-		dist.close_peers();
 		d.release(mk);
 		p.no_peer = true;
 		k1_suffix_array(p);
@@ -1637,7 +1647,7 @@ void k1_suffix_array(Pipeline &p) {
 			compact_lists(d, clsB, sv, newr, nB, CLS_NONE, TGT_S, nullptr, CLS_BIG, TGT_B, cnt + 2, ctot, p.ISA, hnext, N, nbits, o);
 		} else {
 			// the sorted S and M lists lie back to back in the sorter outputs: one pass moves both
-			const PeerView *pvp = peer ? &pv : nullptr;
+			const PeerView *pvp = peer && !getenv("FBG_PEER_LOCALREAD") ? pv_dev : nullptr; // (the variable: timing experiments only, wrong ranks)
 			compact_lists(d, clsS, lp_out, lr_out, nS + nM, CLS_SMALL, TGT_S, cnt, CLS_MID, TGT_M, cnt + 1, ctot, p.ISA, hnext, N, nbits, o, p.col, pvp);
 			compact_lists(d, clsB, sv, newr, nB, CLS_SMALL, TGT_S, cnt, CLS_BIG, TGT_B, cnt + 2, ctot, p.ISA, hnext, N, nbits, o, p.col, pvp);
 			if (mid_min <= BSMALL) compact_lists(d, clsB, sv, newr, nB, CLS_MID, TGT_M, cnt + 1, CLS_NONE, TGT_B, nullptr, ctot, p.ISA, hnext, N, nbits, o, p.col, pvp);
@@ -1666,15 +1676,12 @@ void k1_suffix_array(Pipeline &p) {
 		d.end((double) N * 8.0);
 	}
 	if (peer) {
-		// Ranks: every GPU holds the final ranks of its own columns (what its share of K2 reads); the other
-		// entries are older, hence smaller, values.  The full inverse is only assembled when somebody asks for it.
-		if (p.want_full_index) {
-			d.begin(K_COMM);
-			dist.allreduce_max_u32(p.ISA, N, d.stream);
-			d.end((double) N * 8.0);
-		} else p.isa_partial = true;
-		FBG_CUDA(cudaStreamSynchronize(d.stream)); // past the SA all-reduce: no GPU reads another's ranks any more
-		dist.close_peers();
+		// Ranks: every GPU holds the final ranks of its own columns, older (hence smaller) values elsewhere.  K2 also
+		// reads ranks beyond its own columns (the first character after a gap run, the '#' of an exhausted row), so
+		// the inverse is assembled once, here -- the only rank array that crosses the wire in a build.
+		d.begin(K_COMM);
+		dist.allreduce_max_u32(p.ISA, N, d.stream);
+		d.end((double) N * 8.0);
 	}
 	d.release(mk);
 }
