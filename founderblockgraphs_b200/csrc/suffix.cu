@@ -1138,10 +1138,31 @@ __global__ void k1_dict_place_kernel(const u32 *__restrict__ ov, const u32 *__re
 // what the sort-based round 0 leaves behind: ranks, SA entries of the suffixes alone in their
 // bucket, the S, M and B lists of the next round with R[p+h] looked up (through the table: no
 // rank has to be visible yet)
+// PEER: this GPU only needs the ranks of its own columns [x0, x1) (the last GPU also takes '#' and the sentinel) and the
+// members of the buckets it sorts; a position outside its columns matters only when its bucket spans GPUs
+template <bool PEER>
 __global__ void __launch_bounds__(256) k1_dict_emit_kernel(const u32 *__restrict__ slot_of, const u32 *__restrict__ ord_of, const uint4 *__restrict__ info, const u32 *__restrict__ rank_of_slot,
-                                                           u64 N, u64 hnext, int nbits, u32 mid_min, u32 *__restrict__ R, u32 *__restrict__ SA, CompactOut o) {
+                                                           u64 N, u64 hnext, int nbits, u32 mid_min, u32 *__restrict__ R, u32 *__restrict__ SA, CompactOut o,
+                                                           const u32 *__restrict__ col, const u8 *__restrict__ spans, u32 x0, u32 x1, int last) {
 	u64 p = (u64) blockIdx.x * blockDim.x + threadIdx.x;
 	if (p >= N) return;
+	if (PEER) {
+		const u32 c = col[p];
+		const bool own = c >= x0 && (c < x1 || last);
+		if (!own) {
+			if (!spans[slot_of[p]]) return;
+			// a member of a bucket every GPU sorts: listed below; its rank and SA entry are its owner's business
+			const uint4 v = __ldg(info + slot_of[p]);
+			if (v.z == 1 || v.y == U32_MAX) return;
+			const u64 pn = p + hnext;
+			const u32 r2 = pn < N ? __ldg(rank_of_slot + slot_of[pn]) : 0u;
+			const u32 q = v.y + ord_of[p];
+			if (v.z < mid_min) { o.Slp[q] = (u32) p; o.Slr[q] = v.x; o.Sr2[q] = r2; }
+			else if (v.z <= BSMALL) { o.Mlp[q] = (u32) p; o.Mlr[q] = v.x; o.Mr2[q] = r2; }
+			else { o.Bkey[q] = ((u64) v.x << nbits) | r2; o.Bval[q] = (u32) p; }
+			return;
+		}
+	}
 	const uint4 v = __ldg(info + slot_of[p]);
 	R[p] = v.x;
 	if (v.z == 1) { SA[v.x] = (u32) p; return; }
@@ -1266,9 +1287,9 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	const int cur = radix_sort<u64, true>(d, lb, nd, 0, key_bits0);
 	const u32 *lv = lb.v[cur];
 	const u32 gn = div_up(nd, 256);
-	u8 *mine = nullptr;
+	u8 *mine = nullptr, *spans = nullptr;
 	if (pv) {
-		u8 *spans = d.alloc<u8>(cap);
+		spans = d.alloc<u8>(cap);
 		mine = d.alloc<u8>(ndmax);
 		FBG_CUDA(cudaMemsetAsync(spans, 0, cap, d.stream));
 		d.begin(K_DOUBLING_AUX);
@@ -1334,7 +1355,11 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	}
 	d.begin(K_DOUBLING_AUX);
 	k1_dict_place_kernel<<<gn, 256, 0, d.stream>>>(ov, lv, nd, mid_min, zs, zm, info);
-	k1_dict_emit_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, p.SA, o);
+	if (pv) {
+		FBG_CUDA(cudaMemsetAsync(p.ISA, 0, N * sizeof(u32), d.stream)); // ranks outside this GPU's columns stay 0: the inverse is assembled by max at the end
+		k1_dict_emit_kernel<true><<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, p.SA, o,
+		                                                                 p.col, spans, pv->xb[pv->me], pv->xb[pv->me + 1], pv->me + 1 == pv->world ? 1 : 0);
+	} else k1_dict_emit_kernel<false><<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, p.SA, o, nullptr, nullptr, 0, 0, 0);
 	FBG_LAUNCH_CHECK();
 	d.end((double) N * (8.0 + 4.0 + 4.0 + 12.0) + (double) nd * 40.0);
 	d.note_launches(K_DOUBLING_AUX, 1);
