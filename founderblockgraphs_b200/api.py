@@ -55,8 +55,9 @@ EXPORTS = [
     "fbg_graph_free", "fbg_run", "fbg_run_device", "fbg_get_stream", "fbg_get_stats", "fbg_reset_stats", "fbg_get_f", "fbg_get_text",
     "fbg_get_sa", "fbg_get_isa", "fbg_get_lcp", "fbg_get_dp", "fbg_radix_sort_pairs", "fbg_radix_sort_bench", "fbg_write_xgfa",
     "fbg_check_index", "fbg_set_dp_chunking", "fbg_dist_unique_id", "fbg_dist_init", "fbg_dist_shutdown", "fbg_plan_key_ranges", "fbg_plan_columns",
-    "fbg_format_xgfa", "fbg_read_xgfa", "fbg_save_xgfa", "fbg_read_fasta", "fbg_msa_free",
+    "fbg_format_xgfa", "fbg_read_xgfa", "fbg_save_xgfa", "fbg_read_fasta", "fbg_msa_free", "fbg_radix_sort_pairs_noalloc",
 ]
+NOALLOC_MAX_PAIRS = 1 << 20  # FBG_NOALLOC_MAX_PAIRS
 
 _lib = None
 
@@ -110,6 +111,7 @@ def load_library():
     lib.fbg_get_dp.argtypes = [C.c_void_p, _u64p, _u64p, _u64p]
     lib.fbg_radix_sort_pairs.argtypes = [C.c_void_p, _u64p, _u32p, C.c_uint64, C.c_int, C.c_int]
     lib.fbg_radix_sort_bench.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double)]
+    lib.fbg_radix_sort_pairs_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int]
     lib.fbg_write_xgfa.argtypes = [C.c_char_p, C.c_void_p, C.c_uint64, C.c_uint64, _u64p, C.POINTER(FbgGraph), C.c_int, C.POINTER(C.c_char_p)]
     lib.fbg_format_xgfa.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(FbgGraph), _u64p]
     lib.fbg_read_xgfa.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p]
@@ -391,6 +393,11 @@ class Context:
         vals = np.ascontiguousarray(vals, np.uint32).copy()
         self._check(self.lib.fbg_radix_sort_pairs(self.h, keys.ctypes.data_as(_u64p), vals.ctypes.data_as(_u32p), len(keys), lo_bit, hi_bit))
         return keys, vals
+
+    def radix_sort_pairs_noalloc(self, d_keys_in: int, d_vals_in: int, d_keys_out: int, d_vals_out: int, count: int, lo_bit=0, hi_bit=64):
+        """The radix passes on DEVICE buffers (addresses) without any allocation: scratch is a fixed array inside the
+        library, at most NOALLOC_MAX_PAIRS pairs.  Enqueued on the context's stream; the caller synchronises it."""
+        self._check(self.lib.fbg_radix_sort_pairs_noalloc(self.h, d_keys_in, d_vals_in, d_keys_out, d_vals_out, count, lo_bit, hi_bit))
 
     def radix_sort_bench(self, count: int, lo_bit=0, hi_bit=64, reps=3) -> float:
         ms = C.c_double()

@@ -579,4 +579,106 @@ int fbg_radix_sort_bench(fbg_ctx *ctx, uint64_t count, int lo_bit, int hi_bit, i
 	return FBG_OK;
 }
 
+
 } // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// fbg_radix_sort_pairs_noalloc: the radix passes for callers that must not allocate (code under CUDA
+// graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the
+// reference.  The scratch the passes need -- one
+// ping-pong (key, value) buffer, the per-tile digit count matrix, the digit totals -- lives in a
+// file-scope __device__ array of fixed size, so every GPU that loads the library holds
+// FBG_NOALLOC_SCRATCH_BYTES (about 12.3 MB) until the process exits.
+//
+// In HOST code the array's name is only a host-side stand-in for the symbol, not a device address:
+// its address is taken once per device, with that device current, through cudaGetSymbolAddress
+// (noalloc_scratch_for below) and that pointer is what the kernels get.
+namespace {
+
+constexpr u64 NA_MAX_PAIRS = FBG_NOALLOC_MAX_PAIRS;
+constexpr u64 NA_MAX_TILES = (NA_MAX_PAIRS + RS_TILE - 1) / RS_TILE;
+constexpr u64 NA_OFF_KEYS = 0;                                            // u64[NA_MAX_PAIRS]
+constexpr u64 NA_OFF_VALS = NA_OFF_KEYS + NA_MAX_PAIRS * sizeof(u64);      // u32[NA_MAX_PAIRS]
+constexpr u64 NA_OFF_COUNTS = NA_OFF_VALS + NA_MAX_PAIRS * sizeof(u32);    // u32[RS_BINS][NA_MAX_TILES]
+constexpr u64 NA_OFF_TOTALS = NA_OFF_COUNTS + (u64) RS_BINS * NA_MAX_TILES * sizeof(u32); // u64[RS_BINS]
+constexpr u64 NA_BYTES = NA_OFF_TOTALS + (u64) RS_BINS * sizeof(u64);
+static_assert(NA_BYTES == FBG_NOALLOC_SCRATCH_BYTES, "include/fbg_cuda.h states the size of the scratch array");
+static_assert(NA_OFF_VALS % 256 == 0 && NA_OFF_COUNTS % 256 == 0 && NA_OFF_TOTALS % 256 == 0, "scratch sections stay 256-byte aligned");
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NA_BYTES];
+
+constexpr int NA_MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+unsigned char *g_noalloc_ptr[NA_MAX_DEVICES] = {};
+
+// Device address of the scratch array on `device` (which must be current); set-up work of the
+// first call on a device: the symbol's address and the shared-memory opt-in of the scatter kernel.
+unsigned char *noalloc_scratch_for(int device) {
+	if (device < 0 || device >= NA_MAX_DEVICES) throw cuda_error("device index beyond the no-allocation entry point's table");
+	std::lock_guard<std::mutex> lk(g_noalloc_mu);
+	if (!g_noalloc_ptr[device]) {
+		void *ptr = nullptr;
+		FBG_CUDA(cudaGetSymbolAddress(&ptr, g_noalloc_scratch));
+		if (!ptr) throw cuda_error("cudaGetSymbolAddress returned a null address for the scratch array");
+		FBG_CUDA(cudaFuncSetAttribute(rs_scatter_kernel<u64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sizeof(RsSmem<u64>)));
+		g_noalloc_ptr[device] = static_cast<unsigned char *>(ptr);
+	}
+	return g_noalloc_ptr[device];
+}
+
+} // namespace
+
+extern "C" int fbg_radix_sort_pairs_noalloc(fbg_ctx *ctx, const uint64_t *d_keys_in, const uint32_t *d_vals_in, uint64_t *d_keys_out, uint32_t *d_vals_out,
+                                            uint64_t count, int lo_bit, int hi_bit) {
+	if (!ctx) return FBG_ERR_ARG;
+	if (lo_bit < 0 || hi_bit > 64 || hi_bit < lo_bit) { ctx->err = "bit range must satisfy 0 <= lo_bit <= hi_bit <= 64"; return FBG_ERR_ARG; }
+	if (count > NA_MAX_PAIRS) {
+		ctx->err = "fbg_radix_sort_pairs_noalloc sorts at most " + std::to_string(NA_MAX_PAIRS) + " pairs (FBG_NOALLOC_MAX_PAIRS; its scratch is a fixed device array), got " +
+		           std::to_string(count) + ": use fbg_radix_sort_pairs";
+		return FBG_ERR_UNSUPPORTED;
+	}
+	if (count == 0) return FBG_OK;
+	if (!d_keys_in || !d_vals_in || !d_keys_out || !d_vals_out) { ctx->err = "null device buffer"; return FBG_ERR_ARG; }
+	if ((const void *) d_keys_in == (const void *) d_keys_out || (const void *) d_vals_in == (const void *) d_vals_out) { ctx->err = "input and output buffers must be distinct"; return FBG_ERR_ARG; }
+	FBG_TRY(ctx)
+	Dev &d = ctx->p.dev;
+	FBG_CUDA(cudaSetDevice(d.device));
+	unsigned char *sc = noalloc_scratch_for(d.device);
+	u64 *tkeys = reinterpret_cast<u64 *>(sc + NA_OFF_KEYS);
+	u32 *tvals = reinterpret_cast<u32 *>(sc + NA_OFF_VALS);
+	u32 *counts = reinterpret_cast<u32 *>(sc + NA_OFF_COUNTS);
+	u64 *totals = reinterpret_cast<u64 *>(sc + NA_OFF_TOTALS);
+	const int total = hi_bit - lo_bit;
+	const int passes = (total + 7) / 8;
+	if (passes == 0) { // nothing to sort by: the stable order is the input order
+		FBG_CUDA(cudaMemcpyAsync(d_keys_out, d_keys_in, count * sizeof(u64), cudaMemcpyDeviceToDevice, d.stream));
+		FBG_CUDA(cudaMemcpyAsync(d_vals_out, d_vals_in, count * sizeof(u32), cudaMemcpyDeviceToDevice, d.stream));
+		return FBG_OK;
+	}
+	const u32 ntiles = div_up(count, RS_TILE);
+	// The array keeps what the last call left.  Every count and total a pass reads is written by that
+	// pass first (rs_hist_kernel stores all RS_BINS x ntiles entries, rs_binscan_kernel all totals);
+	// they are cleared all the same, so that no call can ever depend on an earlier one.
+	FBG_CUDA(cudaMemsetAsync(counts, 0, (u64) RS_BINS * ntiles * sizeof(u32), d.stream));
+	FBG_CUDA(cudaMemsetAsync(totals, 0, (u64) RS_BINS * sizeof(u64), d.stream));
+	// ping-pong between the scratch buffer and the caller's output so that the last pass lands in the output;
+	// the input is only read
+	const u64 *kin = d_keys_in;
+	const u32 *vin = d_vals_in;
+	int bit = lo_bit;
+	for (int p = 0; p < passes; p++) {
+		const int bits = (hi_bit - bit + (passes - p) - 1) / (passes - p); // even split, like radix_sort
+		const u32 mask = (1u << bits) - 1;
+		const bool to_out = ((passes - 1 - p) & 1) == 0;
+		u64 *kout = to_out ? d_keys_out : tkeys;
+		u32 *vout = to_out ? d_vals_out : tvals;
+		rs_hist_kernel<u64><<<ntiles, RS_HTHREADS, 0, d.stream>>>(kin, count, bit, mask, ntiles, counts);
+		rs_binscan_kernel<<<RS_BINS, 1024, 0, d.stream>>>(counts, ntiles, totals);
+		rs_scatter_kernel<u64, true><<<ntiles, RS_THREADS, sizeof(RsSmem<u64>), d.stream>>>(kin, vin, kout, vout, count, bit, mask, ntiles, counts, totals);
+		FBG_LAUNCH_CHECK();
+		kin = kout; vin = vout;
+		bit += bits;
+	}
+	FBG_CATCH(ctx)
+	return FBG_OK;
+}

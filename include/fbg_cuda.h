@@ -185,6 +185,25 @@ int fbg_radix_sort_pairs(fbg_ctx *ctx, uint64_t *keys, uint32_t *vals, uint64_t 
  * sorts `count` pseudo-random 64-bit keys generated on the device; returns elapsed ms. */
 int fbg_radix_sort_bench(fbg_ctx *ctx, uint64_t count, int lo_bit, int hi_bit, int reps, double *ms_per_sort);
 
+/* The same radix passes for callers that cannot allocate: code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc.  This entry point has NO counterpart in the
+ * reference.  It calls no cudaMalloc / cudaFree
+ * and no allocating library routine: its scratch (one ping-pong buffer of pairs, the digit count
+ * matrix, the digit totals) is a fixed __device__ array inside the library, FBG_NOALLOC_SCRATCH_BYTES
+ * held by every GPU that loads the library until the process exits.
+ *   - DEVICE buffers on the context's device, inputs only read, outputs distinct from the inputs;
+ *     count <= FBG_NOALLOC_MAX_PAIRS, else FBG_ERR_UNSUPPORTED (fbg_last_error names the limit).
+ *   - Stable LSD sort on bits [lo_bit, hi_bit), bit-identical to fbg_radix_sort_pairs.
+ *   - Work is ENQUEUED on the context's stream (fbg_get_stream) and the call returns without
+ *     synchronising: the outputs are ready when that stream has reached this point.
+ *   - Every call on a GPU -- whatever the context or stream -- shares the one array, which keeps the
+ *     last call's contents (a call clears what it needs): calls that overlap on the GPU race.
+ *     Calls on one context are ordered by its stream; across contexts the caller orders them. */
+#define FBG_NOALLOC_MAX_PAIRS (1ull << 20)
+#define FBG_NOALLOC_SCRATCH_BYTES 12847104ull  /* 2^20 x (8 + 4) B pairs + 256 x 256 x 4 B counts + 256 x 8 B totals */
+int fbg_radix_sort_pairs_noalloc(fbg_ctx *ctx, const uint64_t *d_keys_in, const uint32_t *d_vals_in, uint64_t *d_keys_out, uint32_t *d_vals_out,
+                                 uint64_t count, int lo_bit, int hi_bit);
+
 /* Host-side xGFA formatting, byte-identical to output_efg (fbg.cpp:1185-1301).
  * msa = the same filtered row-major rows; ids = m header strings (used when output_paths). */
 int fbg_write_xgfa(const char *path, const uint8_t *rows_rowmajor, uint64_t m, uint64_t n,
