@@ -55,7 +55,7 @@ EXPORTS = [
     "fbg_graph_free", "fbg_run", "fbg_run_device", "fbg_get_stream", "fbg_get_stats", "fbg_reset_stats", "fbg_get_f", "fbg_get_text",
     "fbg_get_sa", "fbg_get_isa", "fbg_get_lcp", "fbg_get_dp", "fbg_radix_sort_pairs", "fbg_radix_sort_bench", "fbg_write_xgfa",
     "fbg_check_index", "fbg_set_dp_chunking", "fbg_dist_unique_id", "fbg_dist_init", "fbg_dist_shutdown", "fbg_plan_key_ranges", "fbg_plan_columns",
-    "fbg_format_xgfa", "fbg_read_xgfa", "fbg_save_xgfa", "fbg_read_fasta", "fbg_msa_free", "fbg_radix_sort_pairs_noalloc",
+    "fbg_format_xgfa", "fbg_read_xgfa", "fbg_save_xgfa", "fbg_read_fasta", "fbg_msa_free", "fbg_radix_sort_pairs_noalloc", "fbg_device_count",
 ]
 NOALLOC_MAX_PAIRS = 1 << 20  # FBG_NOALLOC_MAX_PAIRS
 

@@ -365,6 +365,12 @@ int fbg_run_device(fbg_ctx *ctx, const void *rows, uint64_t m, uint64_t n, int w
 	return run_common(ctx, rows, m, n, true, want_paths, n_blocks, score, out);
 }
 
+int fbg_device_count(void) {
+	int count = 0;
+	if (cudaGetDeviceCount(&count) != cudaSuccess) { cudaGetLastError(); return 0; }
+	return count;
+}
+
 int fbg_dist_unique_id(uint8_t *out128) {
 	if (!out128) return FBG_ERR_ARG;
 	static NcclApi api;

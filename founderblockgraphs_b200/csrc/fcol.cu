@@ -32,6 +32,8 @@ struct FcolArgs {
 	u32 groups;    // column groups per CTA
 	u64 x0, x1;    // column range [x0, x1)
 	int tricks_off, has_ignore;
+	int only_marked; // sorting kernel after the cluster kernel: only the columns it left marked
+	u32 *dbg;        // FBG_DEBUG: [0] columns left marked, by reason: [1] no cluster, [2] too many rows outside, [3] a row next to the window
 };
 
 // One column group = tpg threads over mpad = tpg * E sorted slots (E <= 8 consecutive slots
@@ -62,19 +64,53 @@ template <bool UP> __device__ __forceinline__ void warp_seg_min(u32 &v, bool &fl
 	}
 }
 
-// dynamic smem per group: key u64[mpad] | A u32[mpad] (PLCP of row i) | RKS u32[mpad] (rank of row i)
-__global__ void __launch_bounds__(1024) k2_fcol_kernel(FcolArgs a) {
+// fi of row i at column x, given the two minima l = min LCP[a..k], r = min LCP[k+1..b+1] of its run (fbg.cpp:1656-1670)
+__device__ __forceinline__ u32 fcol_fi(const FcolArgs &a, u32 i, u32 l, u32 r, u32 rk, u64 x, u64 t, u32 dx) {
+	u64 g = (u64) (l > r ? l : r) + 1;                         // fbg.cpp:1656
+	u64 gg = (u64) rk + g;                                      // fbg.cpp:1657
+	u32 fi;
+	if (gg > a.rowlen[i]) fi = a.tricks_off ? (u32) a.n : a.lastcol[i]; // 1659-1665
+	else fi = a.col[(u64) a.start[i] + gg - 1];                 // 1666
+	if (a.has_ignore) {                                         // 1669-1670
+		u32 ig = a.IG[t * a.m + i] >> dx;
+		u32 ni = ig ? (u32) x + (__ffs(ig) - 1) : a.NIA[t * a.m + i];
+		if (ni < fi) fi = ni;
+	}
+	return fi;
+}
+
+constexpr u32 FC_OCAP = 512;          // cluster path: rows of a column whose rank lies outside the column's cluster
+constexpr u32 FC_MARK = 0xFFFFFFFFu;  // f[x] of a column the cluster path could not take (redone by the sorting kernel)
+
+// CLUSTER = false -- dynamic smem per group: key u64[mpad] | A u32[mpad] (PLCP of row i) | RKS u32[mpad] (rank of row i);
+//   the active rows are sorted by rank on the swizzled bitonic network.
+// CLUSTER = true (one group per CTA, mpad / 8 threads) -- A u32[mpad] | RKS u32[mpad] | TAB u16[mpad] | OKEY u64[FC_OCAP].
+//   The rows of an MSA are near copies of each other, so the suffixes that start in one column lie next to
+//   each other in the suffix array: the ranks of a column's rows form one cluster about m wide (holes where a
+//   suffix of another column sorts in between), plus a few rows elsewhere -- rows inside a gap run (their next
+//   character lies in a later column, hence in that column's cluster) and exhausted rows (their '#').  Instead of
+//   sorting, every row is PLACED at TAB[rank - base], base = the smallest rank near the median of three
+//   probe rows: adjacent slots are consecutive ranks, an empty slot is a foreign suffix, i.e. a run break
+//   (fbg.cpp:1633-1641), and the run minima are the same register / shuffle scans over the slots.  Rows outside
+//   [base, base + mpad) are few: they go through a 512-key network and walk their (short) runs one thread
+//   each.  A column that does not fit the pattern -- no cluster, more than FC_OCAP rows outside, a row
+//   right next to the window (its run would cross the edge) -- gets f[x] = FC_MARK and is redone by the
+//   sorting form of this kernel (only_marked).
+template <bool CLUSTER> __global__ void __launch_bounds__(1024) k2_fcol_kernel(FcolArgs a) {
 	extern __shared__ __align__(16) unsigned char k2_raw[];
-	const u32 mpad = a.mpad, tpg = a.tpg, E = a.E;
+	const u32 mpad = a.mpad, tpg = a.tpg, E = CLUSTER ? 8u : a.E;
 	const u32 grp = threadIdx.x / tpg, tg = threadIdx.x % tpg;
 	const u64 per_group = (u64) mpad * 16;
-	unsigned char *basep = k2_raw + (u64) grp * per_group;
-	u64 *key = reinterpret_cast<u64 *>(basep);
-	u32 *A = reinterpret_cast<u32 *>(basep + (u64) mpad * 8);
+	unsigned char *basep = k2_raw + (CLUSTER ? 0 : (u64) grp * per_group);
+	u64 *key = reinterpret_cast<u64 *>(basep);                                             // !CLUSTER
+	u32 *A = reinterpret_cast<u32 *>(basep + (CLUSTER ? 0 : (u64) mpad * 8));
 	u32 *RKS = A + mpad;
+	unsigned short *TAB = reinterpret_cast<unsigned short *>(RKS + mpad);                   // CLUSTER
+	u64 *OKEY = reinterpret_cast<u64 *>(basep + (u64) mpad * 10);                           // CLUSTER
 	__shared__ u32 red[32];
 	__shared__ u32 wl[32], wr[32];      // per warp: segmented aggregate (value), towards the right / the left
 	__shared__ u32 wfl[32], wfr[32];    // per warp: a run start / a run end inside the warp
+	__shared__ u32 s_probe[3], s_no, s_fb;
 	const u64 m = a.m;
 	const u32 wid = threadIdx.x >> 5, lane = lane_id();
 	const u32 w_first = (grp * tpg) >> 5, w_last = w_first + (tpg >> 5) - 1;
@@ -82,53 +118,165 @@ __global__ void __launch_bounds__(1024) k2_fcol_kernel(FcolArgs a) {
 	for (u64 xb = a.x0 + (u64) blockIdx.x * a.groups; xb < a.x1; xb += (u64) gridDim.x * a.groups) {
 		const u64 x = xb + grp;
 		const bool live = x < a.x1;
+		if (a.only_marked && a.f[x] != FC_MARK) continue; // (one group per CTA: uniform)
 		const u64 t = x >> 5;
 		const u32 dx = (u32) (x & 31), below = (1u << dx) - 1u;
-		// 1. gather
-		for (u32 i = tg; i < mpad; i += tpg) {
-			u64 kk = KEY_INVALID;
-			if (live && i < m) {
-				u32 rk = a.RK[t * m + i] + __popc(a.NG[t * m + i] & below);
-				if (a.tricks_off || rk > 0) {
-					u64 p = (u64) a.start[i] + rk;
-					kk = ((u64) a.ISA[p] << 24) | i;
-					A[i] = a.PLCP[p];
-					RKS[i] = rk;
+		u32 base = 0, n_out = 0;
+		if (!CLUSTER) {
+			// 1. gather
+			for (u32 i = tg; i < mpad; i += tpg) {
+				u64 kk = KEY_INVALID;
+				if (live && i < m) {
+					u32 rk = a.RK[t * m + i] + __popc(a.NG[t * m + i] & below);
+					if (a.tricks_off || rk > 0) {
+						u64 p = (u64) a.start[i] + rk;
+						kk = ((u64) a.ISA[p] << 24) | i;
+						A[i] = a.PLCP[p];
+						RKS[i] = rk;
+					}
+				}
+				key[ts_sw(i)] = kk;
+			}
+			__syncthreads();
+			// 2. bitonic sort ascending by (rank, row)
+			group_tile_sort(key, mpad, tg, tpg);
+		} else {
+			// 1c. gather: this thread's rows are tg, tg + tpg, ... (eight of them); ranks stay in registers
+			u32 myr[8];
+			if (tg < 3) s_probe[tg] = U32_MAX;
+			if (tg == 0) { s_no = 0; s_fb = 0; }
+			reinterpret_cast<uint4 *>(TAB)[tg] = make_uint4(0, 0, 0, 0); // eight slots per thread
+			__syncthreads();
+			const u32 pr0 = (u32) (m / 4), pr1 = (u32) (m / 2), pr2 = (u32) (3 * m / 4);
+			// (three batches of loads -- tables, text offsets, then ranks and LCPs -- so that a thread waits for memory
+			//  three times per column, not three times per row)
+			u32 rkv[8], av[8];
+			u64 pv[8];
+#pragma unroll
+			for (u32 c = 0; c < 8; c++) {
+				const u32 i = tg + c * tpg;
+				rkv[c] = 0; pv[c] = 0;
+				if (live && i < m) { rkv[c] = __ldg(a.RK + t * m + i) + __popc(__ldg(a.NG + t * m + i) & below); pv[c] = __ldg(a.start + i); }
+			}
+#pragma unroll
+			for (u32 c = 0; c < 8; c++) {
+				const u32 i = tg + c * tpg;
+				myr[c] = U32_MAX; av[c] = 0;
+				if (live && i < m && (a.tricks_off || rkv[c] > 0)) { pv[c] += rkv[c]; myr[c] = __ldg(a.ISA + pv[c]); av[c] = __ldg(a.PLCP + pv[c]); }
+			}
+#pragma unroll
+			for (u32 c = 0; c < 8; c++) {
+				const u32 i = tg + c * tpg;
+				if (i < m) {
+					if (myr[c] != U32_MAX) { A[i] = av[c]; RKS[i] = rkv[c]; }
+					if (i == pr0) s_probe[0] = myr[c];
+					if (i == pr1) s_probe[1] = myr[c];
+					if (i == pr2) s_probe[2] = myr[c];
 				}
 			}
-			key[ts_sw(i)] = kk;
+			__syncthreads();
+			// 2c. the cluster lies around the median probe: k rows in the mpad ranks below it (the cluster itself is
+			//     contiguous up to a few foreign suffixes; stray rows -- an SNP a few columns on puts a row some
+			//     thousand ranks away -- only add a few to the count) => window start = pivot - k - slack
+			u32 pa = s_probe[0], pb = s_probe[1], pc = s_probe[2];
+			const u32 lo3 = pa < pb ? pa : pb, hi3 = pa < pb ? pb : pa;
+			const u32 piv = pc < lo3 ? lo3 : (pc > hi3 ? hi3 : pc); // median (inactive rows = U32_MAX sort last)
+			u32 kb = 0;
+#pragma unroll
+			for (u32 c = 0; c < 8; c++) {
+				const u32 r = myr[c];
+				if (r < piv && piv - r <= mpad) kb++;
+			}
+			kb = warp_reduce_sum(kb);
+			if (lane == 0) red[wid] = kb;
+			__syncthreads();
+			kb = 0;
+			for (u32 w = w_first; w <= w_last; w++) kb += red[w];
+			const u32 slack = (mpad - (u32) m) / 4;
+			base = piv == U32_MAX ? U32_MAX : (piv > kb + slack ? piv - kb - slack : 0u);
+			// 3c. place the rows of the window, list the others
+#pragma unroll
+			for (u32 c = 0; c < 8; c++) {
+				const u32 r = myr[c];
+				if (r != U32_MAX) {
+					const u32 i = tg + c * tpg;
+					const u32 dlt = r - base; // (wraps for r < base)
+					if (dlt < mpad) TAB[dlt] = (unsigned short) (i + 1);
+					else {
+						const u32 q = atomicAdd(&s_no, 1u);
+						if (q < FC_OCAP) OKEY[ts_sw(q)] = ((u64) r << 24) | i;
+						if (r + 1 == base || dlt == mpad) s_fb = 1u; // next to the window: its run would cross the edge
+					}
+				}
+			}
+			__syncthreads();
+			n_out = s_no;
+			const bool bad = piv == U32_MAX || base == U32_MAX || n_out > FC_OCAP || s_fb != 0;
+			__syncthreads(); // (s_no / s_fb / red are rewritten by the next column)
+			if (bad) {
+				if (tg == 0 && live) {
+					a.f[x] = FC_MARK;
+					if (a.dbg) { atomicAdd(a.dbg, 1u); if (piv == U32_MAX || base == U32_MAX) atomicAdd(a.dbg + 1, 1u); else if (n_out > FC_OCAP) atomicAdd(a.dbg + 2, 1u); else atomicAdd(a.dbg + 3, 1u); }
+				}
+				continue;
+			}
 		}
-		__syncthreads();
-		// 2. bitonic sort ascending by (rank, row)
-		group_tile_sort(key, mpad, tg, tpg);
 		// 3. the thread's E consecutive sorted slots: run flags, LCP[k] and LCP[k+1]
 		const u32 j0 = tg * E;
 		u32 row[8], lv[8], rv[8];
 		u32 smask = 0, emask = 0, vmask = 0;
-		u64 kprev = j0 ? key[ts_sw(j0 - 1)] : KEY_INVALID;
-		u64 kcur = key[ts_sw(j0)];
+		if (!CLUSTER) {
+			u64 kprev = j0 ? key[ts_sw(j0 - 1)] : KEY_INVALID;
+			u64 kcur = key[ts_sw(j0)];
 #pragma unroll
-		for (u32 c = 0; c < 8; c++) {
-			if (c < E) {
-				const u32 j = j0 + c;
-				const u64 kn = j + 1 < mpad ? key[ts_sw(j + 1)] : KEY_INVALID;
+			for (u32 c = 0; c < 8; c++) {
+				if (c < E) {
+					const u32 j = j0 + c;
+					const u64 kn = j + 1 < mpad ? key[ts_sw(j + 1)] : KEY_INVALID;
+					lv[c] = U32_MAX; rv[c] = U32_MAX; row[c] = 0;
+					bool s = true, e = true;
+					if (kcur != KEY_INVALID) {
+						const u32 i = (u32) (kcur & 0xFFFFFFu);
+						const u64 r = kcur >> 24;
+						row[c] = i;
+						vmask |= 1u << c;
+						lv[c] = A[i];
+						s = (j == 0) || ((kprev >> 24) + 1 != r);
+						e = (kn == KEY_INVALID) || ((kn >> 24) != r + 1);
+						// LCP[r+1]: inside a run it is the next element's own LCP value; only a run's
+						// last element has to look the foreign neighbour up (SA, then PLCP)
+						if (!e) rv[c] = A[(u32) (kn & 0xFFFFFFu)];
+						else rv[c] = r + 1 < a.N ? a.PLCP[a.SA[r + 1]] : 0u;
+					}
+					smask |= (u32) s << c; emask |= (u32) e << c;
+					kprev = kcur; kcur = kn;
+				}
+			}
+		} else {
+			// slot j holds the row whose rank is base + j (0 = none)
+			const uint4 tv = reinterpret_cast<const uint4 *>(TAB)[tg];
+			const u32 w4[4] = {tv.x, tv.y, tv.z, tv.w};
+			u32 prev = j0 ? TAB[j0 - 1] : 0u;
+			const u32 nxt8 = j0 + 8 < mpad ? TAB[j0 + 8] : 0u;
+#pragma unroll
+			for (u32 c = 0; c < 8; c++) {
+				const u32 cur = (w4[c >> 1] >> (16 * (c & 1))) & 0xFFFFu;
+				const u32 nx = c < 7 ? (w4[(c + 1) >> 1] >> (16 * ((c + 1) & 1))) & 0xFFFFu : nxt8;
 				lv[c] = U32_MAX; rv[c] = U32_MAX; row[c] = 0;
 				bool s = true, e = true;
-				if (kcur != KEY_INVALID) {
-					const u32 i = (u32) (kcur & 0xFFFFFFu);
-					const u64 r = kcur >> 24;
+				if (cur) {
+					const u32 i = cur - 1;
+					const u64 r = (u64) base + j0 + c;
 					row[c] = i;
 					vmask |= 1u << c;
 					lv[c] = A[i];
-					s = (j == 0) || ((kprev >> 24) + 1 != r);
-					e = (kn == KEY_INVALID) || ((kn >> 24) != r + 1);
-					// LCP[r+1]: inside a run it is the next element's own LCP value; only a run's
-					// last element has to look the foreign neighbour up (SA, then PLCP)
-					if (!e) rv[c] = A[(u32) (kn & 0xFFFFFFu)];
+					s = prev == 0;
+					e = nx == 0;
+					if (!e) rv[c] = A[nx - 1];
 					else rv[c] = r + 1 < a.N ? a.PLCP[a.SA[r + 1]] : 0u;
 				}
 				smask |= (u32) s << c; emask |= (u32) e << c;
-				kprev = kcur; kcur = kn;
+				prev = cur;
 			}
 		}
 		// 4. segmented prefix-min of lv (run starts) and suffix-min of rv (run ends):
@@ -163,8 +311,11 @@ __global__ void __launch_bounds__(1024) k2_fcol_kernel(FcolArgs a) {
 #pragma unroll
 		for (int c = 7; c >= 0; c--)
 			if ((u32) c < E) { if ((emask >> c) & 1u) closed_r |= (2u << c) - 1u; }
+		u32 gl[8], rl[8], fiv[8];
+		u64 cp[8];
 #pragma unroll
 		for (u32 c = 0; c < 8; c++) {
+			gl[c] = 0; rl[c] = 0; fiv[c] = 0; cp[c] = 0;
 			if (c < E) {
 				if ((smask >> c) & 1u) openl = false;
 				if ((vmask >> c) & 1u) {
@@ -172,18 +323,60 @@ __global__ void __launch_bounds__(1024) k2_fcol_kernel(FcolArgs a) {
 					if (openl) l = cl < l ? cl : l;
 					if (!((closed_r >> c) & 1u)) r = cr < r ? cr : r;
 					const u32 i = row[c];
-					u64 g = (u64) (l > r ? l : r) + 1;                         // fbg.cpp:1656
-					u64 gg = (u64) RKS[i] + g;                                  // fbg.cpp:1657
-					u32 fi;
-					if (gg > a.rowlen[i]) fi = a.tricks_off ? (u32) a.n : a.lastcol[i]; // 1659-1665
-					else fi = a.col[(u64) a.start[i] + gg - 1];                 // 1666
-					if (a.has_ignore) {                                         // 1669-1670
-						u32 ig = a.IG[t * m + i] >> dx;
-						u32 ni = ig ? (u32) x + (__ffs(ig) - 1) : a.NIA[t * m + i];
-						if (ni < fi) fi = ni;
-					}
-					fmax = fi > fmax ? fi : fmax;
+					gl[c] = (l > r ? l : r) + 1;                                  // g, fbg.cpp:1656
+					rl[c] = __ldg(a.rowlen + i);
+					cp[c] = __ldg(a.start + i);
 				}
+			}
+		}
+#pragma unroll
+		for (u32 c = 0; c < 8; c++) {
+			if (c < E && ((vmask >> c) & 1u)) {
+				const u32 i = row[c];
+				const u64 gg = (u64) RKS[i] + gl[c];                             // fbg.cpp:1657
+				if (gg > rl[c]) fiv[c] = a.tricks_off ? (u32) a.n : __ldg(a.lastcol + i); // 1659-1665
+				else fiv[c] = __ldg(a.col + cp[c] + gg - 1);                     // 1666
+			}
+		}
+#pragma unroll
+		for (u32 c = 0; c < 8; c++) {
+			if (c < E && ((vmask >> c) & 1u)) {
+				u32 fi = fiv[c];
+				if (a.has_ignore) {                                             // 1669-1670
+					const u32 i = row[c];
+					u32 ig = a.IG[t * m + i] >> dx;
+					u32 ni = ig ? (u32) x + (__ffs(ig) - 1) : a.NIA[t * m + i];
+					if (ni < fi) fi = ni;
+				}
+				fmax = fi > fmax ? fi : fmax;
+			}
+		}
+		// 5c. the rows outside the window: sorted by rank on a small network, one thread per row walks its run
+		//     (a few neighbours at most: rows that left the same gap run, the '#' of exhausted rows)
+		if (CLUSTER && n_out) {
+			u32 onet = 32;
+			while (onet < n_out) onet <<= 1;
+			for (u32 q = n_out + tg; q < onet; q += tpg) OKEY[ts_sw(q)] = KEY_INVALID;
+			__syncthreads();
+			group_tile_sort(OKEY, onet, tg, tpg);
+			for (u32 o = tg; o < n_out; o += tpg) { // (a group of 256 threads may meet 512 rows)
+				const u64 k = OKEY[ts_sw(o)];
+				const u32 i = (u32) (k & 0xFFFFFFu);
+				u32 l = A[i], r = U32_MAX;
+				for (u32 q = o; q > 0; q--) {
+					const u64 kp = OKEY[ts_sw(q - 1)], kq = OKEY[ts_sw(q)];
+					if ((kp >> 24) + 1 != (kq >> 24)) break;
+					const u32 v = A[(u32) (kp & 0xFFFFFFu)];
+					l = v < l ? v : l;
+				}
+				for (u32 q = o;; q++) {
+					const u64 rq = OKEY[ts_sw(q)] >> 24;
+					const u64 kn = q + 1 < n_out ? OKEY[ts_sw(q + 1)] : KEY_INVALID;
+					if (kn != KEY_INVALID && (kn >> 24) == rq + 1) { const u32 v = A[(u32) (kn & 0xFFFFFFu)]; r = v < r ? v : r; }
+					else { const u32 v = rq + 1 < a.N ? a.PLCP[a.SA[rq + 1]] : 0u; r = v < r ? v : r; break; }
+				}
+				const u32 fi = fcol_fi(a, i, l, r, RKS[i], x, t, dx);
+				fmax = fi > fmax ? fi : fmax;
 			}
 		}
 		// group reduction (groups are warp multiples)
@@ -290,14 +483,35 @@ void k2_compute_f(Pipeline &p) {
 	}
 	a.tricks_off = p.opt.disable_tricks ? 1 : 0;
 	a.has_ignore = p.opt.n_ignore > 0 ? 1 : 0;
+	a.only_marked = 0;
+	a.dbg = nullptr;
+	const bool debug = getenv("FBG_DEBUG") != nullptr;
+	if (debug) { a.dbg = reinterpret_cast<u32 *>(p.scalars + 40); FBG_CUDA(cudaMemsetAsync(a.dbg, 0, 4 * sizeof(u32), d.stream)); }
 	size_t smem = (size_t) a.groups * mpad * 16;
-	FBG_CUDA(cudaFuncSetAttribute(k2_fcol_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+	FBG_CUDA(cudaFuncSetAttribute(k2_fcol_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
 	u64 col_groups = (a.x1 - a.x0 + a.groups - 1) / a.groups;
 	if (col_groups == 0) col_groups = 1;
 	u64 max_grid = (u64) NUM_SMS * 8;
 	u32 grid = (u32) (col_groups < max_grid ? col_groups : max_grid);
 	d.begin(K_FCOL);
-	k2_fcol_kernel<<<grid, threads, smem, d.stream>>>(a);
+	// many rows: placement by rank instead of a sort (cluster form of the kernel), then the sorting form for the
+	// columns that did not fit; the window needs some room beyond the m ranks of the cluster
+	const bool cluster = mpad >= 2048 && gc.groups == 1 && gc.E == 8 && p.m * 10 <= (u64) mpad * 9 && !getenv("FBG_FCOL_SORT");
+	if (cluster) {
+		const size_t smem_c = (size_t) mpad * 10 + (size_t) FC_OCAP * 8;
+		FBG_CUDA(cudaFuncSetAttribute(k2_fcol_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem_c));
+		k2_fcol_kernel<true><<<grid, threads, smem_c, d.stream>>>(a);
+		a.only_marked = 1;
+		d.note_launches(K_FCOL, 1);
+		if (debug) {
+			u32 h[4];
+			FBG_CUDA(cudaMemcpyAsync(h, a.dbg, sizeof h, cudaMemcpyDeviceToHost, d.stream));
+			FBG_CUDA(cudaStreamSynchronize(d.stream));
+			fprintf(stderr, "[fbg] K2 cluster form: %u of %llu columns left to the sorting form (no cluster %u, > %u rows outside %u, row next to the window %u)\n",
+			        h[0], (unsigned long long) (a.x1 - a.x0), h[1], FC_OCAP, h[2], h[3]);
+		}
+	}
+	k2_fcol_kernel<false><<<grid, threads, smem, d.stream>>>(a);
 	FBG_LAUNCH_CHECK();
 	d.end((double) p.m * (double) (a.x1 - a.x0) * 12.0);
 	if (sharded) {

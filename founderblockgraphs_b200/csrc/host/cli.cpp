@@ -13,8 +13,18 @@
 //    unless the extension flag --nonelastic-gfa is given, in which case it writes the
 //    xGFA of that segmentation with the elastic writer.
 //  * --heuristic-subset (hidden) is validated but not implemented.
+//
+// Several GPUs (the reference's counterpart is --threads, fbg.cpp:3390-3399): FBG_GPUS=N (or "all") builds ONE
+// graph on N GPUs of the box.  After the FASTA is parsed -- and before this process touches CUDA -- the tool
+// forks N - 1 ranks (they share the parsed MSA copy-on-write); every rank opens its own GPU, joins the NCCL
+// communicator whose id rank 0 hands out over pipes, and makes the same C-ABI calls (sharded index, f and DP,
+// include/fbg_cuda.h "one MSA across the GPUs of a box"); rank 0 alone prints and writes the file.
 #include "../../../include/fbg_cuda.h"
 #include <getopt.h>
+#include <sys/types.h>
+#include <sys/wait.h>
+#include <unistd.h>
+#include <csignal>
 #include <chrono>
 #include <thread>
 #include <utility>
@@ -134,9 +144,53 @@ void write_graphviz_empty(const char *path) {
 	fclose(fp);
 }
 
+int g_rank = 0; // > 0: a forked rank of a multi-GPU run (silent: rank 0 speaks for all)
+volatile sig_atomic_t g_kids_done = 0;
+
+// rank 0: a forked rank that dies would leave the others waiting in a collective for ever
+void on_sigchld(int) {
+	int st = 0;
+	while (waitpid(-1, &st, WNOHANG) > 0) {
+		if (!WIFEXITED(st) || WEXITSTATUS(st) != 0) {
+			static const char msg[] = "ERROR: a GPU rank of this run failed\n";
+			if (write(2, msg, sizeof msg - 1) < 0) {}
+			_exit(EXIT_FAILURE);
+		}
+		g_kids_done = g_kids_done + 1;
+	}
+}
+
 int fail_cuda(fbg_ctx *ctx, const char *what) {
-	fprintf(stderr, "ERROR: %s: %s\n", what, fbg_last_error(ctx));
+	fprintf(stderr, "ERROR: %s%s: %s\n", g_rank ? "(GPU rank > 0) " : "", what, fbg_last_error(ctx));
 	return EXIT_FAILURE;
+}
+
+// GPUs visible to CUDA, asked in a short-lived child so that this process stays fork-safe (no CUDA state yet)
+int visible_gpus() {
+	int fd[2];
+	if (pipe(fd) != 0) return 1;
+	pid_t pid = fork();
+	if (pid == 0) {
+		close(fd[0]);
+		int n = fbg_device_count();
+		if (write(fd[1], &n, sizeof n) != (ssize_t) sizeof n) _exit(1);
+		_exit(0);
+	}
+	close(fd[1]);
+	int n = 1;
+	if (pid < 0 || read(fd[0], &n, sizeof n) != (ssize_t) sizeof n) n = 1;
+	close(fd[0]);
+	if (pid > 0) waitpid(pid, nullptr, 0);
+	return n < 1 ? 1 : n;
+}
+
+// FBG_GPUS: unset / 1 = one GPU, N = that many, "all" = every visible one
+int wanted_gpus() {
+	const char *e = getenv("FBG_GPUS");
+	if (!e || !*e) return 1;
+	if (!strcmp(e, "all")) return visible_gpus();
+	long v = strtol(e, nullptr, 10);
+	return v < 1 ? 1 : (v > 64 ? 64 : (int) v);
 }
 
 } // namespace
@@ -168,9 +222,11 @@ int main(int argc, char **argv) {
 		last = now;
 	};
 	// the CUDA context takes a few hundred milliseconds to come up: create it while the FASTA is parsed
+	// (one GPU; with several, the ranks are forked after the parse and no CUDA call may come before that)
+	const int world = wanted_gpus();
 	fbg_ctx *ctx = nullptr;
 	int ctx_rc = FBG_OK;
-	std::thread ctx_thread([&]() { ctx_rc = fbg_ctx_create(&ctx, -1); });
+	std::thread ctx_thread([&]() { if (world == 1) ctx_rc = fbg_ctx_create(&ctx, -1); });
 	// read_input (fbg.cpp:151-201): host/fasta_reader.cpp, mapped file, several threads
 	fbg_msa msa;
 	bool opened = fbg_read_fasta(a.input.c_str(), (uint64_t) a.gap_limit, a.elastic, a.paths, 0, &msa) == FBG_OK;
@@ -180,6 +236,42 @@ int main(int argc, char **argv) {
 
 	lap("parse");
 	ctx_thread.join();
+	std::vector<pid_t> kids;
+	if (world > 1) {
+		// fork the other ranks (this process is rank 0), then hand out the NCCL id
+		std::vector<int> wfd;
+		int my_rfd = -1;
+		fflush(stdout); fflush(stderr);
+		signal(SIGCHLD, on_sigchld);
+		for (int r = 1; r < world; r++) {
+			int fd[2];
+			if (pipe(fd) != 0) { fprintf(stderr, "ERROR: cannot create a pipe for GPU rank %d\n", r); return EXIT_FAILURE; }
+			pid_t pid = fork();
+			if (pid < 0) { fprintf(stderr, "ERROR: cannot fork GPU rank %d\n", r); return EXIT_FAILURE; }
+			if (pid == 0) {
+				g_rank = r; my_rfd = fd[0]; close(fd[1]);
+				for (int w : wfd) close(w);
+				kids.clear();
+				signal(SIGCHLD, SIG_DFL);
+				if (!getenv("FBG_DEBUG") && !freopen("/dev/null", "w", stderr)) _exit(1); // rank 0 speaks for all
+				break;
+			}
+			close(fd[0]); wfd.push_back(fd[1]); kids.push_back(pid);
+		}
+		ctx_rc = fbg_ctx_create(&ctx, g_rank);
+		if (ctx_rc != FBG_OK) { int rc = fail_cuda(nullptr, "cannot initialise the GPU"); if (g_rank) _exit(rc); return rc; }
+		uint8_t id[128];
+		if (g_rank == 0) {
+			if (fbg_dist_unique_id(id) != FBG_OK) return fail_cuda(nullptr, "NCCL");
+			for (int w : wfd) { if (write(w, id, sizeof id) != (ssize_t) sizeof id) { fprintf(stderr, "ERROR: cannot reach a GPU rank\n"); return EXIT_FAILURE; } close(w); }
+		} else {
+			size_t got = 0;
+			while (got < sizeof id) { ssize_t k = read(my_rfd, id + got, sizeof id - got); if (k <= 0) _exit(1); got += (size_t) k; }
+			close(my_rfd);
+		}
+		if (fbg_dist_init(ctx, g_rank, world, id) != FBG_OK) { int rc = fail_cuda(ctx, "joining the GPUs of this run"); if (g_rank) _exit(rc); return rc; }
+		if (g_rank == 0) fprintf(stderr, "Building on %d GPUs.\n", world);
+	}
 	if (ctx_rc != FBG_OK) return fail_cuda(nullptr, "cannot initialise the GPU");
 	lap("GPU context (rest after the parse)");
 	if (fbg_set_options(ctx, a.elastic, a.gap_limit, (const uint8_t *) a.ignore.data(), a.ignore.size(), a.tricks_off) != FBG_OK) return fail_cuda(ctx, "options");
@@ -218,6 +310,10 @@ int main(int argc, char **argv) {
 		}
 		fprintf(stderr, "Number of segments: %llu\n", (unsigned long long) nb);
 	}
+	// the collective stages are over: graph and file are rank 0's (K4 / K5 use no collective); the other ranks leave,
+	// rank 0 waits until they have (the watchdog above ends the run if one of them failed)
+	if (g_rank) _exit(EXIT_SUCCESS);
+	while (world > 1 && g_kids_done < (sig_atomic_t) kids.size()) usleep(200);
 	bnd.resize(nb);
 	if (fbg_get_boundaries(ctx, bnd.data()) != FBG_OK) return fail_cuda(ctx, "boundaries");
 	lap("segmentation");

@@ -144,6 +144,7 @@ int fbg_run_device(fbg_ctx *ctx, const void *device_rows, uint64_t m, uint64_t n
  * k-mer key range, f(x) by contiguous column range; rank array and f are merged by NCCL
  * all-reduce(max) over NVLink.  Results (SA, ISA, LCP, f, segmentation, graph) are replicated
  * on every rank and bit-identical to the single-GPU build. */
+int fbg_device_count(void);                 /* CUDA devices visible to this process (0 when there is no usable driver) */
 int fbg_dist_unique_id(uint8_t *out128);   /* rank 0: ncclGetUniqueId; ship the 128 bytes to the other ranks */
 int fbg_dist_init(fbg_ctx *ctx, int rank, int world, const uint8_t *id128);   /* collective */
 int fbg_dist_shutdown(fbg_ctx *ctx);
