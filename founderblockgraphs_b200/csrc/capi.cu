@@ -41,7 +41,7 @@ __global__ void check_index_kernel(const u8 *__restrict__ T, const u32 *__restri
 // every per-MSA array lives in the persistent arena: dropping them is resetting the bump pointer
 void Pipeline::free_all() {
 	NG = IG = RK = NIA = start = rowlen = lastcol = nullptr;
-	T = nullptr; msa = nullptr;
+	T = nullptr; msa = nullptr; BWT = nullptr; have_bwt = false;
 	col = ISA = SA = PLCP = f = bnd = dp_a = dp_b = dp_v = nullptr;
 	dev.pers_top = 0;
 	have_msa = have_index = have_f = have_seg = have_xgfa = false;

@@ -78,6 +78,9 @@ struct Dist {
 	void allreduce_max_u32(u32 *buf, u64 count, cudaStream_t s) const {
 		if (world > 1 && count) check(api.AllReduce(buf, buf, count, NCCL_UINT32, NCCL_MAX, comm, s), "ncclAllReduce(max,u32)");
 	}
+	void allreduce_max_u8(u8 *buf, u64 count, cudaStream_t s) const {
+		if (world > 1 && count) check(api.AllReduce(buf, buf, count, NCCL_UINT8, NCCL_MAX, comm, s), "ncclAllReduce(max,u8)");
+	}
 	void allreduce_sum_u64(u64 *buf, u64 count, cudaStream_t s) const {
 		if (world > 1 && count) check(api.AllReduce(buf, buf, count, NCCL_UINT64, NCCL_SUM, comm, s), "ncclAllReduce(sum,u64)");
 	}

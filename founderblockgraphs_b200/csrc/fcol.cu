@@ -79,6 +79,7 @@ __device__ __forceinline__ u32 fcol_fi(const FcolArgs &a, u32 i, u32 l, u32 r, u
 	return fi;
 }
 
+constexpr u64 FC_CHUNK = 8;           // consecutive columns (column groups) a CTA works through before it moves on
 constexpr u32 FC_OCAP = 512;          // cluster path: rows of a column whose rank lies outside the column's cluster
 constexpr u32 FC_MARK = 0xFFFFFFFFu;  // f[x] of a column the cluster path could not take (redone by the sorting kernel)
 
@@ -115,7 +116,13 @@ template <bool CLUSTER> __global__ void __launch_bounds__(1024) k2_fcol_kernel(F
 	const u32 wid = threadIdx.x >> 5, lane = lane_id();
 	const u32 w_first = (grp * tpg) >> 5, w_last = w_first + (tpg >> 5) - 1;
 
-	for (u64 xb = a.x0 + (u64) blockIdx.x * a.groups; xb < a.x1; xb += (u64) gridDim.x * a.groups) {
+	// A CTA takes chunks of FC_CHUNK consecutive column groups: the text positions of one row at neighbouring columns
+	// are neighbours, so the ISA / PLCP / col sectors a column reads are read again by the next seven -- from this
+	// SM's L1 / L2 instead of from HBM (with single columns dealt out round-robin, ncu showed 35 GB of DRAM reads
+	// for 6 GB of algorithmic bytes on cfg3: every column fetched its sectors anew)
+	const u64 ngroups_total = (a.x1 - a.x0 + a.groups - 1) / a.groups;
+	for (u64 it = (u64) blockIdx.x * FC_CHUNK; it < ngroups_total; it = (it % FC_CHUNK == FC_CHUNK - 1) ? it + 1 + ((u64) gridDim.x - 1) * FC_CHUNK : it + 1) {
+		const u64 xb = a.x0 + it * a.groups;
 		const u64 x = xb + grp;
 		const bool live = x < a.x1;
 		if (a.only_marked && a.f[x] != FC_MARK) continue; // (one group per CTA: uniform)
@@ -491,8 +498,9 @@ void k2_compute_f(Pipeline &p) {
 	FBG_CUDA(cudaFuncSetAttribute(k2_fcol_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
 	u64 col_groups = (a.x1 - a.x0 + a.groups - 1) / a.groups;
 	if (col_groups == 0) col_groups = 1;
+	u64 col_chunks = (col_groups + FC_CHUNK - 1) / FC_CHUNK;
 	u64 max_grid = (u64) NUM_SMS * 8;
-	u32 grid = (u32) (col_groups < max_grid ? col_groups : max_grid);
+	u32 grid = (u32) (col_chunks < max_grid ? col_chunks : max_grid);
 	d.begin(K_FCOL);
 	// many rows: placement by rank instead of a sort (cluster form of the kernel), then the sorting form for the
 	// columns that did not fit; the window needs some room beyond the m ranks of the cluster

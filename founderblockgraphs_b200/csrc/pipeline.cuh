@@ -118,6 +118,8 @@ struct Pipeline {
 	u32 *start = nullptr, *rowlen = nullptr, *lastcol = nullptr;
 	u8 *T = nullptr;
 	u32 *col = nullptr, *ISA = nullptr, *SA = nullptr, *PLCP = nullptr;
+	u8 *BWT = nullptr;     // [N] T[SA[k] - 1], written with the SA entries of a single-GPU full index (suffix.cu SaOut)
+	bool have_bwt = false;
 	u32 *f = nullptr, *bnd = nullptr;
 	u32 *dp_a = nullptr, *dp_b = nullptr; // mml/backtrack or s/prev (+ v)
 	u32 *dp_v = nullptr;
@@ -169,7 +171,7 @@ u64 k5_scratch_need(u64 m, u64 nb, bool paths, u64 id_bytes);
 // bytes of the persistent arena one m x n MSA can need (N <= m*n + m + 1)
 static inline u64 persistent_need(u64 m, u64 n) {
 	u64 pitch = round_up(n, 32), W = pitch / 32, N = m * n + m + 1;
-	return m * pitch + 16 * W * m + 12 * (m + 1) + (N + 64) + 4 * 4 * (N + 1) + 6 * 4 * (n + 2) + 64 * 256 + N + (1u << 19) + 64;
+	return m * pitch + 16 * W * m + 12 * (m + 1) + (N + 64) + 4 * 4 * (N + 1) + 6 * 4 * (n + 2) + 64 * 256 + N + (N + 64) + (1u << 19) + 64;
 }
 
 } // namespace fbg

@@ -199,6 +199,18 @@ template <int MODE> __global__ void __launch_bounds__(KM_THREADS) k1_kmer_kernel
 // rank plus its offset inside the (sorted) bucket.  All rank look-ups R[p+h] of a
 // round are done by the compaction kernel of the round before, i.e. before any
 // rank of the round changes.
+// Where a suffix leaves with its final rank: the SA entry, and -- single-GPU full index -- the BWT character
+// T[p - 1] next to it (0 for p = 0: no other position has that predecessor, the sentinel is the last byte).  The
+// lists are in text order, so the T reads here are cheap, while the LCP stage would otherwise fetch
+// T[SA[k] - 1] for every k at random: ncu showed 55 GB of DRAM reads for that on cfg3 (k1_irr_flag_kernel).
+struct SaOut {
+	u32 *SA; u8 *BWT; const u8 *T;
+	__device__ __forceinline__ void put(u32 rank, u32 p) const {
+		SA[rank] = p;
+		if (BWT) BWT[rank] = p ? __ldg(T + p - 1) : (u8) 0;
+	}
+};
+
 constexpr u32 BSMALL = 8192;     // largest bucket the shared-memory paths take (CAP_max / 2)
 // ... and, when the M list is in use, the S list only keeps buckets below MID_MIN: buckets of
 // MID_MIN .. BSMALL suffixes go to the M list (same record format), where one CTA streams one
@@ -221,7 +233,7 @@ __global__ void k1_heads_kernel(const u64 *__restrict__ keys, u64 na, int hi_shi
 
 // new rank = bucket rank + (sub-head index - bucket-head index); class by sub-bucket size
 __global__ void __launch_bounds__(256) k1_update_kernel(const u64 *__restrict__ keys, const u32 *__restrict__ vals, const u64 *__restrict__ HH, const u32 *__restrict__ HR,
-                                                        u64 na, int hi_shift, u32 rank_off, u32 mid_min, u32 *__restrict__ R, u32 *__restrict__ SA, u32 *__restrict__ newr, u8 *__restrict__ cls, u32 *__restrict__ maxb) {
+                                                        u64 na, int hi_shift, u32 rank_off, u32 mid_min, u32 *__restrict__ R, SaOut so, u32 *__restrict__ newr, u8 *__restrict__ cls, u32 *__restrict__ maxb) {
 	__shared__ u32 smax[8];
 	u64 t = (u64) blockIdx.x * blockDim.x + threadIdx.x;
 	u32 small_size = 0;
@@ -236,7 +248,7 @@ __global__ void __launch_bounds__(256) k1_update_kernel(const u64 *__restrict__ 
 		u32 c = size == 1 ? CLS_DROP : (size < mid_min ? CLS_SMALL : (size <= BSMALL ? CLS_MID : CLS_BIG)); // mid_min = BSMALL + 1: no M list
 		const u32 pv = vals[t];
 		R[pv] = nr;
-		if (c == CLS_DROP) SA[nr] = pv; // a suffix alone in its bucket has its final rank: the SA entry is written as it leaves
+		if (c == CLS_DROP) so.put(nr, pv); // a suffix alone in its bucket has its final rank: the SA entry is written as it leaves
 		newr[t] = nr;
 		cls[t] = (u8) c;
 		if (c == CLS_SMALL && hs == (u32) t) small_size = size;
@@ -451,7 +463,7 @@ __device__ __forceinline__ u32 ts_last_flag(u32 fm, u32 base, u32 &carry) {
 
 template <int CAP> __global__ void __launch_bounds__(TileCfg<CAP>::THREADS, TileCfg<CAP>::MINB)
 k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, const u32 *__restrict__ r2, u64 na, u32 tile,
-                    u32 *__restrict__ R, u32 *__restrict__ SA, u32 *__restrict__ lp_out, u32 *__restrict__ lr_out, u8 *__restrict__ cls_out, u32 *__restrict__ scal) {
+                    u32 *__restrict__ R, SaOut so, u32 *__restrict__ lp_out, u32 *__restrict__ lr_out, u8 *__restrict__ cls_out, u32 *__restrict__ scal) {
 	constexpr int THREADS = TileCfg<CAP>::THREADS;
 	constexpr int ITEMS = CAP / THREADS;
 	constexpr int NW = THREADS / 32;
@@ -655,7 +667,7 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 					const u32 nr = rv4[c] + nless;
 					const bool single = neq == 1;
 					if (nless) R[p] = nr;           // otherwise the rank is the one the suffix already has
-					if (single) SA[nr] = p;
+					if (single) so.put(nr, p);
 					lp_out[w0 + out] = p;
 					lr_out[w0 + out] = nr;
 					cls_out[w0 + out] = (u8) (single ? CLS_DROP : CLS_SMALL);
@@ -718,7 +730,7 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 			const u32 p = STAGE ? lps[e] : lp[w0 + e];
 			const bool single = hs == s && last;
 			if (hrel) R[p] = nr;
-			if (single) SA[nr] = p;
+			if (single) so.put(nr, p);
 			lp_out[w0 + out] = p;
 			lr_out[w0 + out] = nr;
 			cls_out[w0 + out] = (u8) (single ? CLS_DROP : CLS_SMALL);
@@ -730,7 +742,7 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 }
 
 template <int CAP> static void launch_tile_sort(Dev &d, const u32 *lp, const u32 *lr, const u32 *r2, u64 na, u32 maxb,
-                                                u32 *R, u32 *SA, u32 *lp_out, u32 *lr_out, u8 *cls_out, u32 *scal) {
+                                                u32 *R, SaOut SA, u32 *lp_out, u32 *lr_out, u8 *cls_out, u32 *scal) {
 	u32 tile = ((u32) CAP - maxb) & ~3u; // a multiple of four: 16-byte aligned windows for the staging copies
 	const size_t smem = TileCfg<CAP>::SMEM;
 	FBG_CUDA(cudaFuncSetAttribute(k1_tile_sort_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
@@ -786,7 +798,7 @@ constexpr size_t BS_SMEM = (size_t) BSMALL * 8 + ((size_t) BSMALL / 32 + 1) * 4;
 
 __global__ void __launch_bounds__(BS_THREADS, 3)
 k1_bucket_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, const u32 *__restrict__ r2, u64 na, u32 mid_min,
-                      u32 *__restrict__ R, u32 *__restrict__ SA, u32 *__restrict__ lp_out, u32 *__restrict__ lr_out, u8 *__restrict__ cls_out, u32 *__restrict__ scal) {
+                      u32 *__restrict__ R, SaOut so, u32 *__restrict__ lp_out, u32 *__restrict__ lr_out, u8 *__restrict__ cls_out, u32 *__restrict__ scal) {
 	extern __shared__ __align__(16) unsigned char bs_raw[];
 	u64 *key = reinterpret_cast<u64 *>(bs_raw);
 	u32 *bal = reinterpret_cast<u32 *>(bs_raw + (size_t) BSMALL * 8);
@@ -899,7 +911,7 @@ k1_bucket_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, co
 						const u64 out = h + nless + eq_run + (pre & 0xFFFFu) + (u32) __popc(be[j] & lanemask_lt());
 						lp_out[out] = pp[j]; lr_out[out] = req; cls_out[out] = (u8) cls_eq;
 						if (nless) R[pp[j]] = req;
-						if (neq == 1) SA[req] = pp[j];
+						if (neq == 1) so.put(req, pp[j]);
 					} else {
 						const u32 mp = mn_run + (pre >> 16) + (u32) __popc(bm[j] & lanemask_lt());
 						key[ts_sw(mp)] = ((u64) (rv[j] > pv ? 1u : 0u) << 45) | ((u64) rv[j] << 13) | (u64) q;
@@ -942,7 +954,7 @@ k1_bucket_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, co
 					const u32 nr = lrh + (gt ? neq : 0u) + hs;
 					const u32 c = sz == 1 ? CLS_DROP : (sz < mid_min ? CLS_SMALL : CLS_MID);
 					if (nr != lrh) R[p] = nr;
-					if (sz == 1) SA[nr] = p;
+					if (sz == 1) so.put(nr, p);
 					lp_out[out] = p; lr_out[out] = nr; cls_out[out] = (u8) c;
 					if (c == CLS_SMALL && sx == hs) mx = sz > mx ? sz : mx;
 				}
@@ -955,7 +967,7 @@ k1_bucket_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, co
 }
 
 static void launch_bucket_sort(Dev &d, const u32 *lp, const u32 *lr, const u32 *r2, u64 na, u32 mid_min,
-                               u32 *R, u32 *SA, u32 *lp_out, u32 *lr_out, u8 *cls_out, u32 *scal) {
+                               u32 *R, SaOut SA, u32 *lp_out, u32 *lr_out, u8 *cls_out, u32 *scal) {
 	FBG_CUDA(cudaFuncSetAttribute(k1_bucket_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) BS_SMEM));
 	k1_bucket_sort_kernel<<<div_up(na, BS_TILE), BS_THREADS, BS_SMEM, d.stream>>>(lp, lr, r2, na, mid_min, R, SA, lp_out, lr_out, cls_out, scal);
 	FBG_LAUNCH_CHECK();
@@ -1142,7 +1154,7 @@ __global__ void k1_dict_place_kernel(const u32 *__restrict__ ov, const u32 *__re
 // members of the buckets it sorts; a position outside its columns matters only when its bucket spans GPUs
 template <bool PEER>
 __global__ void __launch_bounds__(256) k1_dict_emit_kernel(const u32 *__restrict__ slot_of, const u32 *__restrict__ ord_of, const uint4 *__restrict__ info, const u32 *__restrict__ rank_of_slot,
-                                                           u64 N, u64 hnext, int nbits, u32 mid_min, u32 *__restrict__ R, u32 *__restrict__ SA, CompactOut o,
+                                                           u64 N, u64 hnext, int nbits, u32 mid_min, u32 *__restrict__ R, SaOut so, CompactOut o,
                                                            const u32 *__restrict__ col, const u8 *__restrict__ spans, u32 x0, u32 x1, int last) {
 	u64 p = (u64) blockIdx.x * blockDim.x + threadIdx.x;
 	if (p >= N) return;
@@ -1165,7 +1177,7 @@ __global__ void __launch_bounds__(256) k1_dict_emit_kernel(const u32 *__restrict
 	}
 	const uint4 v = __ldg(info + slot_of[p]);
 	R[p] = v.x;
-	if (v.z == 1) { SA[v.x] = (u32) p; return; }
+	if (v.z == 1) { so.put(v.x, (u32) p); return; }
 	if (v.y == U32_MAX) return; // peer mode: another GPU sorts this bucket
 	const u64 pn = p + hnext;
 	const u32 r2 = pn < N ? __ldg(rank_of_slot + slot_of[pn]) : 0u; // 4-byte entries: a quarter of the L2 traffic of info[]
@@ -1357,9 +1369,9 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	k1_dict_place_kernel<<<gn, 256, 0, d.stream>>>(ov, lv, nd, mid_min, zs, zm, info);
 	if (pv) {
 		FBG_CUDA(cudaMemsetAsync(p.ISA, 0, N * sizeof(u32), d.stream)); // ranks outside this GPU's columns stay 0: the inverse is assembled by max at the end
-		k1_dict_emit_kernel<true><<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, p.SA, o,
+		k1_dict_emit_kernel<true><<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, SaOut{p.SA, p.have_bwt ? p.BWT : nullptr, p.T}, o,
 		                                                                 p.col, spans, pv->xb[pv->me], pv->xb[pv->me + 1], pv->me + 1 == pv->world ? 1 : 0);
-	} else k1_dict_emit_kernel<false><<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, p.SA, o, nullptr, nullptr, 0, 0, 0);
+	} else k1_dict_emit_kernel<false><<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, SaOut{p.SA, p.have_bwt ? p.BWT : nullptr, p.T}, o, nullptr, nullptr, 0, 0, 0);
 	FBG_LAUNCH_CHECK();
 	d.end((double) N * (8.0 + 4.0 + 4.0 + 12.0) + (double) nd * 40.0);
 	d.note_launches(K_DOUBLING_AUX, 1);
@@ -1378,6 +1390,11 @@ void k1_suffix_array(Pipeline &p) {
 	if (!p.ISA) p.ISA = p.dev.palloc<u32>(N + 1); // (a full index built after a sufficient one re-uses the arrays)
 	if (!p.SA) p.SA = p.dev.palloc<u32>(N + 1);
 	if (!p.PLCP) p.PLCP = p.dev.palloc<u32>(N + 1);
+	// BWT next to the SA (SaOut) for the LCP stage of a full index (the sufficient index finds its LCPs differently);
+	// a multi-GPU build merges the bytes like the SA entries: every entry is written by the GPU(s) that sorted its bucket
+	p.have_bwt = !getenv("FBG_NO_BWT");
+	if (p.have_bwt && !p.BWT) p.BWT = p.dev.palloc<u8>(N + 64);
+	if (p.have_bwt && sharded) FBG_CUDA(cudaMemsetAsync(p.BWT, 0, N, d.stream));
 	p.index_lazy = false; p.lazy_depth = 0; p.index_virtual = false; p.dict_nd = 0;
 	// the sufficient index (above): gapless rows, one GPU, unless the full index was asked for
 	const bool lazy_ok = !sharded && p.gaps == 0 && !p.want_full_index && !getenv("FBG_FULL_INDEX");
@@ -1531,6 +1548,7 @@ void k1_suffix_array(Pipeline &p) {
 	FBG_LAUNCH_CHECK();
 	if (!by_dict) d.end((double) N * (1.0 + 8.0 + 4.0));
 
+	const SaOut sao{p.SA, p.have_bwt ? p.BWT : nullptr, p.T};
 	u64 h = (u64) K;      // depth the current ranks are exact to after the round being run
 	int hi_shift = 64;    // round 0: a single level of buckets
 	int key_bits = key_bits0;
@@ -1603,16 +1621,16 @@ void k1_suffix_array(Pipeline &p) {
 		// ---- S path: windows of whole small buckets sorted in shared memory
 		if (nS) {
 			d.begin(K_TILE_SORT);
-			if (2 * maxb <= 2048) launch_tile_sort<2048>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
-			else if (2 * maxb <= 4096) launch_tile_sort<4096>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
-			else if (2 * maxb <= 8192) launch_tile_sort<8192>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
-			else launch_tile_sort<16384>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, p.SA, lp_out, lr_out, clsS, sc32);
+			if (2 * maxb <= 2048) launch_tile_sort<2048>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, sao, lp_out, lr_out, clsS, sc32);
+			else if (2 * maxb <= 4096) launch_tile_sort<4096>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, sao, lp_out, lr_out, clsS, sc32);
+			else if (2 * maxb <= 8192) launch_tile_sort<8192>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, sao, lp_out, lr_out, clsS, sc32);
+			else launch_tile_sort<16384>(d, Slp[sc], Slr[sc], Sr2[sc], nS, maxb, p.ISA, sao, lp_out, lr_out, clsS, sc32);
 			d.end((double) nS * (12.0 + 4.0 + 9.0));
 		}
 		// ---- M path: one CTA streams one bucket
 		if (nM) {
 			d.begin(K_TILE_SORT);
-			launch_bucket_sort(d, Mlp[sc], Mlr[sc], Mr2[sc], nM, mid_min, p.ISA, p.SA, lp_out + nS, lr_out + nS, clsS + nS, sc32);
+			launch_bucket_sort(d, Mlp[sc], Mlr[sc], Mr2[sc], nM, mid_min, p.ISA, sao, lp_out + nS, lr_out + nS, clsS + nS, sc32);
 			d.end((double) nM * (12.0 + 4.0 + 9.0));
 		}
 		// ---- B path
@@ -1629,7 +1647,7 @@ void k1_suffix_array(Pipeline &p) {
 			device_scan<OpMax2x32, false>(d, HH, HH, nB);
 			device_scan<OpMaxU32, false>(d, HR, HR, nB);
 			d.begin(K_DOUBLING_AUX);
-			k1_update_kernel<<<g, 256, 0, d.stream>>>(sk, sv, HH, HR, nB, hi_shift, rank_off, mid_min, p.ISA, p.SA, newr, clsB, sc32);
+			k1_update_kernel<<<g, 256, 0, d.stream>>>(sk, sv, HH, HR, nB, hi_shift, rank_off, mid_min, p.ISA, sao, newr, clsB, sc32);
 			FBG_LAUNCH_CHECK();
 			d.end((double) nB * (8.0 + 4.0 + 8.0 + 4.0 + 4.0 + 4.0 + 1.0));
 		}
@@ -1698,7 +1716,8 @@ void k1_suffix_array(Pipeline &p) {
 		// every GPU wrote the SA entries of its own suffixes only (the rest is still 0): merge like the ranks
 		d.begin(K_COMM);
 		dist.allreduce_max_u32(p.SA, N, d.stream);
-		d.end((double) N * 8.0);
+		if (p.have_bwt) dist.allreduce_max_u8(p.BWT, N, d.stream);
+		d.end((double) N * 10.0);
 	}
 	if (peer) {
 		// Ranks: every GPU holds the final ranks of its own columns, older (hence smaller) values elsewhere.  K2 also
@@ -1722,6 +1741,13 @@ __global__ void k1_irr_flag_kernel(const u32 *__restrict__ SA, const u8 *__restr
 		if (a != 0 && bq != 0 && T[a - 1] == T[bq - 1]) irr = 0;
 	}
 	flag[k] = irr;
+}
+
+// the same from the BWT characters written next to the SA entries (SaOut): BWT[k] = T[SA[k] - 1], 0 for SA[k] = 0
+__global__ void k1_irr_flag_bwt_kernel(const u8 *__restrict__ BWT, u64 N, u32 *__restrict__ flag) {
+	u64 k = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (k >= N) return;
+	flag[k] = (k == 0 || BWT[k] != BWT[k - 1]) ? 1u : 0u;
 }
 
 __global__ void k1_irr_compact_kernel(const u32 *__restrict__ SA, const u32 *__restrict__ flag, const u32 *__restrict__ pos, u64 N, u32 *__restrict__ ia, u32 *__restrict__ ib) {
@@ -1776,7 +1802,8 @@ void k1_lcp(Pipeline &p) {
 	u32 *h_total = reinterpret_cast<u32 *>(p.h_scalars + 8);
 	u32 g = div_up(N, 256);
 	d.begin(K_LCP);
-	k1_irr_flag_kernel<<<g, 256, 0, d.stream>>>(p.SA, p.T, N, flag);
+	if (p.have_bwt) k1_irr_flag_bwt_kernel<<<g, 256, 0, d.stream>>>(p.BWT, N, flag);
+	else k1_irr_flag_kernel<<<g, 256, 0, d.stream>>>(p.SA, p.T, N, flag);
 	FBG_LAUNCH_CHECK();
 	d.end((double) N * (4.0 + 2.0 + 4.0));
 	device_scan<OpSumU32, true>(d, flag, pos, N, total);

@@ -82,10 +82,13 @@ template <class PASS> FBG_HD void ts_schedule(uint32_t cap, PASS &pass) {
 	pass.first();
 	for (uint32_t k = 16; k <= cap; k <<= 1) {
 		uint32_t j = k >> 1;
-		// number of stages of this phase = log2(k); peel 3 at a time from the top,
-		// leaving the remainder (1 or 2) for the last pass
-		int stages = 0;
-		for (uint32_t q = k; q > 1; q >>= 1) stages++;
+		// peel 3 stages at a time from the top, leaving the remainder (1 or 2) for the last pass
+		// number of stages of this phase = log2(k)
+#if defined(__CUDA_ARCH__)
+		int stages = 31 - __clz((int) k);
+#else
+		int stages = 31 - __builtin_clz(k);
+#endif
 		while (stages > 0) {
 			int nst = stages >= 3 ? 3 : stages;
 			if (nst == 3) pass.template run<3>(k, j);
