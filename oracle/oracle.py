@@ -216,6 +216,79 @@ def graph(msa: np.ndarray, boundaries: np.ndarray) -> dict:
                 edge_src=es[: ne.value].copy(), edge_dst=ed[: ne.value].copy(), label_total=lt.value)
 
 
+# --------------------------------------------------- --heuristic-subset
+
+def efg_validate(msa: np.ndarray, boundaries: np.ndarray, ignore: bytes = b""):
+    """efg_validate / efg_validate_node (fbg.cpp:3104-3292) on the graph of `boundaries`: a node that is neither
+    source nor sink and holds no ignore character is INVALID when its label occurs in some edge string
+    label(u) + label(v) anywhere but at the very start of u or of v with that node in the same block.  Returns the
+    set of boundary indices to drop (block b invalid -> boundary b - 1, fbg.cpp:3270-3271).  Plain string search:
+    small inputs only."""
+    g = graph(msa, boundaries)
+    b = [int(x) for x in boundaries]
+    starts = [0] + [x + 1 for x in b[:-1]]
+    n = msa.shape[1]
+
+    def label(v):
+        j, i = int(g["node_block"][v]), int(g["node_row"][v])
+        seg = msa[i, starts[j]: min(b[j], n - 1) + 1]
+        return bytes(seg[seg != 0x2D])
+
+    nn = len(g["node_block"])
+    labels = [label(v) for v in range(nn)]
+    has_in, has_out = [False] * nn, [False] * nn
+    edges = list(zip((int(x) for x in g["edge_src"]), (int(x) for x in g["edge_dst"])))
+    for u, v in edges:
+        has_out[u] = True
+        has_in[v] = True
+    drop = set()
+    for w in range(nn):
+        if not has_in[w] or not has_out[w]:   # is_source / is_sink (fbg.cpp:3116-3117)
+            continue
+        lab = labels[w]
+        if ignore and any(c in lab for c in ignore):  # fbg.cpp:3119-3120
+            continue
+        bw = int(g["node_block"][w])
+        bad = False
+        for u, v in edges:
+            s = labels[u] + labels[v]
+            pos = s.find(lab)
+            while pos >= 0 and not bad:
+                if pos < len(labels[u]):
+                    ok = pos == 0 and int(g["node_block"][u]) == bw
+                else:
+                    ok = pos == len(labels[u]) and int(g["node_block"][v]) == bw
+                bad = not ok
+                pos = s.find(lab, pos + 1)
+            if bad:
+                break
+        if bad and bw > 0:
+            drop.add(bw - 1)
+    return drop
+
+
+def heuristic_subset(msa: np.ndarray, rownum: int, ignore: bytes = b"", disable_tricks: bool = False):
+    """The reference's --heuristic-subset=ROWNUM pipeline (fbg.cpp:3400-3433, 2158-2178, 3467-3500): f = max over
+    chunks of ROWNUM consecutive rows of the chunk's own f, one DP on that f, then blocks are merged with their
+    predecessor until every node passes efg_validate.  Returns (boundaries, [blocks removed per iteration], score,
+    no_solution)."""
+    m, n = msa.shape
+    f = np.zeros(n, np.uint64)
+    for r0 in range(0, m, rownum):
+        f = np.maximum(f, compute_f(np.ascontiguousarray(msa[r0: r0 + rownum]), ignore, disable_tricks))
+    if disable_tricks and int(f[0]) == n:     # fbg.cpp:2048-2053
+        return None, [], None, True
+    mml, _, b = dp_elastic(f)
+    removed = []
+    while True:
+        drop = efg_validate(msa, b, ignore)
+        removed.append(len(drop))
+        if not drop:
+            break
+        b = np.array([x for i, x in enumerate(b) if i not in drop], np.uint64)
+    return b, removed, int(mml[-1]), False
+
+
 def write_xgfa(path: str, msa: np.ndarray, boundaries: np.ndarray, ids=None) -> None:
     m, n = msa.shape
     bnd = np.ascontiguousarray(boundaries, np.uint64)
