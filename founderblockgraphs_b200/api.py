@@ -55,7 +55,7 @@ EXPORTS = [
     "fbg_graph_free", "fbg_run", "fbg_run_device", "fbg_get_stream", "fbg_get_stats", "fbg_reset_stats", "fbg_get_f", "fbg_get_text",
     "fbg_get_sa", "fbg_get_isa", "fbg_get_lcp", "fbg_get_dp", "fbg_radix_sort_pairs", "fbg_radix_sort_bench", "fbg_write_xgfa",
     "fbg_check_index", "fbg_set_dp_chunking", "fbg_dist_unique_id", "fbg_dist_init", "fbg_dist_shutdown", "fbg_plan_key_ranges", "fbg_plan_columns",
-    "fbg_format_xgfa", "fbg_read_xgfa", "fbg_save_xgfa", "fbg_read_fasta", "fbg_msa_free", "fbg_radix_sort_pairs_noalloc", "fbg_device_count",
+    "fbg_format_xgfa", "fbg_read_xgfa", "fbg_save_xgfa", "fbg_read_fasta", "fbg_msa_free", "fbg_radix_sort_pairs_noalloc", "fbg_device_count", "fbg_heuristic_f", "fbg_validate_blocks",
 ]
 NOALLOC_MAX_PAIRS = 1 << 20  # FBG_NOALLOC_MAX_PAIRS
 
@@ -112,6 +112,8 @@ def load_library():
     lib.fbg_radix_sort_pairs.argtypes = [C.c_void_p, _u64p, _u32p, C.c_uint64, C.c_int, C.c_int]
     lib.fbg_radix_sort_bench.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double)]
     lib.fbg_radix_sort_pairs_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int]
+    lib.fbg_heuristic_f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, _u64p, _u64p]
+    lib.fbg_validate_blocks.argtypes = [C.c_void_p, _u64p, _u64p, C.POINTER(FbgGraph)]
     lib.fbg_write_xgfa.argtypes = [C.c_char_p, C.c_void_p, C.c_uint64, C.c_uint64, _u64p, C.POINTER(FbgGraph), C.c_int, C.POINTER(C.c_char_p)]
     lib.fbg_format_xgfa.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(FbgGraph), _u64p]
     lib.fbg_read_xgfa.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p]
@@ -335,6 +337,27 @@ class Context:
 
     def save_xgfa(self, path: str):
         self._check(self.lib.fbg_save_xgfa(self.h, path.encode()))
+
+    def heuristic_subset(self, msa: np.ndarray, rownum: int):
+        """--heuristic-subset=ROWNUM through the C ABI: f = max over row chunks (fbg_heuristic_f), one DP (fbg_segment), then
+        the repair loop (fbg_validate_blocks until nothing is removed).  Options as set by set_options (elastic).
+        Returns (boundaries, [boundaries removed per pass], score, f)."""
+        msa = np.ascontiguousarray(msa, dtype=np.uint8)
+        self._msa = msa
+        self.free_graph()
+        self._check(self.lib.fbg_heuristic_f(self.h, msa.ctypes.data, msa.shape[0], msa.shape[1], rownum, None, None))
+        f = self.get_f()
+        b, score = self.segment()
+        removed = []
+        while True:
+            nr, nbl = C.c_uint64(), C.c_uint64()
+            self._check(self.lib.fbg_validate_blocks(self.h, C.byref(nr), C.byref(nbl), None))
+            removed.append(int(nr.value))
+            if nr.value == 0:
+                break
+        out = np.zeros(nbl.value, np.uint64)
+        self._check(self.lib.fbg_get_boundaries(self.h, out.ctypes.data_as(_u64p)))
+        return out, removed, score, f
 
     def stream_ptr(self) -> int:
         return int(self.lib.fbg_get_stream(self.h) or 0)

@@ -11,8 +11,26 @@ using namespace fbg;
 
 struct fbg_ctx {
 	Pipeline p;
+	Pipeline *aux = nullptr; // --heuristic-subset: indexes the edge text of the repair loop (validate.cu); lives until the loop is done
 	std::string err;
 };
+
+// everything a Pipeline owns on the device
+static void release_pipeline(Pipeline &p) {
+	if (p.dev.stream) cudaStreamSynchronize(p.dev.stream);
+	p.free_all();
+	if (p.scalars) { cudaFree(p.scalars); p.scalars = nullptr; }
+	if (p.h_scalars) { cudaFreeHost(p.h_scalars); p.h_scalars = nullptr; }
+	if (p.xgfa) { cudaFree(p.xgfa); p.xgfa = nullptr; }
+	p.dev.destroy();
+	if (p.dev.stream) { cudaStreamDestroy(p.dev.stream); p.dev.stream = nullptr; }
+}
+static void drop_aux(fbg_ctx *ctx) {
+	if (!ctx->aux) return;
+	release_pipeline(*ctx->aux);
+	delete ctx->aux;
+	ctx->aux = nullptr;
+}
 
 static std::string g_create_err;
 
@@ -47,6 +65,7 @@ void Pipeline::free_all() {
 	have_msa = have_index = have_f = have_seg = have_xgfa = false;
 	want_full_index = index_lazy = false; lazy_depth = 0;
 	index_virtual = force_arrays = false; dict_col = dict_lcp = nullptr; dict_nd = 0;
+	f_external = false;
 }
 
 } // namespace fbg
@@ -105,6 +124,7 @@ void fbg_ctx_destroy(fbg_ctx *ctx) {
 		if (ctx->p.dist.xchg) { cudaFree(ctx->p.dist.xchg); ctx->p.dist.xchg = nullptr; }
 		ctx->p.dist.api.CommDestroy(ctx->p.dist.comm); ctx->p.dist.comm = nullptr;
 	}
+	drop_aux(ctx);
 	ctx->p.free_all();
 	if (ctx->p.scalars) cudaFree(ctx->p.scalars);
 	if (ctx->p.h_scalars) cudaFreeHost(ctx->p.h_scalars);
@@ -169,7 +189,10 @@ static int build_index_impl(fbg_ctx *ctx, bool full, bool need_arrays = true) {
 	return FBG_OK;
 }
 
-int fbg_build_index(fbg_ctx *ctx) { return build_index_impl(ctx, true); }
+int fbg_build_index(fbg_ctx *ctx) {
+	if (ctx && ctx->p.f_external) { ctx->err = "fbg_heuristic_f holds no index of the whole MSA: upload the MSA again for a full build"; return FBG_ERR_ARG; }
+	return build_index_impl(ctx, true);
+}
 
 int fbg_compute_f(fbg_ctx *ctx) {
 	if (!ctx) return FBG_ERR_ARG;
@@ -179,6 +202,7 @@ int fbg_compute_f(fbg_ctx *ctx) {
 	FBG_TRY(ctx)
 	Pipeline &p = ctx->p;
 	if (p.have_f) return FBG_OK;
+	if (p.f_external) { ctx->err = "options changed after fbg_heuristic_f: call it again"; return FBG_ERR_ARG; }
 	// non-elastic: v[j] is defined through f without the row-end tricks and without
 	// ignore characters (fbg.cpp:552-611 has neither)
 	struct Restore { bool &ref, val; ~Restore() { ref = val; } } restore{p.opt.disable_tricks, p.opt.disable_tricks}; // also when K2 throws
@@ -365,6 +389,81 @@ int fbg_run_device(fbg_ctx *ctx, const void *rows, uint64_t m, uint64_t n, int w
 	return run_common(ctx, rows, m, n, true, want_paths, n_blocks, score, out);
 }
 
+namespace fbg {
+__global__ void hs_max_kernel(u32 *__restrict__ acc, const u32 *__restrict__ f, u64 n, int first) {
+	u64 x = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (x < n) { const u32 v = f[x]; acc[x] = first ? v : (v > acc[x] ? v : acc[x]); }
+}
+} // namespace fbg
+
+// --heuristic-subset=ROWNUM, first half (fbg.cpp:3400-3433, worker 2158-2178): f(x) of every chunk of ROWNUM
+// consecutive rows from the chunk's own index, f = their maximum.  Only one chunk's index is ever in device
+// memory.  Then the WHOLE MSA is uploaded and packed (K0: text, bitmaps, rank tables -- what K4 / K5 read; no
+// index) and f installed, so that fbg_segment, fbg_validate_blocks, fbg_build_graph and fbg_format_xgfa follow.
+int fbg_heuristic_f(fbg_ctx *ctx, const uint8_t *rows, uint64_t m, uint64_t n, uint64_t rownum, uint64_t *chunk_gaps, uint64_t *chunk_ignore) {
+	if (!ctx || !rows || m == 0 || n == 0 || rownum == 0) { if (ctx) ctx->err = "empty MSA or chunk size 0"; return FBG_ERR_ARG; }
+	if (!ctx->p.opt.elastic) { ctx->err = "--heuristic-subset belongs to the elastic path (fbg.cpp:3390-3433)"; return FBG_ERR_ARG; }
+	u32 *acc = nullptr;
+	int rc = FBG_OK;
+	drop_aux(ctx);
+	{
+		cudaSetDevice(ctx->p.dev.device);
+		if (cudaMalloc(&acc, (n + 1) * sizeof(u32)) != cudaSuccess) { cudaGetLastError(); ctx->err = "cannot allocate the f accumulator"; return FBG_ERR_CUDA; }
+	}
+	u64 k = 0;
+	for (u64 r0 = 0; r0 < m && rc == FBG_OK; r0 += rownum, k++) {
+		const u64 mc = m - r0 < rownum ? m - r0 : rownum;
+		rc = upload_common(ctx, rows + r0 * n, mc, n, false);
+		if (rc == FBG_OK) rc = fbg_compute_f(ctx);
+		if (rc != FBG_OK) break;
+		Pipeline &p = ctx->p;
+		if (chunk_gaps) chunk_gaps[k] = p.gaps;
+		if (chunk_ignore) chunk_ignore[k] = p.toignore;
+		hs_max_kernel<<<div_up(n, 256), 256, 0, p.dev.stream>>>(acc, p.f, n, r0 == 0 ? 1 : 0);
+		if (cudaStreamSynchronize(p.dev.stream) != cudaSuccess) { ctx->err = "accumulating f failed"; cudaGetLastError(); rc = FBG_ERR_CUDA; }
+	}
+	if (rc == FBG_OK) rc = upload_common(ctx, rows, m, n, false);
+	if (rc == FBG_OK) {
+		try {
+			Pipeline &p = ctx->p;
+			k0_pack(p);
+			p.f = p.dev.palloc<u32>(n + 1);
+			FBG_CUDA(cudaMemcpyAsync(p.f, acc, n * sizeof(u32), cudaMemcpyDeviceToDevice, p.dev.stream));
+			FBG_CUDA(cudaStreamSynchronize(p.dev.stream));
+			p.have_index = true; p.have_f = true; p.f_external = true; p.have_seg = false;
+			p.sa_rounds = 0; p.kmer_dict = 0;
+		} catch (const fbg::unsupported_error &e) { ctx->err = e.what(); rc = FBG_ERR_UNSUPPORTED; }
+		catch (const std::exception &e) { ctx->err = e.what(); cudaGetLastError(); rc = FBG_ERR_CUDA; }
+	}
+	cudaFree(acc);
+	return rc;
+}
+
+// --heuristic-subset, second half: ONE pass of the repair loop (fbg.cpp:3467-3500, efg_validate 3199-3292) over
+// the graph of the current segmentation; blocks holding an invalid node are merged with their predecessor.
+// *n_removed = boundaries dropped ("There are K blocks to remove"); call again until it is 0.
+int fbg_validate_blocks(fbg_ctx *ctx, uint64_t *n_removed, uint64_t *n_blocks, fbg_graph *counts) {
+	if (!ctx || !n_removed || !ctx->p.have_seg || ctx->p.seg_status) { if (ctx) ctx->err = "no segmentation available"; return FBG_ERR_ARG; }
+	if (!ctx->p.opt.elastic) { ctx->err = "the repair loop belongs to the elastic path"; return FBG_ERR_ARG; }
+	if (counts) std::memset(counts, 0, sizeof *counts);
+	FBG_TRY(ctx)
+	Pipeline &p = ctx->p;
+	FBG_CUDA(cudaSetDevice(p.dev.device));
+	if (!ctx->aux) ctx->aux = new Pipeline();
+	ValidateJob v;
+	v.aux = ctx->aux;
+	p.have_xgfa = false;
+	const u64 nb_before = p.nb;
+	k4_graph(p, nullptr, false, nullptr, &v);
+	*n_removed = v.n_removed;
+	if (n_blocks) *n_blocks = p.nb;
+	if (counts) { counts->n_blocks = nb_before; counts->n_nodes = v.n_nodes; counts->n_edges = v.n_edges; counts->n_rows = p.m; counts->label_total = v.label_total; }
+	p.dev.resolve();
+	if (v.n_removed == 0) drop_aux(ctx); // the loop is over: give the edge index's memory back
+	FBG_CATCH(ctx)
+	return FBG_OK;
+}
+
 int fbg_device_count(void) {
 	int count = 0;
 	if (cudaGetDeviceCount(&count) != cudaSuccess) { cudaGetLastError(); return 0; }
@@ -473,17 +572,17 @@ int fbg_get_text(fbg_ctx *ctx, uint8_t *out) {
 	return FBG_OK;
 }
 int fbg_get_sa(fbg_ctx *ctx, uint64_t *out) {
-	if (!ctx || !out || !ctx->p.have_index) { if (ctx) ctx->err = "index not built"; return FBG_ERR_ARG; }
+	if (!ctx || !out || !ctx->p.have_index || ctx->p.f_external) { if (ctx) ctx->err = ctx->p.f_external ? "no index of the whole MSA in --heuristic-subset mode" : "index not built"; return FBG_ERR_ARG; }
 	if (int rc = build_index_impl(ctx, true)) return rc;
 	return copy_u32_as_u64(ctx, ctx->p.SA, ctx->p.N, out);
 }
 int fbg_get_isa(fbg_ctx *ctx, uint64_t *out) {
-	if (!ctx || !out || !ctx->p.have_index) { if (ctx) ctx->err = "index not built"; return FBG_ERR_ARG; }
+	if (!ctx || !out || !ctx->p.have_index || ctx->p.f_external) { if (ctx) ctx->err = ctx->p.f_external ? "no index of the whole MSA in --heuristic-subset mode" : "index not built"; return FBG_ERR_ARG; }
 	if (int rc = build_index_impl(ctx, true)) return rc;
 	return copy_u32_as_u64(ctx, ctx->p.ISA, ctx->p.N, out);
 }
 int fbg_get_lcp(fbg_ctx *ctx, uint64_t *out) {
-	if (!ctx || !out || !ctx->p.have_index) { if (ctx) ctx->err = "index not built"; return FBG_ERR_ARG; }
+	if (!ctx || !out || !ctx->p.have_index || ctx->p.f_external) { if (ctx) ctx->err = ctx->p.f_external ? "no index of the whole MSA in --heuristic-subset mode" : "index not built"; return FBG_ERR_ARG; }
 	if (int rc = build_index_impl(ctx, true)) return rc;
 	FBG_TRY(ctx)
 	Pipeline &p = ctx->p;
@@ -507,7 +606,7 @@ int fbg_get_dp(fbg_ctx *ctx, uint64_t *a, uint64_t *b, uint64_t *v) {
 }
 
 int fbg_check_index(fbg_ctx *ctx, uint32_t nsamples, uint64_t seed, uint32_t *n_bad) {
-	if (!ctx || !n_bad || !ctx->p.have_index) { if (ctx) ctx->err = "index not built"; return FBG_ERR_ARG; }
+	if (!ctx || !n_bad || !ctx->p.have_index || ctx->p.f_external) { if (ctx) ctx->err = "index not built"; return FBG_ERR_ARG; }
 	if (int rc = build_index_impl(ctx, true)) return rc;
 	FBG_TRY(ctx)
 	Pipeline &p = ctx->p;

@@ -218,7 +218,7 @@ static void d2h(u64 *dst, const u32 *src, u64 count, u64 *wide, cudaStream_t s) 
 	FBG_CUDA(cudaMemcpyAsync(dst, wide, count * sizeof(u64), cudaMemcpyDeviceToHost, s));
 }
 
-void k4_graph(Pipeline &p, Graph *gp, bool want_node_of, XgfaJob *x) {
+void k4_graph(Pipeline &p, Graph *gp, bool want_node_of, XgfaJob *x, ValidateJob *v) {
 	Dev &d = p.dev;
 	const u64 m = p.m, nb = p.nb, R = m * nb;
 	if (R >= 0xFFFFFFF0ull) throw unsupported_error("more than 2^32 (row,block) records");
@@ -226,7 +226,7 @@ void k4_graph(Pipeline &p, Graph *gp, bool want_node_of, XgfaJob *x) {
 	if (gc.mpad > 8192) throw unsupported_error("more than 8192 rows is not supported by the shared-memory dedup kernel");
 	u64 id_bytes = 0;
 	if (x && x->paths) for (u64 i = 0; i < m; i++) id_bytes += strlen(x->ids[i]);
-	d.ensure(R * 72 + (nb + 1) * 12 + (R / SCAN_TILE + 2) * 24 + (4u << 20) + (x ? k5_scratch_need(m, nb, x->paths, id_bytes) : 0));
+	d.ensure(R * 72 + (nb + 1) * 12 + (R / SCAN_TILE + 2) * 24 + (4u << 20) + (x ? k5_scratch_need(m, nb, x->paths, id_bytes) : 0) + (v ? k6_scratch_need(m, nb) : 0));
 	u64 mk = d.mark();
 	u64 *H1 = d.alloc<u64>(R), *H2 = d.alloc<u64>(R);
 	u32 *LEN = d.alloc<u32>(R), *POS = d.alloc<u32>(R), *REP = d.alloc<u32>(R), *HEAD = d.alloc<u32>(R), *NIDX = d.alloc<u32>(R);
@@ -308,6 +308,14 @@ void k4_graph(Pipeline &p, Graph *gp, bool want_node_of, XgfaJob *x) {
 		gd.heights = heights; gd.node_block = node_block; gd.node_row = node_row; gd.es = es; gd.ed = ed;
 		gd.EOFF = EOFF; gd.node_of = node_of; gd.LEN = LEN; gd.POS = POS; gd.label_total = label_sum;
 		k5_emit_xgfa(p, gd, *x);
+	}
+	if (v) {
+		GraphDev gd;
+		gd.m = m; gd.nb = nb; gd.nn = nn; gd.ne = ne;
+		gd.heights = heights; gd.node_block = node_block; gd.node_row = node_row; gd.es = es; gd.ed = ed;
+		gd.EOFF = EOFF; gd.node_of = node_of; gd.LEN = LEN; gd.POS = POS; gd.label_total = label_sum;
+		v->n_nodes = nn; v->n_edges = ne; v->label_total = label_sum;
+		k6_validate(p, gd, *v);
 	}
 	d.release(mk);
 }

@@ -12,7 +12,11 @@
 //    make_efg.  This tool prints the same statistics and stops with exit 1,
 //    unless the extension flag --nonelastic-gfa is given, in which case it writes the
 //    xGFA of that segmentation with the elastic writer.
-//  * --heuristic-subset (hidden) is validated but not implemented.
+//  * --heuristic-subset=ROWNUM (hidden; fbg.cpp:3400-3433, 3467-3500) needs --elastic --gfa: f(x) from row chunks
+//    (one chunk's index in GPU memory at a time), one DP, then the repair loop; same xGFA bytes as the reference
+//    for m <= 100 rows (beyond that the reference's transpose worker corrupts its own input, fbg.cpp:330-337).
+//    With -p the reference runs into an assertion of its own while writing (fbg.cpp:1421): so does this tool
+//    (message, exit 134, no file).  Always on one GPU.
 //
 // Several GPUs (the reference's counterpart is --threads, fbg.cpp:3390-3399): FBG_GPUS=N (or "all") builds ONE
 // graph on N GPUs of the box.  After the FASTA is parsed -- and before this process touches CUDA -- the tool
@@ -209,7 +213,8 @@ int main(int argc, char **argv) {
 		return EXIT_FAILURE;
 	}
 	if (a.heuristic_subset < -1 || a.heuristic_subset == 0) { fprintf(stderr, "wrong value for --heuristic-subset!\n"); return EXIT_FAILURE; }
-	if (a.heuristic_subset != -1) { fprintf(stderr, "--heuristic-subset is not implemented in the GPU build.\n"); return EXIT_FAILURE; }
+	const bool hs = a.heuristic_subset != -1;
+	if (hs && !(a.elastic && a.gfa)) { fprintf(stderr, "--heuristic-subset is only supported together with --elastic --gfa.\n"); return EXIT_FAILURE; }
 
 	auto start = std::chrono::high_resolution_clock::now();
 	// FBG_TIMING=1: wall-clock per stage on stderr at the end (parse and write are host work)
@@ -223,13 +228,18 @@ int main(int argc, char **argv) {
 	};
 	// the CUDA context takes a few hundred milliseconds to come up: create it while the FASTA is parsed
 	// (one GPU; with several, the ranks are forked after the parse and no CUDA call may come before that)
-	const int world = wanted_gpus();
+	const int world = hs ? 1 : wanted_gpus();
 	fbg_ctx *ctx = nullptr;
 	int ctx_rc = FBG_OK;
 	std::thread ctx_thread([&]() { if (world == 1) ctx_rc = fbg_ctx_create(&ctx, -1); });
 	// read_input (fbg.cpp:151-201): host/fasta_reader.cpp, mapped file, several threads
 	fbg_msa msa;
 	bool opened = fbg_read_fasta(a.input.c_str(), (uint64_t) a.gap_limit, a.elastic, a.paths, 0, &msa) == FBG_OK;
+	if (opened && hs && msa.messages && msa.messages[0]) { // parse_input takes every row or none (fbg.cpp:230-234, 250-254)
+		ctx_thread.join();
+		fprintf(stderr, "MSA rows have mismatching size!\n");
+		return EXIT_FAILURE;
+	}
 	if (opened && msa.messages) fputs(msa.messages, stderr);
 	if (!opened || msa.m == 0 || msa.n == 0) { ctx_thread.join(); fprintf(stderr, "Unable to read sequences from the input\n."); return EXIT_FAILURE; }
 	fprintf(stderr, "Input MSA[1..%llu,1..%llu]\n", (unsigned long long) msa.m, (unsigned long long) msa.n);
@@ -275,12 +285,26 @@ int main(int argc, char **argv) {
 	if (ctx_rc != FBG_OK) return fail_cuda(nullptr, "cannot initialise the GPU");
 	lap("GPU context (rest after the parse)");
 	if (fbg_set_options(ctx, a.elastic, a.gap_limit, (const uint8_t *) a.ignore.data(), a.ignore.size(), a.tricks_off) != FBG_OK) return fail_cuda(ctx, "options");
+	fbg_stats st;
+	if (hs) {
+		// fbg.cpp:3400-3433: f(x) chunk by chunk, the maximum of the chunks' values
+		const uint64_t R = (uint64_t) a.heuristic_subset, nch = (msa.m + R - 1) / R;
+		std::vector<uint64_t> cg(nch), ci(nch);
+		int rc = fbg_heuristic_f(ctx, msa.rows, msa.m, msa.n, R, cg.data(), ci.data());
+		if (rc != FBG_OK) return fail_cuda(ctx, "index construction (row chunks)");
+		for (uint64_t k = 0; k < nch; k++) {
+			fprintf(stderr, "Reading MSA[%llu..%llu]...\n", (unsigned long long) (k * R), (unsigned long long) (k * R + R - 1));
+			fprintf(stderr, "MSA contains %llu gaps.\n", (unsigned long long) cg[k]);
+			fprintf(stderr, "MSA contains %llu characters to ignore for the semi-repeat-free property.\n", (unsigned long long) ci[k]);
+		}
+		fbg_get_stats(ctx, &st);
+		lap("row-chunk indexes + f");
+	} else {
 	if (fbg_upload_msa(ctx, msa.rows, msa.m, msa.n) != FBG_OK) return fail_cuda(ctx, "MSA upload");
 	fprintf(stderr, "Building the MSA index (suffix array, LCP) on the GPU.\n");
 	// index + f(x) in one call: the library then builds only as much of the index as f(x) can
 	// depend on (on gapless input far less than the full SA / ISA / LCP an explicit fbg_build_index gives)
 	if (fbg_compute_f(ctx) != FBG_OK) return fail_cuda(ctx, "index construction");
-	fbg_stats st;
 	fbg_get_stats(ctx, &st);
 	lap("upload + index + f");
 	// the reference reports size_in_mega_bytes(cst) here (fbg.cpp:3380); this build reports the device memory its index
@@ -288,14 +312,17 @@ int main(int argc, char **argv) {
 	fprintf(stderr, "MSA index construction complete, index requires %g MiB.\n", (double) st.arena_peak_bytes / (1024.0 * 1024.0));
 	// fbg.cpp:3396-3399: checked only now, after the index has been built
 	if (a.elastic && !(a.threads == -1 || a.threads > 0)) { fprintf(stderr, "Invalid number of threads.\n"); return EXIT_FAILURE; }
+	}
 
 	uint64_t nb = 0, score = 0;
 	fbg_graph g;
 	memset(&g, 0, sizeof g);
 	std::vector<uint64_t> bnd;
 	if (a.elastic) {
-		fprintf(stderr, "MSA contains %llu gaps.\n", (unsigned long long) st.gaps);
-		fprintf(stderr, "MSA contains %llu characters to ignore for the semi-repeat-free property.\n", (unsigned long long) st.to_ignore);
+		if (!hs) {
+			fprintf(stderr, "MSA contains %llu gaps.\n", (unsigned long long) st.gaps);
+			fprintf(stderr, "MSA contains %llu characters to ignore for the semi-repeat-free property.\n", (unsigned long long) st.to_ignore);
+		}
 		int rc = fbg_segment(ctx, &nb, &score);
 		if (rc == FBG_ERR_NOSEG) { fprintf(stderr, "No valid segmentation found!\n"); return EXIT_FAILURE; }
 		if (rc != FBG_OK) return fail_cuda(ctx, "segmentation");
@@ -314,6 +341,22 @@ int main(int argc, char **argv) {
 	// rank 0 waits until they have (the watchdog above ends the run if one of them failed)
 	if (g_rank) _exit(EXIT_SUCCESS);
 	while (world > 1 && g_kids_done < (sig_atomic_t) kids.size()) usleep(200);
+	if (hs) {
+		// fbg.cpp:3467-3500: merge blocks until every node passes efg_validate
+		int iterations = 0;
+		for (;;) {
+			uint64_t removed = 0, left = 0;
+			fbg_graph gc;
+			iterations++;
+			if (fbg_validate_blocks(ctx, &removed, &left, &gc) != FBG_OK) return fail_cuda(ctx, "graph validation");
+			fprintf(stderr, "#nodes=%llu\ntotal length of node labels=%llu\n#edges=%llu\n", (unsigned long long) gc.n_nodes, (unsigned long long) gc.label_total, (unsigned long long) gc.n_edges);
+			fprintf(stderr, "There are %llu blocks to remove\n", (unsigned long long) removed);
+			nb = left;
+			if (removed == 0) break;
+		}
+		fprintf(stderr, "Graph fixed in %diterations\xE2\x80\xA6\n", iterations - 1);
+		lap("repair loop");
+	}
 	bnd.resize(nb);
 	if (fbg_get_boundaries(ctx, bnd.data()) != FBG_OK) return fail_cuda(ctx, "boundaries");
 	lap("segmentation");
@@ -343,6 +386,10 @@ int main(int argc, char **argv) {
 		}
 	}
 	fprintf(stderr, "Writing the xGFA to disk\xE2\x80\xA6\n");
+	if (hs && a.paths) {
+		fprintf(stderr, "founderblockgraph: boundaries[j] > previndex - 1 failed (the reference's output_efg_external cannot write paths, fbg.cpp:1421)\n");
+		return 134;
+	}
 	if (ids_bad) {
 		fprintf(stderr, "founderblockgraph: identifiers.size() == paths.size() failed (rows were skipped while reading; fbg.cpp:1292)\n");
 		return 134;

@@ -108,6 +108,15 @@ struct XgfaJob {
 	u64 n_nodes = 0, n_edges = 0, label_total = 0, max_height = 0, n_bytes = 0;
 };
 
+struct Pipeline;
+// repair loop of --heuristic-subset (validate.cu): one efg_validate pass on the graph K4 has just built
+struct ValidateJob {
+	Pipeline *aux = nullptr;   // auxiliary pipeline that indexes the edge text (own arenas, own stream)
+	u64 n_removed = 0;         // boundaries dropped by this pass
+	u64 edge_text_len = 0;     // characters of the edge text it indexed
+	u64 n_nodes = 0, n_edges = 0, label_total = 0; // of the graph that was checked ("#nodes=", "total length of node labels=", "#edges=", fbg.cpp:1119-1120,1172)
+};
+
 struct Pipeline {
 	Dev dev;
 	Dist dist;
@@ -143,6 +152,8 @@ struct Pipeline {
 	// no per-position array at all: the sorted list of DISTINCT k-mers with their column and the
 	// LCP to the k-mer before is the whole index ("virtual"; fcol.cu k2_from_dict)
 	bool index_virtual = false, force_arrays = false;
+	// --heuristic-subset (fbg_heuristic_f): f is the maximum over row chunks and there is no index of the whole MSA
+	bool f_external = false;
 	bool no_peer = false; // multi-GPU: the peer-mode attempt of this build was given up, use the key-range form (suffix.cu)
 	u32 *dict_col = nullptr, *dict_lcp = nullptr; // [dict_nd], [dict_nd + 1] in rank order
 	u64 dict_nd = 0;
@@ -163,7 +174,9 @@ void k1_lcp(Pipeline &p);
 void k2_compute_f(Pipeline &p);
 void k3_segment(Pipeline &p);
 // g: host copy of the graph arrays (may be null); x: also format the xGFA on the device (may be null)
-void k4_graph(Pipeline &p, Graph *g, bool want_node_of, XgfaJob *x = nullptr);
+void k4_graph(Pipeline &p, Graph *g, bool want_node_of, XgfaJob *x = nullptr, ValidateJob *v = nullptr);
+void k6_validate(Pipeline &p, const GraphDev &gd, ValidateJob &v);
+u64 k6_scratch_need(u64 m, u64 nb);
 void k5_emit_xgfa(Pipeline &p, const GraphDev &gd, XgfaJob &x);
 // scratch bytes K5 needs on top of K4's (R = m * nb records)
 u64 k5_scratch_need(u64 m, u64 nb, bool paths, u64 id_bytes);

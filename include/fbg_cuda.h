@@ -138,6 +138,23 @@ int fbg_run(fbg_ctx *ctx, const uint8_t *rows_rowmajor, uint64_t m, uint64_t n, 
 int fbg_run_device(fbg_ctx *ctx, const void *device_rows, uint64_t m, uint64_t n, int want_paths,
                    uint64_t *n_blocks, uint64_t *score, fbg_graph *out);
 
+/* ---- --heuristic-subset=ROWNUM (hidden option of the reference: memory relief at the price of optimality).
+ * fbg_heuristic_f replaces the row-chunk loop of main() and its workers (fbg.cpp:3400-3433, 2158-2178): for every
+ * chunk of ROWNUM consecutive rows the chunk's own index and f(x) are built (K0..K2, one chunk in device memory at a
+ * time), f = the maximum over the chunks; then the whole MSA is uploaded and packed (no index of it is ever built)
+ * and f installed, so that fbg_segment -> fbg_validate_blocks (until nothing is removed) -> fbg_build_graph /
+ * fbg_format_xgfa follow.  Elastic options only.  chunk_gaps / chunk_ignore (may be NULL, else ceil(m / rownum)
+ * entries) receive the two "MSA contains ..." counts the reference prints per chunk (fbg.cpp:1858-1859).
+ * fbg_validate_blocks replaces ONE iteration of the repair loop (fbg.cpp:3467-3500: make_efg_external +
+ * efg_validate 3199-3292): a node that is neither source nor sink, and holds no ignore character, is invalid when
+ * its label occurs in an edge string label(u)label(v) anywhere but at the start of u or v with that node in its
+ * own block; every block holding an invalid node is merged with its predecessor.  The edge strings are indexed by
+ * the same suffix sorter as the MSA.  *n_removed = boundaries dropped in this pass, *n_blocks = blocks left; counts
+ * (may be NULL) = scalar fields of the graph that was checked ("#nodes=", "total length of node labels=",
+ * "#edges=", fbg.cpp:1119-1120, 1172).  Call until *n_removed == 0. */
+int fbg_heuristic_f(fbg_ctx *ctx, const uint8_t *rows_rowmajor, uint64_t m, uint64_t n, uint64_t rownum, uint64_t *chunk_gaps, uint64_t *chunk_ignore);
+int fbg_validate_blocks(fbg_ctx *ctx, uint64_t *n_removed, uint64_t *n_blocks, fbg_graph *counts);
+
 /* ---- one MSA across the GPUs of a box (new: the reference is single-process; its only
  * parallelism is std::thread over column ranges, fbg.cpp:2278-2289).  One process per GPU;
  * every process uploads the same MSA and makes the same calls.  Suffix sorting is sharded by

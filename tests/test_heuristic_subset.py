@@ -58,3 +58,42 @@ def test_oracle_heuristic_subset_matches_reference(c, tmp_path):
     p = str(tmp_path / "o.xgfa")
     O.write_xgfa(p, msa, b)
     assert open(p, "rb").read() == c["xgfa"]
+
+
+# ------------------------------------------------------------------------------- GPU
+@pytest.mark.gpu
+@pytest.mark.parametrize("c", OK_CASES, ids=cid)
+def test_gpu_heuristic_subset_matches_reference(gpu_ctx, c):
+    msa = load(c)
+    o = opts(c)
+    gpu_ctx.set_options(elastic=True, gap_limit=1, ignore_chars=o["ignore"], disable_tricks=o["tricks_off"])
+    b, removed, score, f = gpu_ctx.heuristic_subset(msa, c["hs"])
+    assert removed == c["removed"] and score == c["score"]
+    # f is the maximum over the row chunks of the chunk's own f
+    f_ref = np.zeros(msa.shape[1], np.uint64)
+    for r0 in range(0, msa.shape[0], c["hs"]):
+        f_ref = np.maximum(f_ref, O.compute_f(np.ascontiguousarray(msa[r0: r0 + c["hs"]]), o["ignore"], o["tricks_off"]))
+    assert np.array_equal(f, f_ref)
+    assert gpu_ctx.xgfa_bytes() == c["xgfa"]
+    # there is no index of the whole MSA in this mode, and the library says so
+    import founderblockgraphs_b200 as pkg
+    with pytest.raises(pkg.api.FbgError):
+        gpu_ctx.sa()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("c", [c for c in CASES if c["fixture"] in ("hs_rep_10x150.fasta", "hs_rep_gapsN_12x200.fasta", "hs_rep_40x300.fasta", "msa.fasta")
+                               and c["hs"] in (2, 5)], ids=cid)
+def test_cli_heuristic_subset_matches_reference(c, tmp_path):
+    import re
+    import founderblockgraphs_b200 as pkg
+    out = str(tmp_path / "o.xgfa")
+    pr = pkg.api.main(["--input", os.path.join(FIXTURES, c["fixture"]), "--output", out] + c["flags"], capture_output=True, timeout=300)
+    err = pr.stderr.decode()
+    if c["exit"] != 0:  # -p: the reference dies of its own assertion while writing (fbg.cpp:1421)
+        assert pr.returncode == 134 and not os.path.exists(out)
+        return
+    assert pr.returncode == 0, err[-2000:]
+    assert open(out, "rb").read() == c["xgfa"]
+    assert [int(x) for x in re.findall(r"There are (\d+) blocks to remove", err)] == c["removed"]
+    assert "(optimal segment length = %d)" % c["score"] in err and "Graph fixed in %diterations" % (len(c["removed"]) - 1) in err
