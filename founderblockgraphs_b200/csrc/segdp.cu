@@ -190,6 +190,22 @@ __global__ void __launch_bounds__(256) k3_elastic_verify_kernel(const u32 *__res
 
 // per chunk c: q[c] = min of the local values in the w columns up to the next chunk's last
 // source (the plateau the next chunk starts from); then B[c] = max_{c' < c} q[c'] (B[0] = 0).
+// One WAVE of the whole-range DP: column j only reads columns x < U[j] (U is monotone, U[j] <= j), so once
+// the columns below j0 are final, every column with U[j] <= j0 can be computed at once, one warp each.  With
+// long blocks (cfg3: no admissible block under ~1400 columns) the whole DP is a few dozen such waves spread
+// over all SMs instead of one CTA walking 100 000 columns (17 ms -> about 1 ms).  val is read and written
+// in place: reads go to columns < j0, writes to columns >= j0.
+__global__ void __launch_bounds__(256) k3_elastic_wave_kernel(const u32 *__restrict__ f, const u32 *__restrict__ U, u64 n, u32 *val, u32 *__restrict__ bt, u64 j0, u64 j1) {
+	const u64 j = (((u64) blockIdx.x * blockDim.x + threadIdx.x) >> 5) + j0;
+	if (j >= j1) return;
+	u32 best, bx;
+	elastic_scan(j, U[j], 0, (u32) n, [&](u64 x) { return f[x]; }, [&](u64 x) { return val[x]; }, best, bx);
+	if (lane_id() == 0) {
+		if (bx == U32_MAX) best = (u32) n + 1;
+		val[j] = best; bt[j] = bx;
+	}
+}
+
 __global__ void __launch_bounds__(1024) k3_plateau_kernel(const u32 *__restrict__ loc, u64 n_cols, u64 C, u64 H, u64 wq, u32 nchunks, u32 limit, bool nonelastic, u32 *__restrict__ B) {
 	__shared__ u32 sm[32];
 	u32 carry = 0;
@@ -513,6 +529,31 @@ static void dp_solve(Pipeline &p, bool elastic, const u32 *U_or_v, u32 *val, u32
 	u32 *flags = reinterpret_cast<u32 *>(p.scalars + 26); // [0] warm-up lost, [1] changes of the last pass
 	u32 *h_flags = reinterpret_cast<u32 *>(p.h_scalars + 26);
 	auto whole = [&]() {
+		if (elastic && !getenv("FBG_DP_NO_WAVES")) {
+			// waves of mutually independent columns (k3_elastic_wave_kernel), if they come out wide
+			std::vector<u32> hu(n + 1);
+			FBG_CUDA(cudaMemcpyAsync(hu.data(), U_or_v, (n + 1) * sizeof(u32), cudaMemcpyDeviceToHost, d.stream));
+			FBG_CUDA(cudaStreamSynchronize(d.stream));
+			std::vector<u64> cuts; // wave k = columns [cuts[k], cuts[k+1]) of 1..n
+			u64 j0 = 1;
+			while (j0 <= n && cuts.size() <= 4096) {
+				cuts.push_back(j0);
+				u64 lo = j0 + 1, hi = n + 1; // first j > j0 with U[j] > j0
+				while (lo < hi) { const u64 mid = (lo + hi) >> 1; if (hu[mid] > j0) hi = mid; else lo = mid + 1; }
+				j0 = lo;
+			}
+			if (j0 > n && (cuts.size() * 64 <= n || getenv("FBG_DP_WAVES"))) { // (the variable: test hook, waves on small inputs too)
+				cuts.push_back(n + 1);
+				FBG_CUDA(cudaMemsetAsync(val, 0, sizeof(u32), d.stream)); // mml[0] = 0
+				FBG_CUDA(cudaMemsetAsync(ptr, 0, sizeof(u32), d.stream));
+				for (size_t k = 0; k + 1 < cuts.size(); k++)
+					k3_elastic_wave_kernel<<<div_up((cuts[k + 1] - cuts[k]) * 32, 256), 256, 0, d.stream>>>(p.f, U_or_v, n, val, ptr, cuts[k], cuts[k + 1]);
+				FBG_LAUNCH_CHECK();
+				d.note_launches(K_DP, cuts.size() - 1);
+				if (debug) fprintf(stderr, "[fbg] K3 whole-range DP in %zu waves of independent columns\n", cuts.size() - 1);
+				return;
+			}
+		}
 		if (elastic) k3_elastic_dp_kernel<<<1, DPW * 32, 0, d.stream>>>(p.f, U_or_v, n, ncols + 1, 0, 0u, val, ptr, flags);
 		else k3_nonelastic_dp_kernel<<<1, DPW * 32, 0, d.stream>>>(U_or_v, n, ncols + 1, 0, 0u, val, ptr, flags);
 		FBG_LAUNCH_CHECK();
