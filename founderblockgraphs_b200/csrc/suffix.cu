@@ -447,6 +447,28 @@ __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc) {
 	const u32 d = (u32) __cvta_generic_to_shared(smem_dst);
 	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
 }
+// 1-D bulk copy global -> shared through the TMA unit (cp.async.bulk, SASS UBLKCP): issued by ONE thread, no per-thread
+// address arithmetic; completion is counted in bytes on an mbarrier.  Addresses and size are multiples of 16.
+__device__ __forceinline__ void mbar_init(u64 *bar, u32 count) {
+	const u32 a = (u32) __cvta_generic_to_shared(bar);
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(a), "r"(count) : "memory");
+	asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(u64 *bar, u32 bytes) {
+	const u32 a = (u32) __cvta_generic_to_shared(bar);
+	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(a), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, u32 bytes, u64 *bar) {
+	const u32 d = (u32) __cvta_generic_to_shared(smem_dst), a = (u32) __cvta_generic_to_shared(bar);
+	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(d), "l"(gsrc), "r"(bytes), "r"(a) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(u64 *bar, u32 parity) {
+	const u32 a = (u32) __cvta_generic_to_shared(bar);
+	u32 ok;
+	do {
+		asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }" : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+	} while (!ok);
+}
 __device__ __forceinline__ void cp_async_wait_all() {
 	asm volatile("cp.async.commit_group;" ::: "memory");
 	asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -501,15 +523,24 @@ k1_tile_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, cons
 		}
 	}
 	if (STAGE) {
-		// the tile length is a multiple of four elements, so window and lists are 16-byte aligned
+		// The three windows come in by bulk copies (TMA unit): one thread names source, destination and size, the
+		// other 255 issue nothing (the per-thread cp.async form spent 13 % of the kernel's instructions here).
+		// The tile length is a multiple of four elements, so window and lists are 16-byte aligned; the last
+		// window of a list may end off a multiple of 16 bytes: those (at most three) elements are copied by hand.
+		__shared__ __align__(8) u64 s_bar;
 		const u32 nq = wlen >> 2;
-		for (u32 q = tid; q < nq; q += THREADS) {
-			cp_async16(lrs + 4 + 4 * q, lr + w0 + 4 * q); cp_async16(r2s + 4 * q, r2 + w0 + 4 * q); cp_async16(lps + 4 * q, lp + w0 + 4 * q);
+		if (tid == 0) mbar_init(&s_bar, 1);
+		__syncthreads();
+		if (tid == 0 && nq) {
+			mbar_expect_tx(&s_bar, 3 * 16 * nq);
+			bulk_g2s(lrs + 4, lr + w0, 16 * nq, &s_bar);
+			bulk_g2s(r2s, r2 + w0, 16 * nq, &s_bar);
+			bulk_g2s(lps, lp + w0, 16 * nq, &s_bar);
 		}
 		const u32 idx = 4 * nq + tid;
-		if (idx < wlen) { cp_async4(lrs + 4 + idx, lr + w0 + idx); cp_async4(r2s + idx, r2 + w0 + idx); cp_async4(lps + idx, lp + w0 + idx); }
-		if (tid == 32 && w0 > 0) cp_async4(lrs + 3, lr + w0 - 1);
-		cp_async_wait_all();
+		if (idx < wlen) { lrs[4 + idx] = lr[w0 + idx]; r2s[idx] = r2[w0 + idx]; lps[idx] = lp[w0 + idx]; }
+		if (tid == 32 && w0 > 0) lrs[3] = lr[w0 - 1];
+		if (nq) mbar_wait(&s_bar, 0);
 	}
 	__syncthreads();
 
