@@ -169,9 +169,11 @@ template <int MODE> __global__ void __launch_bounds__(KM_THREADS) k1_kmer_kernel
 		for (int it = 0; it < KM_ITEMS; it++) {
 			if (g0 + it < N && sl[it] != U32_MAX) {
 				if (!full) { dk.slot_of[g0 + it] = sl[it]; dk.ord_of[g0 + it] = od[it]; }
-				// smallest member of the bucket: it orders the S list by text position (a reduction
-				// without a return value, so nothing waits for it)
-				atomicMin(dk.first + sl[it], (u32) (g0 + it));
+				// one small member of the bucket orders the S / M lists by text position and stands for the bucket's
+				// column(s) where any member will do: the minimum over the first 16 arrivals (CTAs run roughly in text
+				// order, so that is the true minimum or close to it; an atomicMin for EVERY position cost 5 ms on cfg3,
+				// the first arrival alone gave a worse layout and lost the 5 ms again in the sorters)
+				if (od[it] < 16) atomicMin(dk.first + sl[it], (u32) (g0 + it));
 			}
 		}
 	}
