@@ -72,12 +72,28 @@ void Pipeline::free_all() {
 
 static const char *KNAMES[K_COUNT] = {"pack", "kmer", "radix_hist", "radix_scatter", "scan", "doubling_aux", "lcp", "fcol", "dp", "graph", "tile_sort", "comm", "emit", "edges"};
 
+// A stage that throws leaves its scratch allocations on the bump arena and possibly an open timing record: put the
+// context back into the state every entry point expects (scratch empty, nothing in flight), so that the caller can
+// go on using it -- upload another MSA, change the options -- after an error.  The per-MSA arrays stay; whatever the
+// failed stage was producing is simply not marked as present.
+static void recover_after_error(fbg_ctx *ctx) {
+	for (Pipeline *q : {&ctx->p, ctx->aux}) {
+		if (!q) continue;
+		if (q->dev.stream) cudaStreamSynchronize(q->dev.stream);
+		q->dev.arena_top = 0;
+		q->dev.open_id = -1;
+		for (auto &r : q->dev.recs) { q->dev.pool.push_back(r.a); q->dev.pool.push_back(r.b); }
+		q->dev.recs.clear();
+	}
+	cudaGetLastError();
+}
+
 #define FBG_TRY(ctx) try {
 #define FBG_CATCH(ctx)                                                         \
 	}                                                                          \
-	catch (const fbg::unsupported_error &e) { (ctx)->err = e.what(); return FBG_ERR_UNSUPPORTED; } \
-	catch (const fbg::cuda_error &e) { (ctx)->err = e.what(); cudaGetLastError(); return FBG_ERR_CUDA; } \
-	catch (const std::exception &e) { (ctx)->err = e.what(); return FBG_ERR_CUDA; }
+	catch (const fbg::unsupported_error &e) { (ctx)->err = e.what(); recover_after_error(ctx); return FBG_ERR_UNSUPPORTED; } \
+	catch (const fbg::cuda_error &e) { (ctx)->err = e.what(); recover_after_error(ctx); return FBG_ERR_CUDA; } \
+	catch (const std::exception &e) { (ctx)->err = e.what(); recover_after_error(ctx); return FBG_ERR_CUDA; }
 
 extern "C" {
 

@@ -823,45 +823,19 @@ __global__ void k1_active_total_kernel(const u64 *cnt, u64 *tot) {
 //           ballots, ranks / classes / outputs of the minority.
 // Per element: 8 B (lr, r2) + 8 B (r2 again, mostly from L2, lp) read, 9 B written, 4 B rank scatter, and
 // about a tenth of the instructions of the window kernel.
-//
-// Rank-window form of the minority (later rounds).  From depth ~ 300 on, a third to a half of a bucket differs
-// from the pivot and a 4096-key network was half of the kernel's instructions.  The r2 of nearly all of these
-// elements are ranks inside ONE earlier bucket -- the rows of the column h characters on -- i.e. they lie within a
-// few thousand ranks of the pivot.  When the minority is larger than `win_min`, the elements with
-// r2 in [lo, lo + BS_WBINS), lo = pivot - BS_WBINS / 2, are therefore COUNTED instead of compared: pass B adds one
-// to the 16-bit counter of bin r2 - lo (shared-memory atomics, two counters per word) and keeps (bin, index in
-// bucket) in 4 bytes; an exclusive scan of the counters gives every bin -- every sub-bucket -- its head, and each
-// element takes a slot of its sub-bucket by decrementing the counter (the order inside a sub-bucket that stays
-// tied is free).  Only the elements outside the window (rows that had a gap or a second difference on the way;
-// at most BS_OCAP, else the whole minority goes through the network as before) are sorted by the network; they
-// lie below or above every element of the window.
 constexpr int BS_THREADS = 512;
 constexpr int BS_TILE = 2048;
 constexpr int BS_CH = BS_THREADS * 4;   // elements per streaming step
 constexpr int BS_MAXHEADS = 32;         // bucket heads per BS_TILE slots (2 when every bucket has >= MID_MIN elements)
-constexpr u32 BS_WBINS = 8192;          // ranks covered by the window
-constexpr u32 BS_OCAP = 1024;           // keys of the network when the window is in use
-constexpr u32 BS_WIN_MIN = 256;         // smallest minority that is counted (below: the network is cheaper than the scan of the bins)
-// shared memory: network form  key u64[BSMALL] @0;  window form  key u64[BS_OCAP] @0, wrec u32[BSMALL], cw u32[BS_WBINS / 2],
-// ex u16[BS_WBINS + 2];  both: bal (one ballot word per 32 sorted keys) at the end
-constexpr size_t BS_OFF_WREC = (size_t) BS_OCAP * 8;
-constexpr size_t BS_OFF_CW = BS_OFF_WREC + (size_t) BSMALL * 4;
-constexpr size_t BS_OFF_EX = BS_OFF_CW + (size_t) BS_WBINS * 2;
-constexpr size_t BS_OFF_BAL = (BS_OFF_EX + ((size_t) BS_WBINS + 2) * 2 + 7) / 8 * 8;
-constexpr size_t BS_SMEM = BS_OFF_BAL + ((size_t) BSMALL / 32 + 1) * 4;
-static_assert(BS_OFF_BAL >= (size_t) BSMALL * 8, "the network form needs BSMALL keys in front of the ballot words");
-static_assert(BS_WBINS / 2 == BS_THREADS * 8 && BSMALL <= 8192, "bin scan: eight counter words per thread; 13-bit indices");
+constexpr size_t BS_SMEM = (size_t) BSMALL * 8 + ((size_t) BSMALL / 32 + 1) * 4;
 
 __global__ void __launch_bounds__(BS_THREADS, 3)
-k1_bucket_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, const u32 *__restrict__ r2, u64 na, u32 mid_min, u32 win_min,
+k1_bucket_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, const u32 *__restrict__ r2, u64 na, u32 mid_min,
                       u32 *__restrict__ R, SaOut so, u32 *__restrict__ lp_out, u32 *__restrict__ lr_out, u8 *__restrict__ cls_out, u32 *__restrict__ scal) {
 	extern __shared__ __align__(16) unsigned char bs_raw[];
 	u64 *key = reinterpret_cast<u64 *>(bs_raw);
-	u32 *wrec = reinterpret_cast<u32 *>(bs_raw + BS_OFF_WREC);
-	u32 *cw = reinterpret_cast<u32 *>(bs_raw + BS_OFF_CW);
-	unsigned short *ex = reinterpret_cast<unsigned short *>(bs_raw + BS_OFF_EX);
-	u32 *bal = reinterpret_cast<u32 *>(bs_raw + BS_OFF_BAL);
-	__shared__ u32 s_heads[BS_MAXHEADS], s_nheads, s_red[3][BS_THREADS / 32], s_cnt[4 * (BS_THREADS / 32)], s_pre[4 * (BS_THREADS / 32)], s_tot, s_nw;
+	u32 *bal = reinterpret_cast<u32 *>(bs_raw + (size_t) BSMALL * 8);
+	__shared__ u32 s_heads[BS_MAXHEADS], s_nheads, s_red[3][BS_THREADS / 32], s_cnt[4 * (BS_THREADS / 32)], s_pre[4 * (BS_THREADS / 32)], s_tot;
 	constexpr u32 NW = BS_THREADS / 32;
 	const u32 tid = threadIdx.x, w = tid >> 5, l = tid & 31;
 	const u64 w0 = (u64) blockIdx.x * BS_TILE;
@@ -900,8 +874,7 @@ k1_bucket_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, co
 			const u32 pa = r2[h], pb = tb < na ? r2[tb] : pa, pc = tc < na ? r2[tc] : pa;
 			pv = pb == pc ? pb : pa;
 		}
-		const u32 lo = pv > BS_WBINS / 2 ? pv - BS_WBINS / 2 : 0u, pbin = pv - lo;
-		// pass A (nl, ng: below / above the pivot in the low half, of these outside the window in the high half)
+		// pass A
 		u32 cnt = 0, nl = 0, ng = 0;
 		bool broken = false;
 		for (u32 c0 = 0;; c0 += BS_CH) {
@@ -917,8 +890,7 @@ k1_bucket_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, co
 			for (int j = 0; j < 4; j++) {
 				const u64 t = h + c0 + (u32) j * BS_THREADS + tid;
 				const bool in = t < na && a[j] == lrh;
-				const u32 far = (b[j] - lo >= BS_WBINS) ? 0x10001u : 1u;
-				cnt += in ? 1u : 0u; nl += (in && b[j] < pv) ? far : 0u; ng += (in && b[j] > pv) ? far : 0u;
+				cnt += in ? 1u : 0u; nl += (in && b[j] < pv) ? 1u : 0u; ng += (in && b[j] > pv) ? 1u : 0u;
 				all_in = all_in && in;
 			}
 			if (!__syncthreads_and(all_in ? 1 : 0)) break;
@@ -932,17 +904,7 @@ k1_bucket_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, co
 #pragma unroll
 		for (u32 ww = 0; ww < NW; ww++) { size += s_red[0][ww]; nless += s_red[1][ww]; ngr += s_red[2][ww]; }
 		if (size > BSMALL) { if (tid == 0) scal[1] = 1u; return; }
-		u32 n_ol = nless >> 16, n_oh = ngr >> 16; // outside the window, below / above it
-		nless &= 0xFFFFu; ngr &= 0xFFFFu;
 		const u32 nmin = nless + ngr, neq = size - nmin;
-		const bool win = nmin > win_min && n_ol + n_oh <= BS_OCAP;
-		if (!win) { n_ol = nless; n_oh = ngr; } // everything through the network
-		const u32 n_net = n_ol + n_oh, n_win = nmin - n_net;
-		if (win) {
-#pragma unroll
-			for (int j = 0; j < 8; j++) cw[(u32) j * BS_THREADS + tid] = 0u;
-			if (tid == 0) s_nw = 0u;
-		}
 		const u32 cls_eq = neq == 1 ? CLS_DROP : (neq < mid_min ? CLS_SMALL : CLS_MID);
 		const u32 req = lrh + nless; // rank of the elements equal to the pivot
 		if (cls_eq == CLS_SMALL) mx = neq > mx ? neq : mx;
@@ -962,7 +924,7 @@ k1_bucket_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, co
 				const u32 q = c0 + (u32) j * BS_THREADS + tid;
 				const bool in = q < size;
 				be[j] = __ballot_sync(0xffffffffu, in && rv[j] == pv);
-				bm[j] = __ballot_sync(0xffffffffu, in && rv[j] != pv && (!win || rv[j] - lo >= BS_WBINS)); // keys of the network
+				bm[j] = __ballot_sync(0xffffffffu, in && rv[j] != pv);
 				if (l == 0) s_cnt[j * NW + w] = (u32) __popc(be[j]) | ((u32) __popc(bm[j]) << 16);
 			}
 			__syncthreads();
@@ -983,68 +945,33 @@ k1_bucket_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, co
 						lp_out[out] = pp[j]; lr_out[out] = req; cls_out[out] = (u8) cls_eq;
 						if (nless) R[pp[j]] = req;
 						if (neq == 1) so.put(req, pp[j]);
-					} else if (!win || rv[j] - lo >= BS_WBINS) {
+					} else {
 						const u32 mp = mn_run + (pre >> 16) + (u32) __popc(bm[j] & lanemask_lt());
 						key[ts_sw(mp)] = ((u64) (rv[j] > pv ? 1u : 0u) << 45) | ((u64) rv[j] << 13) | (u64) q;
-					}
-				}
-				if (win) { // elements of the window: count their bin, keep (bin, index in bucket)
-					const bool iw = q < size && rv[j] != pv && rv[j] - lo < BS_WBINS;
-					const u32 bw = __ballot_sync(0xffffffffu, iw);
-					if (bw) {
-						u32 base = 0;
-						if (l == (u32) __ffs(bw) - 1u) base = atomicAdd(&s_nw, (u32) __popc(bw));
-						base = __shfl_sync(0xffffffffu, base, __ffs(bw) - 1);
-						if (iw) {
-							const u32 bin = rv[j] - lo;
-							atomicAdd(&cw[bin >> 1], 1u << ((bin & 1u) << 4));
-							wrec[base + (u32) __popc(bw & lanemask_lt())] = (bin << 13) | q;
-						}
 					}
 				}
 			}
 			const u32 tot = s_tot;
 			eq_run += tot & 0xFFFFu; mn_run += tot >> 16;
 		}
-		if (win) { // exclusive scan of the bin counters -> head of every sub-bucket of the window
-			__syncthreads();
-			const uint4 c0 = reinterpret_cast<const uint4 *>(cw)[2 * tid], c1 = reinterpret_cast<const uint4 *>(cw)[2 * tid + 1];
-			const u32 wv[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
-			u32 sum = 0;
-#pragma unroll
-			for (int j = 0; j < 8; j++) sum += (wv[j] & 0xFFFFu) + (wv[j] >> 16);
-			const u32 inc = warp_incl_sum(sum);
-			if (l == 31) s_red[0][w] = inc;
-			__syncthreads();
-			u32 run = inc - sum;
-			for (u32 ww = 0; ww < w; ww++) run += s_red[0][ww];
-			u32 *ex2 = reinterpret_cast<u32 *>(ex) + 8 * tid; // two 16-bit heads per word
-#pragma unroll
-			for (int j = 0; j < 8; j++) {
-				const u32 e0 = run, e1 = run + (wv[j] & 0xFFFFu);
-				run = e1 + (wv[j] >> 16);
-				ex2[j] = e0 | (e1 << 16);
-			}
-			if (tid == BS_THREADS - 1) ex[BS_WBINS] = (unsigned short) run;
-		}
-		if (n_net) {
+		if (nmin) {
 			u32 net = 32;
-			while (net < n_net) net <<= 1;
-			for (u32 slot = n_net + tid; slot < net; slot += BS_THREADS) key[ts_sw(slot)] = ~0ull;
+			while (net < nmin) net <<= 1;
+			for (u32 slot = nmin + tid; slot < net; slot += BS_THREADS) key[ts_sw(slot)] = ~0ull;
 			__syncthreads();
 			tile_bitonic_sort_rt<BS_THREADS>(key, net);
-			// sub-bucket heads of the sorted keys, one ballot word per 32 slots
-			for (u32 s0 = 0; s0 < n_net; s0 += BS_THREADS) {
+			// sub-bucket heads of the sorted minority, one ballot word per 32 slots
+			for (u32 s0 = 0; s0 < nmin; s0 += BS_THREADS) {
 				const u32 sx = s0 + tid;
-				const bool hd = sx < n_net && (sx == 0 || (key[ts_sw(sx)] >> 13) != (key[ts_sw(sx - 1)] >> 13));
+				const bool hd = sx < nmin && (sx == 0 || (key[ts_sw(sx)] >> 13) != (key[ts_sw(sx - 1)] >> 13));
 				const u32 bw = __ballot_sync(0xffffffffu, hd);
-				if (l == 0 && sx < n_net) bal[sx >> 5] = bw;
+				if (l == 0 && sx < nmin) bal[sx >> 5] = bw;
 			}
 			__syncthreads();
-			const u32 ngrp = (n_net + 31) >> 5;
-			for (u32 s0 = 0; s0 < n_net; s0 += BS_THREADS) {
+			const u32 ngrp = (nmin + 31) >> 5;
+			for (u32 s0 = 0; s0 < nmin; s0 += BS_THREADS) {
 				const u32 sx = s0 + tid;
-				if (sx < n_net) {
+				if (sx < nmin) {
 					const u64 k = key[ts_sw(sx)];
 					const u32 g = sx >> 5, bi = sx & 31;
 					u32 m1 = bal[g] & (0xFFFFFFFFu >> (31 - bi)), g1 = g;
@@ -1052,37 +979,18 @@ k1_bucket_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, co
 					const u32 hs = g1 * 32 + 31 - (u32) __clz(m1);  // head of my sub-bucket
 					u32 m2 = bi == 31 ? 0u : (bal[g] & (0xFFFFFFFFu << (bi + 1))), g2 = g;
 					while (m2 == 0 && ++g2 < ngrp) m2 = bal[g2];
-					const u32 he = m2 ? g2 * 32 + (u32) __ffs(m2) - 1 : n_net; // head of the next one
+					const u32 he = m2 ? g2 * 32 + (u32) __ffs(m2) - 1 : nmin; // head of the next one
 					const u32 sz = he - hs;
 					const bool gt = (k >> 45) & 1ull;
 					const u32 p = lp[h + ((u32) k & (BSMALL - 1))];
-					const u32 sh = gt ? neq + n_win : 0u; // the keys above the window follow the pivot's elements and the window
-					const u64 out = h + sh + sx;
-					const u32 nr = lrh + sh + hs;
+					const u64 out = h + (gt ? neq : 0u) + sx;
+					const u32 nr = lrh + (gt ? neq : 0u) + hs;
 					const u32 c = sz == 1 ? CLS_DROP : (sz < mid_min ? CLS_SMALL : CLS_MID);
 					if (nr != lrh) R[p] = nr;
 					if (sz == 1) so.put(nr, p);
 					lp_out[out] = p; lr_out[out] = nr; cls_out[out] = (u8) c;
 					if (c == CLS_SMALL && sx == hs) mx = sz > mx ? sz : mx;
 				}
-			}
-		}
-		if (win) {
-			__syncthreads(); // heads of the bins written
-			for (u32 i = tid; i < n_win; i += BS_THREADS) {
-				const u32 rec = wrec[i], bin = rec >> 13, q = rec & (BSMALL - 1);
-				const u32 hsft = (bin & 1u) << 4;
-				const u32 arr = ((atomicSub(&cw[bin >> 1], 1u << hsft) >> hsft) & 0xFFFFu) - 1u; // my slot in the sub-bucket
-				const u32 e0 = ex[bin], sz = (u32) ex[bin + 1] - e0;
-				const u32 off = n_ol + e0 + (bin > pbin ? neq : 0u);
-				const u32 p = lp[h + q];
-				const u32 nr = lrh + off;
-				const u32 c = sz == 1 ? CLS_DROP : (sz < mid_min ? CLS_SMALL : CLS_MID);
-				if (nr != lrh) R[p] = nr;
-				if (sz == 1) so.put(nr, p);
-				const u64 out = h + off + arr;
-				lp_out[out] = p; lr_out[out] = nr; cls_out[out] = (u8) c;
-				if (c == CLS_SMALL && arr == 0) mx = sz > mx ? sz : mx;
 			}
 		}
 		__syncthreads(); // key, bal and the counters are used again by the next bucket
@@ -1093,12 +1001,8 @@ k1_bucket_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, co
 
 static void launch_bucket_sort(Dev &d, const u32 *lp, const u32 *lr, const u32 *r2, u64 na, u32 mid_min,
                                u32 *R, SaOut SA, u32 *lp_out, u32 *lr_out, u8 *cls_out, u32 *scal) {
-	static const u32 win_min = [] { // FBG_BS_WIN_MIN: test hook (0: every minority through the rank window; above BSMALL: never)
-		const char *e = getenv("FBG_BS_WIN_MIN");
-		return e ? (u32) strtoul(e, nullptr, 10) : BS_WIN_MIN;
-	}();
 	FBG_CUDA(cudaFuncSetAttribute(k1_bucket_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) BS_SMEM));
-	k1_bucket_sort_kernel<<<div_up(na, BS_TILE), BS_THREADS, BS_SMEM, d.stream>>>(lp, lr, r2, na, mid_min, win_min, R, SA, lp_out, lr_out, cls_out, scal);
+	k1_bucket_sort_kernel<<<div_up(na, BS_TILE), BS_THREADS, BS_SMEM, d.stream>>>(lp, lr, r2, na, mid_min, R, SA, lp_out, lr_out, cls_out, scal);
 	FBG_LAUNCH_CHECK();
 }
 
@@ -1837,6 +1741,7 @@ void k1_suffix_array(Pipeline &p) {
 		sc ^= 1;
 		if (h_sc[5] == 0) break; // nothing tied on any GPU
 		if (h >= N) throw cuda_error("prefix doubling did not converge");
+		if (getenv("FBG_TEST_FAIL_K1")) throw cuda_error("FBG_TEST_FAIL_K1: failure injected after the first doubling round (test hook)");
 		hi_shift = nbits;
 		key_bits = 2 * nbits;
 		h *= 2;

@@ -574,3 +574,29 @@ def test_sufficient_index_then_full_index_on_request(gpu_ctx):
     assert ctx.check_index(20000, 3) == 0
     b, score = ctx.segment()
     assert np.array_equal(ctx.get_f(), f) and np.array_equal(f, O.compute_f(msa, b"", False))
+
+
+@pytest.mark.gpu
+def test_context_usable_after_a_failed_stage(gpu_ctx, monkeypatch):
+    """A stage that throws half way (scratch allocated, kernels in flight, a timing record open) must leave the
+    context usable: the next build on it gives the same bytes as before (FBG_TEST_FAIL_K1 injects the failure after
+    the first doubling round of K1; found when an experimental kernel made K1 throw and every later build on that
+    context failed with 'device arena exhausted')."""
+    import founderblockgraphs_b200 as pkg
+    from founderblockgraphs_b200 import synth
+    msa, c = synth.make_config("cfg3", 0.004, seed=31)  # gapped: needs doubling rounds
+    gpu_ctx.set_options(elastic=True, gap_limit=1, ignore_chars=b"")
+    gpu_ctx.upload(msa)
+    f0 = gpu_ctx.compute_f().copy()
+    b0, s0 = gpu_ctx.segment()
+    monkeypatch.setenv("FBG_TEST_FAIL_K1", "1")
+    for _ in range(2):
+        gpu_ctx.upload(msa)
+        with pytest.raises(pkg.api.FbgError, match="FBG_TEST_FAIL_K1"):
+            gpu_ctx.compute_f()
+    monkeypatch.delenv("FBG_TEST_FAIL_K1")
+    for _ in range(2):
+        gpu_ctx.upload(msa)
+        f1 = gpu_ctx.compute_f()
+        b1, s1 = gpu_ctx.segment()
+        assert np.array_equal(f0, f1) and np.array_equal(b0, b1) and s0 == s1
