@@ -33,6 +33,8 @@ struct FcolArgs {
 	u64 x0, x1;    // column range [x0, x1)
 	int tricks_off, has_ignore;
 	int only_marked; // sorting kernel after the cluster kernel: only the columns it left marked
+	const u32 *RC, *AC; // staged form: rank and LCP of row i at column x at [(x - xs0) * m + i] (k2_stage_kernel); null: gathered here
+	u64 xs0;
 	u32 *dbg;        // FBG_DEBUG: [0] columns left marked, by reason: [1] no cluster, [2] too many rows outside, [3] a row next to the window
 };
 
@@ -77,6 +79,42 @@ __device__ __forceinline__ u32 fcol_fi(const FcolArgs &a, u32 i, u32 l, u32 r, u
 		if (ni < fi) fi = ni;
 	}
 	return fi;
+}
+
+// ---- staging: ISA[p_i(x)] and PLCP[p_i(x)] in COLUMN-major order for a slab of columns.
+// The column kernels below need, per column, the rank and the LCP of every row's current suffix: two 4-byte gathers
+// per cell, m different 128-byte lines per column and array.  Along a ROW the same reads are consecutive addresses
+// (p_i(x + 1) = p_i(x) or p_i(x) + 1), so this kernel reads them the cheap way round -- a warp takes one row and the 32
+// columns of one bitmap word: one or two lines per array -- transposes 32 x 32 tiles in shared memory and writes
+// lines of 32 consecutive rows of one column.  16 B per cell of streaming traffic instead of 64 B of sectors fetched
+// through the column kernel's dependent-load chain.  A row that is not evaluated at x (fbg.cpp:1605-1608: no character
+// before the column, tricks on) gets rank U32_MAX.
+__global__ void __launch_bounds__(256) k2_stage_kernel(FcolArgs a, u64 xs0, u64 xs1, u32 *__restrict__ RC, u32 *__restrict__ AC) {
+	__shared__ u32 tr[32][33], ta[32][33];
+	const u32 w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const u64 m = a.m, i0 = (u64) blockIdx.x * 32, t = (xs0 >> 5) + blockIdx.y, x = t * 32 + lane;
+	const u32 below = (1u << lane) - 1u;
+#pragma unroll
+	for (u32 k = 0; k < 4; k++) {
+		const u32 rr = w + 8 * k;
+		const u64 i = i0 + rr;
+		u32 r = U32_MAX, v = 0;
+		if (i < m && x < xs1) {
+			const u32 rk = __ldg(a.RK + t * m + i) + __popc(__ldg(a.NG + t * m + i) & below);
+			if (a.tricks_off || rk > 0) {
+				const u64 p = (u64) __ldg(a.start + i) + rk;
+				r = __ldg(a.ISA + p); v = __ldg(a.PLCP + p);
+			}
+		}
+		tr[rr][lane] = r; ta[rr][lane] = v;
+	}
+	__syncthreads();
+#pragma unroll
+	for (u32 k = 0; k < 4; k++) {
+		const u32 c = w + 8 * k;
+		const u64 xc = t * 32 + c, i = i0 + lane;
+		if (i < m && xc < xs1) { RC[(xc - xs0) * m + i] = tr[lane][c]; AC[(xc - xs0) * m + i] = ta[lane][c]; }
+	}
 }
 
 constexpr u64 FC_CHUNK = 8;           // consecutive columns (column groups) a CTA works through before it moves on
@@ -135,7 +173,10 @@ template <bool CLUSTER> __global__ void __launch_bounds__(1024) k2_fcol_kernel(F
 				u64 kk = KEY_INVALID;
 				if (live && i < m) {
 					u32 rk = a.RK[t * m + i] + __popc(a.NG[t * m + i] & below);
-					if (a.tricks_off || rk > 0) {
+					if (a.RC) {
+						const u32 r = a.RC[(x - a.xs0) * m + i];
+						if (r != U32_MAX) { kk = ((u64) r << 24) | i; A[i] = a.AC[(x - a.xs0) * m + i]; RKS[i] = rk; }
+					} else if (a.tricks_off || rk > 0) {
 						u64 p = (u64) a.start[i] + rk;
 						kk = ((u64) a.ISA[p] << 24) | i;
 						A[i] = a.PLCP[p];
@@ -169,7 +210,8 @@ template <bool CLUSTER> __global__ void __launch_bounds__(1024) k2_fcol_kernel(F
 			for (u32 c = 0; c < 8; c++) {
 				const u32 i = tg + c * tpg;
 				myr[c] = U32_MAX; av[c] = 0;
-				if (live && i < m && (a.tricks_off || rkv[c] > 0)) { pv[c] += rkv[c]; myr[c] = __ldg(a.ISA + pv[c]); av[c] = __ldg(a.PLCP + pv[c]); }
+				if (a.RC) { if (live && i < m) { myr[c] = __ldg(a.RC + (x - a.xs0) * m + i); av[c] = __ldg(a.AC + (x - a.xs0) * m + i); } }
+				else if (live && i < m && (a.tricks_off || rkv[c] > 0)) { pv[c] += rkv[c]; myr[c] = __ldg(a.ISA + pv[c]); av[c] = __ldg(a.PLCP + pv[c]); }
 			}
 #pragma unroll
 			for (u32 c = 0; c < 8; c++) {
@@ -491,6 +533,7 @@ void k2_compute_f(Pipeline &p) {
 	a.tricks_off = p.opt.disable_tricks ? 1 : 0;
 	a.has_ignore = p.opt.n_ignore > 0 ? 1 : 0;
 	a.only_marked = 0;
+	a.RC = nullptr; a.AC = nullptr; a.xs0 = 0;
 	a.dbg = nullptr;
 	const bool debug = getenv("FBG_DEBUG") != nullptr;
 	if (debug) { a.dbg = reinterpret_cast<u32 *>(p.scalars + 40); FBG_CUDA(cudaMemsetAsync(a.dbg, 0, 4 * sizeof(u32), d.stream)); }
@@ -500,28 +543,63 @@ void k2_compute_f(Pipeline &p) {
 	if (col_groups == 0) col_groups = 1;
 	u64 col_chunks = (col_groups + FC_CHUNK - 1) / FC_CHUNK;
 	u64 max_grid = (u64) NUM_SMS * 8;
-	u32 grid = (u32) (col_chunks < max_grid ? col_chunks : max_grid);
-	d.begin(K_FCOL);
+	(void) col_chunks;
 	// many rows: placement by rank instead of a sort (cluster form of the kernel), then the sorting form for the
 	// columns that did not fit; the window needs some room beyond the m ranks of the cluster
 	const bool cluster = mpad >= 2048 && gc.groups == 1 && gc.E == 8 && p.m * 10 <= (u64) mpad * 9 && !getenv("FBG_FCOL_SORT");
-	if (cluster) {
-		const size_t smem_c = (size_t) mpad * 10 + (size_t) FC_OCAP * 8;
-		FBG_CUDA(cudaFuncSetAttribute(k2_fcol_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem_c));
-		k2_fcol_kernel<true><<<grid, threads, smem_c, d.stream>>>(a);
-		a.only_marked = 1;
-		d.note_launches(K_FCOL, 1);
-		if (debug) {
-			u32 h[4];
-			FBG_CUDA(cudaMemcpyAsync(h, a.dbg, sizeof h, cudaMemcpyDeviceToHost, d.stream));
-			FBG_CUDA(cudaStreamSynchronize(d.stream));
-			fprintf(stderr, "[fbg] K2 cluster form: %u of %llu columns left to the sorting form (no cluster %u, > %u rows outside %u, row next to the window %u)\n",
-			        h[0], (unsigned long long) (a.x1 - a.x0), h[1], FC_OCAP, h[2], h[3]);
-		}
+	const size_t smem_c = (size_t) mpad * 10 + (size_t) FC_OCAP * 8;
+	if (cluster) FBG_CUDA(cudaFuncSetAttribute(k2_fcol_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem_c));
+	// Slabs of columns: ranks and LCPs staged column-major (k2_stage_kernel), then the column kernels on the slab.
+	// FBG_FCOL_NO_STAGE=1: the column kernels gather from ISA / PLCP themselves (one slab = the whole range).
+	const bool stage = !getenv("FBG_FCOL_NO_STAGE") && a.x1 > a.x0;
+	u64 slab = a.x1 - a.x0 ? a.x1 - a.x0 : 1;
+	u32 *RC = nullptr, *AC = nullptr;
+	u64 mk = 0;
+	if (stage) {
+		const u64 budget = 1ull << 30; // bytes per staged array
+		slab = budget / (4 * p.m) / 256 * 256;
+		if (slab < 256) slab = 256;
+		if (slab > (1ull << 20)) slab = 1ull << 20; // (grid.y of the staging kernel = slab / 32)
+		if (slab > ((a.x1 - a.x0 + 31) / 32 + 1) * 32) slab = ((a.x1 - a.x0 + 31) / 32 + 1) * 32;
+		d.ensure(2 * (slab * p.m * 4 + 256) + (1u << 20));
+		mk = d.mark();
+		RC = d.alloc<u32>(slab * p.m); AC = d.alloc<u32>(slab * p.m);
 	}
-	k2_fcol_kernel<false><<<grid, threads, smem, d.stream>>>(a);
-	FBG_LAUNCH_CHECK();
-	d.end((double) p.m * (double) (a.x1 - a.x0) * 12.0);
+	const u64 xa = a.x0, xe = a.x1;
+	d.begin(K_FCOL);
+	for (u64 s0 = stage ? (xa & ~31ull) : xa; s0 < xe; s0 += slab) {
+		const u64 s1 = s0 + slab < xe ? s0 + slab : xe;
+		a.x0 = s0 < xa ? xa : s0; a.x1 = s1;
+		a.RC = RC; a.AC = AC; a.xs0 = s0;
+		a.only_marked = 0;
+		if (stage) {
+			dim3 sg((u32) div_up(p.m, 32), (u32) div_up(s1 - s0, 32));
+			k2_stage_kernel<<<sg, 256, 0, d.stream>>>(a, s0, s1, RC, AC);
+			d.note_launches(K_FCOL, 1);
+		}
+		u64 groups_here = (a.x1 - a.x0 + a.groups - 1) / a.groups;
+		u64 chunks_here = (groups_here + FC_CHUNK - 1) / FC_CHUNK;
+		if (chunks_here == 0) chunks_here = 1;
+		const u32 grid_here = (u32) (chunks_here < max_grid ? chunks_here : max_grid);
+		if (cluster) {
+			k2_fcol_kernel<true><<<grid_here, threads, smem_c, d.stream>>>(a);
+			a.only_marked = 1;
+			d.note_launches(K_FCOL, 1);
+		}
+		k2_fcol_kernel<false><<<grid_here, threads, smem, d.stream>>>(a);
+		FBG_LAUNCH_CHECK();
+		if (s1 < xe) d.note_launches(K_FCOL, 1);
+	}
+	a.x0 = xa; a.x1 = xe;
+	if (cluster && debug) {
+		u32 h[4];
+		FBG_CUDA(cudaMemcpyAsync(h, a.dbg, sizeof h, cudaMemcpyDeviceToHost, d.stream));
+		FBG_CUDA(cudaStreamSynchronize(d.stream));
+		fprintf(stderr, "[fbg] K2 cluster form: %u of %llu columns left to the sorting form (no cluster %u, > %u rows outside %u, row next to the window %u)\n",
+		        h[0], (unsigned long long) (a.x1 - a.x0), h[1], FC_OCAP, h[2], h[3]);
+	}
+	d.end((double) p.m * (double) (a.x1 - a.x0) * (stage ? 28.0 : 12.0));
+	if (stage) d.release(mk);
 	if (sharded) {
 		d.begin(K_COMM);
 		p.dist.allreduce_max_u32(p.f, p.n, d.stream);
