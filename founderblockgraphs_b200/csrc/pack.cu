@@ -128,27 +128,45 @@ __global__ void __launch_bounds__(1024) k0_starts_kernel(const u32 *__restrict__
 	if (threadIdx.x == 0) { start[m] = (u32) carry; totals[2] = carry + 1; }
 }
 
-// one thread per (row, 32-column tile): scatter non-gap bytes and their columns
+// one thread per (row, 32-column tile), one warp per 1024 columns of a row: the lanes compact their non-gap bytes and
+// the columns of these into the warp's shared-memory strip at (text position - the warp's first text position),
+// the warp writes the strip out with consecutive lanes on consecutive addresses.  (The first form let every lane
+// write its own 32 bytes / 32 words straight to T and col: 64 store instructions per lane, each touching 32
+// different sectors per warp -- 4.8 ms on cfg3 for 3 GB of traffic.)
 __global__ void __launch_bounds__(256) k0_text_kernel(const u8 *__restrict__ msa, u64 pitch, u64 m, u64 n, u64 W, u64 wb,
                                                       const u32 *__restrict__ RK, const u32 *__restrict__ start, const u32 *__restrict__ rowlen,
                                                       u8 *__restrict__ T, u32 *__restrict__ col, u64 N) {
+	__shared__ u8 sT[8][1024];
+	__shared__ u32 sC[8][1024];
+	const u32 wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	u64 row = blockIdx.x / wb;
 	u64 t = (blockIdx.x % wb) * 256 + threadIdx.x;
-	if (t >= W) return;
-	const u8 *src = msa + row * pitch + t * 32;
-	uint4 a = ld_nc_u4(src), b = ld_nc_u4(src + 16);
-	u32 w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-	u64 p = (u64) start[row] + RK[t * m + row];
-	u64 lim = n - t * 32 < 32 ? n - t * 32 : 32;
+	if (t - lane >= W) return; // the whole warp lies behind the last tile
+	const bool act = t < W;
+	u32 w[8] = {0x2D2D2D2Du, 0x2D2D2D2Du, 0x2D2D2D2Du, 0x2D2D2D2Du, 0x2D2D2D2Du, 0x2D2D2D2Du, 0x2D2D2D2Du, 0x2D2D2D2Du};
+	u64 p = 0;
+	u64 lim = 0;
+	if (act) {
+		const u8 *src = msa + row * pitch + t * 32;
+		uint4 a = ld_nc_u4(src), b = ld_nc_u4(src + 16);
+		w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w; w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
+		p = (u64) start[row] + RK[t * m + row];
+		lim = n - t * 32 < 32 ? n - t * 32 : 32;
+	}
+	const u64 p0 = __shfl_sync(0xffffffffu, p, 0);
+	u32 o = act ? (u32) (p - p0) : 0u;
 #pragma unroll
 	for (int q = 0; q < 8; q++) {
 #pragma unroll
 		for (int s = 0; s < 4; s++) {
 			u32 c = (w[q] >> (8 * s)) & 0xFFu;
 			u32 x = q * 4 + s;
-			if (x < lim && c != 0x2Du) { T[p] = (u8) c; col[p] = (u32) (t * 32) + x; p++; }
+			if (x < lim && c != 0x2Du) { sT[wid][o] = (u8) c; sC[wid][o] = (u32) (t * 32) + x; o++; }
 		}
 	}
+	const u32 total = __reduce_max_sync(0xffffffffu, o); // (text positions grow with the lane)
+	__syncwarp();
+	for (u32 j = lane; j < total; j += 32) { T[p0 + j] = sT[wid][j]; col[p0 + j] = sC[wid][j]; }
 	if (t == W - 1) {
 		u64 e = (u64) start[row] + rowlen[row];
 		T[e] = (u8) '#'; col[e] = (u32) n;

@@ -222,7 +222,9 @@ template <class Op> __device__ __forceinline__ typename Op::T warp_reduce_op(typ
 	return v;
 }
 
-template <class Op, bool EXCL> __global__ void __launch_bounds__(SCAN_THREADS)
+// SUBIDX (32-bit sums / maxima only): the element index is subtracted from what is written (PLCP from the running
+// maximum of position + irreducible LCP, suffix.cu: saves a pass over the array)
+template <class Op, bool EXCL, bool SUBIDX = false> __global__ void __launch_bounds__(SCAN_THREADS)
 scan_lookback_kernel(const typename Op::T *in, typename Op::T *out, u64 n, u32 *flag, typename Op::T *agg, typename Op::T *incl, u32 *ticket, typename Op::T *total_out) {
 	typedef typename Op::T T;
 	__shared__ T sm[32];
@@ -290,12 +292,12 @@ scan_lookback_kernel(const typename Op::T *in, typename Op::T *out, u64 n, u32 *
 #pragma unroll
 	for (int i = 0; i < SCAN_ITEMS; i++) {
 		const u64 idx = base + (u64) i * 32;
-		if (idx < n) out[idx] = Op::f(pre, v[i]);
+		if (idx < n) out[idx] = SUBIDX ? (T) (Op::f(pre, v[i]) - (T) idx) : Op::f(pre, v[i]);
 	}
 }
 
 // Device-wide scan. in/out may alias. total_out: optional device scalar receiving the grand total.
-template <class Op, bool EXCL> void device_scan(Dev &d, const typename Op::T *in, typename Op::T *out, u64 n, typename Op::T *total_out = nullptr) {
+template <class Op, bool EXCL, bool SUBIDX = false> void device_scan(Dev &d, const typename Op::T *in, typename Op::T *out, u64 n, typename Op::T *total_out = nullptr) {
 	typedef typename Op::T T;
 	if (n == 0) { if (total_out) FBG_CUDA(cudaMemsetAsync(total_out, 0, sizeof(T), d.stream)); return; }
 	u32 nt = div_up(n, SCAN_TILE);
@@ -304,7 +306,7 @@ template <class Op, bool EXCL> void device_scan(Dev &d, const typename Op::T *in
 	T *agg = d.alloc<T>(nt), *incl = d.alloc<T>(nt);
 	d.begin(K_SCAN);
 	FBG_CUDA(cudaMemsetAsync(flag, 0, ((u64) nt + 1) * sizeof(u32), d.stream));
-	scan_lookback_kernel<Op, EXCL><<<nt, SCAN_THREADS, 0, d.stream>>>(in, out, n, flag, agg, incl, flag + nt, total_out);
+	scan_lookback_kernel<Op, EXCL, SUBIDX><<<nt, SCAN_THREADS, 0, d.stream>>>(in, out, n, flag, agg, incl, flag + nt, total_out);
 	FBG_LAUNCH_CHECK();
 	d.end((double) n * sizeof(T) * 2.0);
 	d.release(mk);

@@ -30,7 +30,23 @@ __global__ void k1_presence_kernel(const u8 *__restrict__ T, u64 N, u32 *__restr
 	__shared__ u32 s[256];
 	s[threadIdx.x] = 0;
 	__syncthreads();
-	for (u64 i = (u64) blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (u64) gridDim.x * blockDim.x) s[T[i]] = 1;
+	// 16 bytes per load, four loads in flight per thread (one byte per load left the kernel at 0.3 TB/s: latency-bound)
+	const u64 nv = N / 16, stride = (u64) gridDim.x * blockDim.x;
+	const uint4 *T4 = reinterpret_cast<const uint4 *>(T); // T is 256-byte aligned
+	for (u64 i0 = (u64) blockIdx.x * blockDim.x + threadIdx.x; i0 < nv; i0 += 4 * stride) {
+		uint4 v[4];
+#pragma unroll
+		for (int k = 0; k < 4; k++) { const u64 i = i0 + (u64) k * stride; v[k] = i < nv ? T4[i] : make_uint4(0, 0, 0, 0); }
+#pragma unroll
+		for (int k = 0; k < 4; k++) {
+			if (i0 + (u64) k * stride < nv) {
+				const u32 w[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
+#pragma unroll
+				for (int q = 0; q < 4; q++) { s[w[q] & 0xFFu] = 1; s[(w[q] >> 8) & 0xFFu] = 1; s[(w[q] >> 16) & 0xFFu] = 1; s[w[q] >> 24] = 1; }
+			}
+		}
+	}
+	for (u64 i = nv * 16 + (u64) blockIdx.x * blockDim.x + threadIdx.x; i < N; i += stride) s[T[i]] = 1;
 	__syncthreads();
 	if (s[threadIdx.x]) present[threadIdx.x] = 1;
 }
@@ -1792,6 +1808,49 @@ __global__ void k1_irr_compact_kernel(const u32 *__restrict__ SA, const u32 *__r
 	ib[q] = k ? SA[k - 1] : U32_MAX;
 }
 
+// The irreducible ranks straight from the BWT bytes, without an N-word flag array and its scan: a thread takes 16
+// consecutive ranks (one 16-byte load + the byte before), a CTA 4096; k1_irr_count leaves the number of irreducible
+// ranks per CTA, their exclusive scan (one small CTA) is where k1_irr_emit -- the same flags again, a block-wide
+// scan of the per-thread counts -- starts writing (SA[k], SA[k-1]).  0.5 GB read twice instead of 10 GB moved.
+constexpr int IRR_ITEMS = 16;
+constexpr int IRR_TILE = 256 * IRR_ITEMS;
+__device__ __forceinline__ u32 irr_mask16(const u8 *__restrict__ BWT, u64 N, u64 k0) {
+	// bit j: rank k0 + j is irreducible (BWT differs from the rank before, or rank 0); BWT is 256-byte aligned, k0 % 16 == 0
+	if (k0 >= N) return 0u;
+	const uint4 v = *reinterpret_cast<const uint4 *>(BWT + k0); // (BWT holds N + 64 bytes)
+	const u32 w[4] = {v.x, v.y, v.z, v.w};
+	u32 prev = k0 ? (u32) BWT[k0 - 1] : 0x100u, mask = 0;
+#pragma unroll
+	for (int j = 0; j < 16; j++) {
+		const u32 c = (w[j >> 2] >> (8 * (j & 3))) & 0xFFu;
+		if (c != prev && k0 + (u64) j < N) mask |= 1u << j;
+		prev = c;
+	}
+	return mask;
+}
+__global__ void __launch_bounds__(256) k1_irr_count_kernel(const u8 *__restrict__ BWT, u64 N, u32 *__restrict__ partial) {
+	__shared__ u32 sm[32];
+	const u32 c = (u32) __popc(irr_mask16(BWT, N, ((u64) blockIdx.x * 256 + threadIdx.x) * IRR_ITEMS));
+	u32 tot;
+	block_excl_scan<OpSumU32>(c, sm, &tot);
+	if (threadIdx.x == 0) partial[blockIdx.x] = tot;
+}
+__global__ void __launch_bounds__(256) k1_irr_emit_kernel(const u8 *__restrict__ BWT, const u32 *__restrict__ SA, u64 N, const u32 *__restrict__ partial,
+                                                          u32 *__restrict__ ia, u32 *__restrict__ ib) {
+	__shared__ u32 sm[32];
+	const u64 k0 = ((u64) blockIdx.x * 256 + threadIdx.x) * IRR_ITEMS;
+	u32 mask = irr_mask16(BWT, N, k0);
+	u32 tot;
+	u32 q = partial[blockIdx.x] + block_excl_scan<OpSumU32>((u32) __popc(mask), sm, &tot);
+	while (mask) {
+		const u64 k = k0 + (u32) __ffs(mask) - 1u;
+		mask &= mask - 1u;
+		ia[q] = SA[k];
+		ib[q] = k ? SA[k - 1] : U32_MAX;
+		q++;
+	}
+}
+
 // one warp per irreducible pair: 32 bytes per step, ballot for the first mismatch
 __global__ void __launch_bounds__(256) k1_irr_lcp_kernel(const u8 *__restrict__ T, u64 N, const u32 *__restrict__ ia, const u32 *__restrict__ ib, u64 ni, u32 *__restrict__ M) {
 	u64 wgl = ((u64) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -1812,11 +1871,6 @@ __global__ void __launch_bounds__(256) k1_irr_lcp_kernel(const u8 *__restrict__ 
 	}
 }
 
-__global__ void k1_plcp_kernel(u32 *__restrict__ M, u64 N) {
-	u64 p = (u64) blockIdx.x * blockDim.x + threadIdx.x;
-	if (p < N) M[p] = M[p] - (u32) p;
-}
-
 void k1_lcp(Pipeline &p) {
 	Dev &d = p.dev;
 	const u64 N = p.N;
@@ -1829,22 +1883,36 @@ void k1_lcp(Pipeline &p) {
 		d.end((double) N * 4.0);
 		return;
 	}
-	d.ensure(N * 16 + (N / SCAN_TILE + 2) * 24 + (4u << 20));
+	const bool from_bwt = p.have_bwt && !getenv("FBG_LCP_FLAGS"); // FBG_LCP_FLAGS=1: the flag-array form also with BWT bytes (test hook)
+	d.ensure(N * (from_bwt ? 8 : 16) + (N / SCAN_TILE + 2) * 24 + (N / IRR_TILE + 2) * 4 + (4u << 20));
 	u64 mk = d.mark();
-	u32 *flag = d.alloc<u32>(N), *pos = d.alloc<u32>(N), *ia = d.alloc<u32>(N), *ib = d.alloc<u32>(N);
+	u32 *ia = d.alloc<u32>(N), *ib = d.alloc<u32>(N);
 	u32 *total = reinterpret_cast<u32 *>(p.scalars + 8);
 	u32 *h_total = reinterpret_cast<u32 *>(p.h_scalars + 8);
 	u32 g = div_up(N, 256);
-	d.begin(K_LCP);
-	if (p.have_bwt) k1_irr_flag_bwt_kernel<<<g, 256, 0, d.stream>>>(p.BWT, N, flag);
-	else k1_irr_flag_kernel<<<g, 256, 0, d.stream>>>(p.SA, p.T, N, flag);
-	FBG_LAUNCH_CHECK();
-	d.end((double) N * (4.0 + 2.0 + 4.0));
-	device_scan<OpSumU32, true>(d, flag, pos, N, total);
-	d.begin(K_LCP);
-	k1_irr_compact_kernel<<<g, 256, 0, d.stream>>>(p.SA, flag, pos, N, ia, ib);
-	FBG_CUDA(cudaMemsetAsync(p.PLCP, 0, N * sizeof(u32), d.stream));
-	FBG_LAUNCH_CHECK();
+	if (from_bwt) {
+		const u32 nt = (u32) div_up(N, IRR_TILE);
+		u32 *partial = d.alloc<u32>((u64) nt + 1);
+		d.begin(K_LCP);
+		k1_irr_count_kernel<<<nt, 256, 0, d.stream>>>(p.BWT, N, partial);
+		scan_partials_kernel<OpSumU32><<<1, 1024, 0, d.stream>>>(partial, nt, total);
+		k1_irr_emit_kernel<<<nt, 256, 0, d.stream>>>(p.BWT, p.SA, N, partial, ia, ib);
+		FBG_CUDA(cudaMemsetAsync(p.PLCP, 0, N * sizeof(u32), d.stream));
+		FBG_LAUNCH_CHECK();
+		d.note_launches(K_LCP, 2);
+	} else {
+		u32 *flag = d.alloc<u32>(N), *pos = d.alloc<u32>(N);
+		d.begin(K_LCP);
+		if (p.have_bwt) k1_irr_flag_bwt_kernel<<<g, 256, 0, d.stream>>>(p.BWT, N, flag);
+		else k1_irr_flag_kernel<<<g, 256, 0, d.stream>>>(p.SA, p.T, N, flag);
+		FBG_LAUNCH_CHECK();
+		d.end((double) N * (4.0 + 2.0 + 4.0));
+		device_scan<OpSumU32, true>(d, flag, pos, N, total);
+		d.begin(K_LCP);
+		k1_irr_compact_kernel<<<g, 256, 0, d.stream>>>(p.SA, flag, pos, N, ia, ib);
+		FBG_CUDA(cudaMemsetAsync(p.PLCP, 0, N * sizeof(u32), d.stream));
+		FBG_LAUNCH_CHECK();
+	}
 	FBG_CUDA(cudaMemcpyAsync(h_total, total, sizeof(u32), cudaMemcpyDeviceToHost, d.stream));
 	FBG_CUDA(cudaStreamSynchronize(d.stream));
 	u64 ni = *h_total;
@@ -1852,13 +1920,10 @@ void k1_lcp(Pipeline &p) {
 	if (warps == 0) warps = 1;
 	k1_irr_lcp_kernel<<<div_up(warps * 32, 256), 256, 0, d.stream>>>(p.T, N, ia, ib, ni, p.PLCP);
 	FBG_LAUNCH_CHECK();
-	d.end((double) N * 16.0 + (double) ni * 12.0);
+	d.end((from_bwt ? (double) N * 6.0 : (double) N * 16.0) + (double) ni * 12.0);
 	d.note_launches(K_LCP, 1);
-	device_scan<OpMaxU32, false>(d, p.PLCP, p.PLCP, N);
-	d.begin(K_LCP);
-	k1_plcp_kernel<<<g, 256, 0, d.stream>>>(p.PLCP, N);
-	FBG_LAUNCH_CHECK();
-	d.end((double) N * 8.0);
+	device_scan<OpMaxU32, false, true>(d, p.PLCP, p.PLCP, N); // PLCP[p] = max_{q <= p} (q + irreducible LCP at q) - p
+	(void) g;
 	d.release(mk);
 }
 
