@@ -178,8 +178,8 @@ template <int MODE> __global__ void __launch_bounds__(KM_THREADS) k1_kmer_kernel
 		if (full) {
 			// 32 contiguous bytes per thread and array
 			uint4 *so = reinterpret_cast<uint4 *>(dk.slot_of + g0), *oo = reinterpret_cast<uint4 *>(dk.ord_of + g0);
-			so[0] = make_uint4(sl[0], sl[1], sl[2], sl[3]); so[1] = make_uint4(sl[4], sl[5], sl[6], sl[7]);
-			oo[0] = make_uint4(od[0], od[1], od[2], od[3]); oo[1] = make_uint4(od[4], od[5], od[6], od[7]);
+			__stcs(so, make_uint4(sl[0], sl[1], sl[2], sl[3])); __stcs(so + 1, make_uint4(sl[4], sl[5], sl[6], sl[7]));
+			__stcs(oo, make_uint4(od[0], od[1], od[2], od[3])); __stcs(oo + 1, make_uint4(od[4], od[5], od[6], od[7]));
 		}
 #pragma unroll
 		for (int it = 0; it < KM_ITEMS; it++) {
@@ -368,7 +368,7 @@ __global__ void __launch_bounds__(CP_THREADS, CP_MINB) k1_cls_write_kernel(const
 #pragma unroll
 	for (int i = 0; i < CP_ITEMS; i++) {
 		u64 t = w0 + (u64) i * 32 + l;
-		u8 v = t < na ? cls[t] : (u8) CLS_DROP;
+		u8 v = t < na ? __ldcs(cls + t) : (u8) CLS_DROP; // (the lists are read once and written once: streaming hints keep R in L2)
 		v = v == ca ? (u8) 1 : (v == cb ? (u8) 2 : (u8) 0); // 1 -> target a, 2 -> target b, 0 -> not moved by this call
 		c[i] = v;
 		cs += __popc(__ballot_sync(0xffffffffu, v == 1));
@@ -391,7 +391,7 @@ __global__ void __launch_bounds__(CP_THREADS, CP_MINB) k1_cls_write_kernel(const
 		for (int k = 0; k < CP_CHUNK; k++) {
 			const u64 t = w0 + (u64) (i0 + k) * 32 + l;
 			pp[k] = 0; rr[k] = 0;
-			if (c[i0 + k]) { pp[k] = lp[t]; rr[k] = lr[t]; }
+			if (c[i0 + k]) { pp[k] = __ldcs(lp + t); rr[k] = __ldcs(lr + t); }
 		}
 		if (PEER) {
 			u32 cq[CP_CHUNK];
@@ -416,11 +416,11 @@ __global__ void __launch_bounds__(CP_THREADS, CP_MINB) k1_cls_write_kernel(const
 		for (int k = 0; k < CP_CHUNK; k++) {
 			const int i = i0 + k;
 			const u32 ma = __ballot_sync(0xffffffffu, c[i] == 1), mb = __ballot_sync(0xffffffffu, c[i] == 2);
-			if (c[i] == 1) { const u32 d = qa + __popc(ma & lanemask_lt()); alp[d] = pp[k]; alr[d] = rr[k]; ar2[d] = r2[k]; }
+			if (c[i] == 1) { const u32 d = qa + __popc(ma & lanemask_lt()); __stcs(alp + d, pp[k]); __stcs(alr + d, rr[k]); __stcs(ar2 + d, r2[k]); }
 			else if (c[i] == 2) {
 				const u32 d = qb + __popc(mb & lanemask_lt());
 				if (tgt_b == TGT_B) { o.Bkey[d] = ((u64) rr[k] << nbits) | r2[k]; o.Bval[d] = pp[k]; }
-				else { blp[d] = pp[k]; blr[d] = rr[k]; br2[d] = r2[k]; }
+				else { __stcs(blp + d, pp[k]); __stcs(blr + d, rr[k]); __stcs(br2 + d, r2[k]); }
 			}
 			qa += __popc(ma); qb += __popc(mb);
 		}
@@ -958,7 +958,7 @@ k1_bucket_sort_kernel(const u32 *__restrict__ lp, const u32 *__restrict__ lr, co
 					const u32 pre = s_pre[j * NW + w];
 					if (rv[j] == pv) {
 						const u64 out = h + nless + eq_run + (pre & 0xFFFFu) + (u32) __popc(be[j] & lanemask_lt());
-						lp_out[out] = pp[j]; lr_out[out] = req; cls_out[out] = (u8) cls_eq;
+						__stcs(lp_out + out, pp[j]); __stcs(lr_out + out, req); cls_out[out] = (u8) cls_eq;
 						if (nless) R[pp[j]] = req;
 						if (neq == 1) so.put(req, pp[j]);
 					} else {
@@ -1134,12 +1134,23 @@ __global__ void k1_dict_list_kernel(const u64 *__restrict__ key, const u32 *__re
 // its k-mer with the column the run ends in).  A bucket that spans the ranges of several GPUs (a gap run
 // across a range boundary, a repeat) is kept by EVERY GPU: each sorts it in full, identically, so whoever
 // owns a member's column holds that member's up-to-date rank without any rank crossing the wire.
-__global__ void k1_dict_spans_kernel(const u32 *__restrict__ slot_of, const u32 *__restrict__ first, const u32 *__restrict__ col, u64 N, PeerView pv, u8 *__restrict__ spans) {
+// (the N-wide pass compares two bytes -- the owner of the position's column, from a table of n + 2 entries, and the owner of
+// the bucket's smallest member, found once per distinct k-mer -- instead of looking up first[s] and col[first[s]] per position)
+__global__ void k1_owner_table_kernel(u32 ncols, PeerView pv, u8 *__restrict__ ownc) {
+	u32 c = blockIdx.x * blockDim.x + threadIdx.x;
+	if (c < ncols) ownc[c] = (u8) pv.owner(c);
+}
+__global__ void k1_dict_own1_kernel(const u32 *__restrict__ lv, const u32 *__restrict__ first, const u32 *__restrict__ col, const u8 *__restrict__ ownc, u32 nd, u8 *__restrict__ own1) {
+	u32 t = blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= nd) return;
+	const u32 s = lv[t];
+	own1[s] = ownc[col[first[s]]];
+}
+__global__ void k1_dict_spans_kernel(const u32 *__restrict__ slot_of, const u32 *__restrict__ col, const u8 *__restrict__ ownc, const u8 *__restrict__ own1, u64 N, u8 *__restrict__ spans) {
 	u64 p = (u64) blockIdx.x * blockDim.x + threadIdx.x;
 	if (p >= N) return;
-	const u32 s = slot_of[p];
-	const u32 ca = col[p], cb = __ldg(col + first[s]);
-	if (ca != cb && pv.owner(ca) != pv.owner(cb)) spans[s] = 1;
+	const u32 s = __ldcs(slot_of + p);
+	if (__ldg(ownc + __ldcs(col + p)) != __ldg(own1 + s)) spans[s] = 1;
 }
 __global__ void k1_dict_mine_kernel(const u32 *__restrict__ lv, const u32 *__restrict__ first, const u32 *__restrict__ col, const u8 *__restrict__ spans, u32 nd, PeerView pv, u8 *__restrict__ mine) {
 	u32 t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1224,13 +1235,13 @@ __global__ void __launch_bounds__(256) k1_dict_emit_kernel(const u32 *__restrict
 			return;
 		}
 	}
-	const uint4 v = __ldg(info + slot_of[p]);
-	R[p] = v.x;
+	const uint4 v = __ldg(info + __ldcs(slot_of + p)); // (slot_of, ord_of, R stream through once: hints keep the table in L2)
+	__stcs(R + p, v.x);
 	if (v.z == 1) { so.put(v.x, (u32) p); return; }
 	if (v.y == U32_MAX) return; // peer mode: another GPU sorts this bucket
 	const u64 pn = p + hnext;
 	const u32 r2 = pn < N ? __ldg(rank_of_slot + slot_of[pn]) : 0u; // 4-byte entries: a quarter of the L2 traffic of info[]
-	const u32 q = v.y + ord_of[p];
+	const u32 q = v.y + __ldcs(ord_of + p);
 	if (v.z < mid_min) { o.Slp[q] = (u32) p; o.Slr[q] = v.x; o.Sr2[q] = r2; }
 	else if (v.z <= BSMALL) { o.Mlp[q] = (u32) p; o.Mlr[q] = v.x; o.Mr2[q] = r2; }
 	else { o.Bkey[q] = ((u64) v.x << nbits) | r2; o.Bval[q] = (u32) p; }
@@ -1243,7 +1254,7 @@ static u32 dict_capacity(u64 N) {
 }
 static u64 dict_scratch_bytes(u64 N) {
 	u64 cap = dict_capacity(N);
-	return cap * (8 + 4 + 4 + 16 + 4 + 1) + (cap / 2) * (16 + 8 + 8 + 16 + 8 + 1) + (cap / SCAN_TILE + 2) * 24 + (cap / 2 / RS_TILE + 2) * RS_BINS * 12 + (1u << 16);
+	return cap * (8 + 4 + 4 + 16 + 4 + 1 + 1) + (cap / 2) * (16 + 8 + 8 + 16 + 8 + 1) + (cap / SCAN_TILE + 2) * 24 + (cap / 2 / RS_TILE + 2) * RS_BINS * 12 + (1u << 16) + N + (1u << 12);
 }
 
 // Returns false (nothing written that matters) when the text has too many distinct k-mers for
@@ -1352,9 +1363,12 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	if (pv) {
 		spans = d.alloc<u8>(cap);
 		mine = d.alloc<u8>(ndmax);
+		u8 *own1 = d.alloc<u8>(cap), *ownc = d.alloc<u8>(p.n + 2);
 		FBG_CUDA(cudaMemsetAsync(spans, 0, cap, d.stream));
 		d.begin(K_DOUBLING_AUX);
-		k1_dict_spans_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, dk.first, p.col, N, *pv, spans);
+		k1_owner_table_kernel<<<div_up(p.n + 2, 256), 256, 0, d.stream>>>((u32) p.n + 2u, *pv, ownc);
+		k1_dict_own1_kernel<<<gn, 256, 0, d.stream>>>(lv, dk.first, p.col, ownc, nd, own1);
+		k1_dict_spans_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, p.col, ownc, own1, N, spans);
 		k1_dict_mine_kernel<<<gn, 256, 0, d.stream>>>(lv, dk.first, p.col, spans, nd, *pv, mine);
 		FBG_LAUNCH_CHECK();
 		d.end((double) N * 8.0 + (double) nd * 13.0);
