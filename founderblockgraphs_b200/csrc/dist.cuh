@@ -59,6 +59,7 @@ struct PeerView {
 	u32 *R[MAX_PEERS];
 	u32 xb[MAX_PEERS + 1]; // GPU g owns the text positions of columns [xb[g], xb[g+1]); '#' and the sentinel (column >= n) go to the last
 	int me, world;
+	const u32 *notmine;    // one bit per text position: its column belongs to another GPU (62 MB for 5e8 positions: the look-ups of a round stay in L2)
 	__host__ __device__ int owner(u32 c) const {
 		int g = 0;
 		while (g + 1 < world && c >= xb[g + 1]) g++;

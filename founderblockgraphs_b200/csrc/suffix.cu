@@ -394,16 +394,20 @@ __global__ void __launch_bounds__(CP_THREADS, CP_MINB) k1_cls_write_kernel(const
 			if (c[i0 + k]) { pp[k] = __ldcs(lp + t); rr[k] = __ldcs(lr + t); }
 		}
 		if (PEER) {
-			u32 cq[CP_CHUNK];
+			// nearly every look-up stays on this GPU (a bucket's members lie in its columns, p + h leaves them only near
+			// the range's end): one bit per position says so; the column -- hence the owner -- is looked up for the rest
+			u32 nm[CP_CHUNK];
 #pragma unroll
 			for (int k = 0; k < CP_CHUNK; k++) {
 				const u64 q = (u64) pp[k] + hnext;
-				cq[k] = (c[i0 + k] && q < N) ? col[q] : 0u;
+				nm[k] = (c[i0 + k] && q < N) ? (__ldg(pv.notmine + (q >> 5)) >> (q & 31)) & 1u : 0u;
 			}
 #pragma unroll
 			for (int k = 0; k < CP_CHUNK; k++) {
 				const u64 q = (u64) pp[k] + hnext;
-				r2[k] = (c[i0 + k] && q < N) ? __ldcg(pv.R[pv.owner(cq[k])] + q) : 0u; // never through L1: the owner rewrites it every round
+				r2[k] = 0u;
+				if (c[i0 + k] && q < N) r2[k] = nm[k] ? __ldcg(pv.R[pv.owner(col[q])] + q) // never through L1: the owner rewrites it every round
+				                                      : R[q];
 			}
 		} else {
 #pragma unroll
@@ -1134,6 +1138,27 @@ __global__ void k1_dict_list_kernel(const u64 *__restrict__ key, const u32 *__re
 // its k-mer with the column the run ends in).  A bucket that spans the ranges of several GPUs (a gap run
 // across a range boundary, a repeat) is kept by EVERY GPU: each sorts it in full, identically, so whoever
 // owns a member's column holds that member's up-to-date rank without any rank crossing the wire.
+__global__ void k1_notmine_kernel(const u32 *__restrict__ col, u64 N, u32 x0, u32 x1, int last, u32 *__restrict__ bits) {
+	const u64 p = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	bool nm = false;
+	if (p < N) { const u32 c = __ldcs(col + p); nm = !(c >= x0 && (c < x1 || last)); }
+	const u32 w = __ballot_sync(0xffffffffu, nm);
+	if ((threadIdx.x & 31) == 0 && p < N) bits[p >> 5] = w;
+}
+// the text positions of row i whose column lies in [x0, x1): own_a[i] <= p < own_b[i] (the last GPU: through the row's '#',
+// and the final sentinel after the last row)
+__global__ void k1_own_ranges_kernel(const u32 *__restrict__ RK, const u32 *__restrict__ NG, const u32 *__restrict__ start, const u32 *__restrict__ rowlen,
+                                     u64 m, u64 n, u32 x0, u32 x1, int last, u32 *__restrict__ own_a, u32 *__restrict__ own_b) {
+	const u64 i = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= m) return;
+	auto rank_at = [&](u32 x) -> u32 {
+		if (x >= n) return rowlen[i];
+		const u64 t = x >> 5;
+		return RK[t * m + i] + (u32) __popc(NG[t * m + i] & ((1u << (x & 31)) - 1u));
+	};
+	own_a[i] = start[i] + rank_at(x0);
+	own_b[i] = last ? start[i] + rowlen[i] + 1u + (i == m - 1 ? 1u : 0u) : start[i] + rank_at(x1);
+}
 // (the N-wide pass compares two bytes -- the owner of the position's column, from a table of n + 2 entries, and the owner of
 // the bucket's smallest member, found once per distinct k-mer -- instead of looking up first[s] and col[first[s]] per position)
 __global__ void k1_owner_table_kernel(u32 ncols, PeerView pv, u8 *__restrict__ ownc) {
@@ -1152,11 +1177,12 @@ __global__ void k1_dict_spans_kernel(const u32 *__restrict__ slot_of, const u32 
 	const u32 s = __ldcs(slot_of + p);
 	if (__ldg(ownc + __ldcs(col + p)) != __ldg(own1 + s)) spans[s] = 1;
 }
-__global__ void k1_dict_mine_kernel(const u32 *__restrict__ lv, const u32 *__restrict__ first, const u32 *__restrict__ col, const u8 *__restrict__ spans, u32 nd, PeerView pv, u8 *__restrict__ mine) {
+__global__ void k1_dict_mine_kernel(const u32 *__restrict__ lv, const u8 *__restrict__ own1, const u8 *__restrict__ spans, u32 nd, int me, u8 *__restrict__ mine, u32 *__restrict__ nspan) {
 	u32 t = blockIdx.x * blockDim.x + threadIdx.x;
 	if (t >= nd) return;
 	const u32 s = lv[t];
-	mine[t] = (spans[s] || pv.owner(col[first[s]]) == pv.me) ? 1 : 0;
+	mine[t] = (spans[s] || own1[s] == (u8) me) ? 1 : 0;
+	if (spans[s]) atomicAdd(nspan, 1u);
 }
 // bucket sizes in k-mer order: all of them (their exclusive scan = the ranks) and the big ones (B list offsets);
 // mine: null, or which buckets this GPU sorts
@@ -1212,16 +1238,23 @@ __global__ void k1_dict_place_kernel(const u32 *__restrict__ ov, const u32 *__re
 // rank has to be visible yet)
 // PEER: this GPU only needs the ranks of its own columns [x0, x1) (the last GPU also takes '#' and the sentinel) and the
 // members of the buckets it sorts; a position outside its columns matters only when its bucket spans GPUs
-template <bool PEER>
+// MODE 0: one GPU, every position.  Peer mode: MODE 1 = this GPU's own positions (grid.y = row, its text range from
+// k1_own_ranges_kernel: no thread for the (world - 1) / world of the text that belongs to the others), MODE 2 = the
+// members of the buckets every GPU sorts that lie in other GPUs' columns (N-wide; returns at once when no bucket spans).
+template <int MODE>
 __global__ void __launch_bounds__(256) k1_dict_emit_kernel(const u32 *__restrict__ slot_of, const u32 *__restrict__ ord_of, const uint4 *__restrict__ info, const u32 *__restrict__ rank_of_slot,
                                                            u64 N, u64 hnext, int nbits, u32 mid_min, u32 *__restrict__ R, SaOut so, CompactOut o,
-                                                           const u32 *__restrict__ col, const u8 *__restrict__ spans, u32 x0, u32 x1, int last) {
+                                                           const u32 *__restrict__ notmine, const u8 *__restrict__ spans, const u32 *__restrict__ own_a, const u32 *__restrict__ own_b, const u32 *__restrict__ nspan) {
 	u64 p = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (MODE == 1) {
+		p += own_a[blockIdx.y];
+		if (p >= own_b[blockIdx.y]) return;
+	}
+	if (MODE == 2 && *nspan == 0) return;
 	if (p >= N) return;
-	if (PEER) {
-		const u32 c = col[p];
-		const bool own = c >= x0 && (c < x1 || last);
-		if (!own) {
+	if (MODE == 2) {
+		{
+			if (!((notmine[p >> 5] >> (p & 31)) & 1u)) return; // mine: written by the MODE 1 pass
 			if (!spans[slot_of[p]]) return;
 			// a member of a bucket every GPU sorts: listed below; its rank and SA entry are its owner's business
 			const uint4 v = __ldg(info + slot_of[p]);
@@ -1369,7 +1402,7 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 		k1_owner_table_kernel<<<div_up(p.n + 2, 256), 256, 0, d.stream>>>((u32) p.n + 2u, *pv, ownc);
 		k1_dict_own1_kernel<<<gn, 256, 0, d.stream>>>(lv, dk.first, p.col, ownc, nd, own1);
 		k1_dict_spans_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, p.col, ownc, own1, N, spans);
-		k1_dict_mine_kernel<<<gn, 256, 0, d.stream>>>(lv, dk.first, p.col, spans, nd, *pv, mine);
+		k1_dict_mine_kernel<<<gn, 256, 0, d.stream>>>(lv, own1, spans, nd, pv->me, mine, sc + 6);
 		FBG_LAUNCH_CHECK();
 		d.end((double) N * 8.0 + (double) nd * 13.0);
 		d.note_launches(K_DOUBLING_AUX, 1);
@@ -1432,9 +1465,16 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	k1_dict_place_kernel<<<gn, 256, 0, d.stream>>>(ov, lv, nd, mid_min, zs, zm, info);
 	if (pv) {
 		FBG_CUDA(cudaMemsetAsync(p.ISA, 0, N * sizeof(u32), d.stream)); // ranks outside this GPU's columns stay 0: the inverse is assembled by max at the end
-		k1_dict_emit_kernel<true><<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, SaOut{p.SA, p.have_bwt ? p.BWT : nullptr, p.T}, o,
-		                                                                 p.col, spans, pv->xb[pv->me], pv->xb[pv->me + 1], pv->me + 1 == pv->world ? 1 : 0);
-	} else k1_dict_emit_kernel<false><<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, SaOut{p.SA, p.have_bwt ? p.BWT : nullptr, p.T}, o, nullptr, nullptr, 0, 0, 0);
+		const u32 x0 = pv->xb[pv->me], x1 = pv->xb[pv->me + 1];
+		const int last = pv->me + 1 == pv->world ? 1 : 0;
+		u32 *own_a = d.alloc<u32>(p.m), *own_b = d.alloc<u32>(p.m);
+		k1_own_ranges_kernel<<<div_up(p.m, 256), 256, 0, d.stream>>>(p.RK, p.NG, p.start, p.rowlen, p.m, p.n, x0, x1, last, own_a, own_b);
+		const SaOut sao{p.SA, p.have_bwt ? p.BWT : nullptr, p.T};
+		const dim3 g1((u32) div_up((u64) (x1 - x0) + 2, 256), (u32) p.m); // a row has at most x1 - x0 characters in these columns (+ '#', + the sentinel)
+		k1_dict_emit_kernel<1><<<g1, 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, sao, o, pv->notmine, spans, own_a, own_b, sc + 6);
+		k1_dict_emit_kernel<2><<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, sao, o, pv->notmine, spans, own_a, own_b, sc + 6);
+		d.note_launches(K_DOUBLING_AUX, 2);
+	} else k1_dict_emit_kernel<0><<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, SaOut{p.SA, p.have_bwt ? p.BWT : nullptr, p.T}, o, nullptr, nullptr, nullptr, nullptr, nullptr);
 	FBG_LAUNCH_CHECK();
 	d.end((double) N * (8.0 + 4.0 + 4.0 + 12.0) + (double) nd * 40.0);
 	d.note_launches(K_DOUBLING_AUX, 1);
@@ -1529,7 +1569,7 @@ void k1_suffix_array(Pipeline &p) {
 	// scratch of this phase: 98 B per suffix sorted here (sort ping-pong 24, heads 16, classes 2,
 	// S lists 24, M lists 24, sorter outputs 8) + radix count matrices + (key-range form) the N-word bucket directory
 	d.release(mk);
-	d.ensure(cap * 100 + (capN - cap) * 8 + (cap / RS_TILE + 2) * RS_BINS * 12 + (u64) km_grid * 8 + (sharded && !peer ? N * 4 + (N / SCAN_TILE + 2) * 24 : dict_scratch_bytes(N)) + (16u << 20));
+	d.ensure(cap * 100 + (capN - cap) * 8 + (cap / RS_TILE + 2) * RS_BINS * 12 + (u64) km_grid * 8 + (sharded && !peer ? N * 4 + (N / SCAN_TILE + 2) * 24 : dict_scratch_bytes(N)) + (peer ? N / 8 + 4096 : 0) + (16u << 20));
 	mk = d.mark();
 
 	RadixBuffers rb;
@@ -1565,6 +1605,10 @@ void k1_suffix_array(Pipeline &p) {
 		void *rp[MAX_PEERS];
 		dist.open_peers(d.pers, p.ISA, rp, d.stream);
 		for (int g = 0; g < dist.world; g++) pv.R[g] = static_cast<u32 *>(rp[g]);
+		u32 *nmb = d.alloc<u32>(N / 32 + 2);
+		k1_notmine_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(p.col, N, pv.xb[pv.me], pv.xb[pv.me + 1], pv.me + 1 == pv.world ? 1 : 0, nmb);
+		FBG_LAUNCH_CHECK();
+		pv.notmine = nmb;
 		pv_dev = d.alloc<PeerView>(1);
 		FBG_CUDA(cudaMemcpyAsync(pv_dev, &pv, sizeof pv, cudaMemcpyHostToDevice, d.stream));
 		FBG_CUDA(cudaStreamSynchronize(d.stream)); // pv lives on this function's stack
