@@ -1280,6 +1280,87 @@ __global__ void __launch_bounds__(256) k1_dict_emit_kernel(const u32 *__restrict
 	else { o.Bkey[q] = ((u64) v.x << nbits) | r2; o.Bval[q] = (u32) p; }
 }
 
+// ---- the same emission in TILE order (one GPU): a CTA takes 32 rows x the 32 columns of one bitmap word.
+// In text order a warp's 32 positions belong to 32 different buckets: 32 sectors of info[], 32 of rank_of_slot[] and
+// 3 x 32 of the lists per warp instruction -- ncu: 38 GB of DRAM traffic for 14 GB of algorithmic bytes, L2-bound.
+// Here phase 1 reads the per-position inputs along the ROWS (a warp per row, consecutive text positions: coalesced)
+// into shared memory; phase 2 turns the tile: a warp takes a COLUMN, its lanes the 32 rows -- nearly always one
+// bucket, so the table look-ups of a warp hit one or two sectors and its list writes go to (nearly) consecutive
+// slots, the arrival numbers of consecutive rows being (nearly) consecutive; phase 3 writes the ranks along the
+// rows again.  Same bytes in the same places as the text-order kernel; '#' and the sentinel by k1_dict_emit_ends.
+__global__ void __launch_bounds__(256) k1_dict_emit_tile_kernel(const u32 *__restrict__ slot_of, const u32 *__restrict__ ord_of, const uint4 *__restrict__ info, const u32 *__restrict__ rank_of_slot,
+                                                                u64 N, u64 hnext, int nbits, u32 mid_min, u32 *__restrict__ R, SaOut so, CompactOut o,
+                                                                const u32 *__restrict__ RK, const u32 *__restrict__ NG, const u32 *__restrict__ start, u64 m) {
+	__shared__ u32 sS[32][33], sO[32][33], sN[32][33]; // slot of p, arrival number of p, slot of p + hnext -> (phase 2) rank of p
+	__shared__ u32 sNG[32], sP0[32];
+	const u32 w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const u64 i0 = (u64) blockIdx.x * 32, t = blockIdx.y;
+	if (threadIdx.x < 32) {
+		const u64 i = i0 + threadIdx.x;
+		sNG[threadIdx.x] = i < m ? NG[t * m + i] : 0u;
+		sP0[threadIdx.x] = i < m ? start[i] + RK[t * m + i] : 0u;
+	}
+	__syncthreads();
+	// phase 1: rows
+#pragma unroll
+	for (u32 k = 0; k < 4; k++) {
+		const u32 rr = w + 8 * k;
+		const u32 cnt = (u32) __popc(sNG[rr]);
+		if (lane < cnt) {
+			const u64 p = (u64) sP0[rr] + lane, pn = p + hnext;
+			sS[rr][lane] = __ldcs(slot_of + p);
+			sO[rr][lane] = __ldcs(ord_of + p);
+			sN[rr][lane] = pn < N ? slot_of[pn] : U32_MAX;
+		}
+	}
+	__syncthreads();
+	// phase 2: columns (lane = row)
+	const u32 ng = sNG[lane], p0 = sP0[lane];
+#pragma unroll
+	for (u32 k = 0; k < 4; k++) {
+		const u32 c = w + 8 * k;
+		if ((ng >> c) & 1u) {
+			const u32 j = (u32) __popc(ng & ((1u << c) - 1u));
+			const u32 p = p0 + j;
+			const uint4 v = __ldg(info + sS[lane][j]);
+			const u32 sn = sN[lane][j];
+			sN[lane][j] = v.x; // the rank, for phase 3
+			if (v.z == 1) so.put(v.x, p);
+			else {
+				const u32 r2 = sn != U32_MAX ? __ldg(rank_of_slot + sn) : 0u;
+				const u32 q = v.y + sO[lane][j];
+				if (v.z < mid_min) { o.Slp[q] = p; o.Slr[q] = v.x; o.Sr2[q] = r2; }
+				else if (v.z <= BSMALL) { o.Mlp[q] = p; o.Mlr[q] = v.x; o.Mr2[q] = r2; }
+				else { o.Bkey[q] = ((u64) v.x << nbits) | r2; o.Bval[q] = p; }
+			}
+		}
+	}
+	__syncthreads();
+	// phase 3: rows
+#pragma unroll
+	for (u32 k = 0; k < 4; k++) {
+		const u32 rr = w + 8 * k;
+		if (lane < (u32) __popc(sNG[rr])) __stcs(R + (u64) sP0[rr] + lane, sN[rr][lane]);
+	}
+}
+// the '#' behind every row and the final sentinel (text-order code, m + 1 positions)
+__global__ void k1_dict_emit_ends_kernel(const u32 *__restrict__ slot_of, const u32 *__restrict__ ord_of, const uint4 *__restrict__ info, const u32 *__restrict__ rank_of_slot,
+                                         u64 N, u64 hnext, int nbits, u32 mid_min, u32 *__restrict__ R, SaOut so, CompactOut o,
+                                         const u32 *__restrict__ start, const u32 *__restrict__ rowlen, u64 m) {
+	const u64 i = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i > m) return;
+	const u64 p = i < m ? (u64) start[i] + rowlen[i] : N - 1;
+	const uint4 v = __ldg(info + slot_of[p]);
+	R[p] = v.x;
+	if (v.z == 1) { so.put(v.x, (u32) p); return; }
+	const u64 pn = p + hnext;
+	const u32 r2 = pn < N ? __ldg(rank_of_slot + slot_of[pn]) : 0u;
+	const u32 q = v.y + ord_of[p];
+	if (v.z < mid_min) { o.Slp[q] = (u32) p; o.Slr[q] = v.x; o.Sr2[q] = r2; }
+	else if (v.z <= BSMALL) { o.Mlp[q] = (u32) p; o.Mlr[q] = v.x; o.Mr2[q] = r2; }
+	else { o.Bkey[q] = ((u64) v.x << nbits) | r2; o.Bval[q] = (u32) p; }
+}
+
 static u32 dict_capacity(u64 N) {
 	u32 cap = 1u << 16;
 	while ((u64) cap * 8 < N && cap < (1u << 30)) cap <<= 1;
@@ -1474,6 +1555,13 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 		k1_dict_emit_kernel<1><<<g1, 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, sao, o, pv->notmine, spans, own_a, own_b, sc + 6);
 		k1_dict_emit_kernel<2><<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, sao, o, pv->notmine, spans, own_a, own_b, sc + 6);
 		d.note_launches(K_DOUBLING_AUX, 2);
+	} else if (p.gaps != 0 && p.W <= 65535 && !getenv("FBG_EMIT_TEXT_ORDER")) {
+		// (a gapless text has no RK / NG tables; FBG_EMIT_TEXT_ORDER=1: the text-order kernel, for comparison)
+		const SaOut sao{p.SA, p.have_bwt ? p.BWT : nullptr, p.T};
+		const dim3 gt((u32) div_up(p.m, 32), (u32) p.W);
+		k1_dict_emit_tile_kernel<<<gt, 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, sao, o, p.RK, p.NG, p.start, p.m);
+		k1_dict_emit_ends_kernel<<<div_up(p.m + 1, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, sao, o, p.start, p.rowlen, p.m);
+		d.note_launches(K_DOUBLING_AUX, 1);
 	} else k1_dict_emit_kernel<0><<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, SaOut{p.SA, p.have_bwt ? p.BWT : nullptr, p.T}, o, nullptr, nullptr, nullptr, nullptr, nullptr);
 	FBG_LAUNCH_CHECK();
 	d.end((double) N * (8.0 + 4.0 + 4.0 + 12.0) + (double) nd * 40.0);
