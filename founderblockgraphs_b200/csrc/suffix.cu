@@ -1290,11 +1290,14 @@ __global__ void __launch_bounds__(256) k1_dict_emit_kernel(const u32 *__restrict
 // rows again.  Same bytes in the same places as the text-order kernel; '#' and the sentinel by k1_dict_emit_ends.
 __global__ void __launch_bounds__(256) k1_dict_emit_tile_kernel(const u32 *__restrict__ slot_of, const u32 *__restrict__ ord_of, const uint4 *__restrict__ info, const u32 *__restrict__ rank_of_slot,
                                                                 u64 N, u64 hnext, int nbits, u32 mid_min, u32 *__restrict__ R, SaOut so, CompactOut o,
-                                                                const u32 *__restrict__ RK, const u32 *__restrict__ NG, const u32 *__restrict__ start, u64 m) {
+                                                                const u32 *__restrict__ RK, const u32 *__restrict__ NG, const u32 *__restrict__ start, u64 m,
+                                                                u32 tw0, u32 x0, u32 x1) {
+	// [x0, x1): the columns this GPU owns (peer mode; one GPU: all of them), tw0 = x0 / 32
 	__shared__ u32 sS[32][33], sO[32][33], sN[32][33]; // slot of p, arrival number of p, slot of p + hnext -> (phase 2) rank of p
 	__shared__ u32 sNG[32], sP0[32];
 	const u32 w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	const u64 i0 = (u64) blockIdx.x * 32, t = blockIdx.y;
+	const u32 ngroups = (u32) ((m + 31) / 32); // (one-dimensional grid, row group fastest: the blocks in flight work on few buckets)
+	const u64 i0 = (u64) (blockIdx.x % ngroups) * 32, t = (u64) tw0 + blockIdx.x / ngroups;
 	if (threadIdx.x < 32) {
 		const u64 i = i0 + threadIdx.x;
 		sNG[threadIdx.x] = i < m ? NG[t * m + i] : 0u;
@@ -1319,14 +1322,15 @@ __global__ void __launch_bounds__(256) k1_dict_emit_tile_kernel(const u32 *__res
 #pragma unroll
 	for (u32 k = 0; k < 4; k++) {
 		const u32 c = w + 8 * k;
-		if ((ng >> c) & 1u) {
+		const u32 x = (u32) t * 32u + c;
+		if (((ng >> c) & 1u) && x >= x0 && x < x1) {
 			const u32 j = (u32) __popc(ng & ((1u << c) - 1u));
 			const u32 p = p0 + j;
 			const uint4 v = __ldg(info + sS[lane][j]);
 			const u32 sn = sN[lane][j];
 			sN[lane][j] = v.x; // the rank, for phase 3
 			if (v.z == 1) so.put(v.x, p);
-			else {
+			else if (v.y != U32_MAX) { // (peer mode: U32_MAX = another GPU sorts this bucket)
 				const u32 r2 = sn != U32_MAX ? __ldg(rank_of_slot + sn) : 0u;
 				const u32 q = v.y + sO[lane][j];
 				if (v.z < mid_min) { o.Slp[q] = p; o.Slr[q] = v.x; o.Sr2[q] = r2; }
@@ -1340,7 +1344,10 @@ __global__ void __launch_bounds__(256) k1_dict_emit_tile_kernel(const u32 *__res
 #pragma unroll
 	for (u32 k = 0; k < 4; k++) {
 		const u32 rr = w + 8 * k;
-		if (lane < (u32) __popc(sNG[rr])) __stcs(R + (u64) sP0[rr] + lane, sN[rr][lane]);
+		if (lane < (u32) __popc(sNG[rr])) {
+			const u32 x = (u32) t * 32u + __fns(sNG[rr], 0, (int) lane + 1); // the column of the row's lane-th character in this word
+			if (x >= x0 && x < x1) __stcs(R + (u64) sP0[rr] + lane, sN[rr][lane]);
+		}
 	}
 }
 // the '#' behind every row and the final sentinel (text-order code, m + 1 positions)
@@ -1353,6 +1360,7 @@ __global__ void k1_dict_emit_ends_kernel(const u32 *__restrict__ slot_of, const 
 	const uint4 v = __ldg(info + slot_of[p]);
 	R[p] = v.x;
 	if (v.z == 1) { so.put(v.x, (u32) p); return; }
+	if (v.y == U32_MAX) return;
 	const u64 pn = p + hnext;
 	const u32 r2 = pn < N ? __ldg(rank_of_slot + slot_of[pn]) : 0u;
 	const u32 q = v.y + ord_of[p];
@@ -1551,15 +1559,25 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 		u32 *own_a = d.alloc<u32>(p.m), *own_b = d.alloc<u32>(p.m);
 		k1_own_ranges_kernel<<<div_up(p.m, 256), 256, 0, d.stream>>>(p.RK, p.NG, p.start, p.rowlen, p.m, p.n, x0, x1, last, own_a, own_b);
 		const SaOut sao{p.SA, p.have_bwt ? p.BWT : nullptr, p.T};
-		const dim3 g1((u32) div_up((u64) (x1 - x0) + 2, 256), (u32) p.m); // a row has at most x1 - x0 characters in these columns (+ '#', + the sentinel)
-		k1_dict_emit_kernel<1><<<g1, 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, sao, o, pv->notmine, spans, own_a, own_b, sc + 6);
+		if (p.gaps != 0 && !getenv("FBG_EMIT_TEXT_ORDER")) { // tile order over this GPU's columns (a gapless text has no RK / NG tables)
+			const u32 xe = x1 < (u32) p.n ? x1 : (u32) p.n;
+			if (xe > x0) {
+				const u64 gt = div_up(p.m, 32) * (((u64) xe + 31) / 32 - x0 / 32);
+				if (gt > 0x7FFFFFFFull) throw unsupported_error("round 0: more than 2^31 tiles of 32 rows x 32 columns");
+				k1_dict_emit_tile_kernel<<<(u32) gt, 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, sao, o, p.RK, p.NG, p.start, p.m, x0 / 32, x0, xe);
+			}
+			if (last) k1_dict_emit_ends_kernel<<<div_up(p.m + 1, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, sao, o, p.start, p.rowlen, p.m);
+		} else {
+			const dim3 g1((u32) div_up((u64) (x1 - x0) + 2, 256), (u32) p.m); // a row has at most x1 - x0 characters in these columns (+ '#', + the sentinel)
+			k1_dict_emit_kernel<1><<<g1, 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, sao, o, pv->notmine, spans, own_a, own_b, sc + 6);
+		}
 		k1_dict_emit_kernel<2><<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, sao, o, pv->notmine, spans, own_a, own_b, sc + 6);
 		d.note_launches(K_DOUBLING_AUX, 2);
-	} else if (p.gaps != 0 && p.W <= 65535 && !getenv("FBG_EMIT_TEXT_ORDER")) {
+	} else if (p.gaps != 0 && div_up(p.m, 32) * p.W <= 0x7FFFFFFFull && !getenv("FBG_EMIT_TEXT_ORDER")) {
 		// (a gapless text has no RK / NG tables; FBG_EMIT_TEXT_ORDER=1: the text-order kernel, for comparison)
 		const SaOut sao{p.SA, p.have_bwt ? p.BWT : nullptr, p.T};
-		const dim3 gt((u32) div_up(p.m, 32), (u32) p.W);
-		k1_dict_emit_tile_kernel<<<gt, 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, sao, o, p.RK, p.NG, p.start, p.m);
+		const u32 gt = (u32) (div_up(p.m, 32) * p.W);
+		k1_dict_emit_tile_kernel<<<gt, 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, sao, o, p.RK, p.NG, p.start, p.m, 0u, 0u, (u32) p.n);
 		k1_dict_emit_ends_kernel<<<div_up(p.m + 1, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, sao, o, p.start, p.rowlen, p.m);
 		d.note_launches(K_DOUBLING_AUX, 1);
 	} else k1_dict_emit_kernel<0><<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, SaOut{p.SA, p.have_bwt ? p.BWT : nullptr, p.T}, o, nullptr, nullptr, nullptr, nullptr, nullptr);
