@@ -1280,6 +1280,117 @@ __global__ void __launch_bounds__(256) k1_dict_emit_kernel(const u32 *__restrict
 	else { o.Bkey[q] = ((u64) v.x << nbits) | r2; o.Bval[q] = (u32) p; }
 }
 
+// ---- the insert of MODE 4 in TILE order (texts with gaps: the RK / NG tables give the tiles).  In text order the 32
+// positions of a warp hold 32 different k-mers: 32 probes, 32 counter atomics, 32 minimum atomics into a 1 GB
+// table.  A CTA here takes 32 rows x the 32 columns of one bitmap word: the keys are built along the rows (text
+// staged per row, coalesced), then a warp takes a COLUMN -- its 32 rows mostly hold ONE k-mer: the lanes with equal
+// keys elect a leader (__match_any_sync), the leader alone probes the table, adds the size of its group to the
+// bucket's counter and folds its position (the smallest of the group: the lowest row) into the bucket's minimum; the
+// members take consecutive arrival numbers.  Slots and arrival numbers go back through shared memory and are
+// written along the rows.  '#' and the final sentinel: k1_kmer_ends_kernel.
+__device__ __forceinline__ u32 kd_insert(const KmerDict &dk, u64 key) {
+	u32 s = kd_hash(key) & dk.mask, probes = 0;
+	u64 c = __ldcg(dk.key + s);
+	for (;;) {
+		if (c == key) break;
+		if (c == KD_EMPTY) {
+			u64 prev = atomicCAS(reinterpret_cast<unsigned long long *>(dk.key + s), (unsigned long long) KD_EMPTY, (unsigned long long) key);
+			if (prev == KD_EMPTY || prev == key) break;
+		}
+		s = (s + 1) & dk.mask;
+		if (++probes > KD_MAX_PROBES) { *dk.overflow = 1u; return U32_MAX; }
+		c = __ldcg(dk.key + s);
+	}
+	return s;
+}
+__global__ void __launch_bounds__(256) k1_kmer_tile_kernel(const u8 *__restrict__ T, u64 N, CodeTable tab, int K, int b, KmerDict dk,
+                                                           const u32 *__restrict__ RK, const u32 *__restrict__ NG, const u32 *__restrict__ start, u64 m, u64 W) {
+	__shared__ u64 sK[32][33];
+	__shared__ u32 sS[32][33], sO[32][33];
+	__shared__ u8 sT[32][64]; // the codes of a row's 32 + K - 1 <= 63 characters from its first position in this word
+	__shared__ u8 stab[256];
+	__shared__ u32 sNG[32], sP0[32], s_stop;
+	const u32 w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	// Blocks run word-fastest: a row group is (nearly) done before the next one starts, so the arrival numbers of a bucket
+	// grow with the row as they do with the text-order insert.  (Row-group-fastest made the order of the 32-row groups
+	// inside a bucket random; compaction and bucket sort of every later round then ran 10-20 % slower: neighbouring buckets
+	// no longer ask for the ranks of a row at about the same time.)
+	const u32 nwords = (u32) W;
+	const u64 i0 = (u64) (blockIdx.x / nwords) * 32, t = blockIdx.x % nwords;
+	stab[threadIdx.x] = tab.code[threadIdx.x];
+	if (threadIdx.x == 0) s_stop = *reinterpret_cast<volatile u32 *>(dk.overflow);
+	if (threadIdx.x < 32) {
+		const u64 i = i0 + threadIdx.x;
+		sNG[threadIdx.x] = i < m ? NG[t * m + i] : 0u;
+		sP0[threadIdx.x] = i < m ? start[i] + RK[t * m + i] : 0u;
+	}
+	__syncthreads();
+	if (s_stop) return; // the table overflowed: the caller falls back
+	const u64 kmask = (K * b >= 64) ? ~0ull : ((1ull << (K * b)) - 1ull);
+	// phase 1: rows -- text codes, then one key per position
+#pragma unroll
+	for (u32 k = 0; k < 4; k++) {
+		const u32 rr = w + 8 * k;
+		const u32 cnt = (u32) __popc(sNG[rr]);
+		if (cnt) { // (uniform over the warp)
+			const u64 g0 = (u64) sP0[rr] + lane, g1 = g0 + 32;
+			sT[rr][lane] = g0 < N ? stab[T[g0]] : (u8) 0;
+			sT[rr][lane + 32] = g1 < N ? stab[T[g1]] : (u8) 0;
+			__syncwarp();
+			if (lane < cnt) {
+				u64 key = 0;
+				for (int c = 0; c < K; c++) key = (key << b) | sT[rr][lane + c];
+				sK[rr][lane] = key & kmask;
+			}
+		}
+	}
+	__syncthreads();
+	// phase 2: columns (lane = row)
+	const u32 ng = sNG[lane], p0 = sP0[lane];
+#pragma unroll
+	for (u32 k = 0; k < 4; k++) {
+		const u32 c = w + 8 * k;
+		const bool act = (ng >> c) & 1u;
+		const u32 am = __ballot_sync(0xffffffffu, act);
+		if (act) {
+			const u32 j = (u32) __popc(ng & ((1u << c) - 1u));
+			const u64 key = sK[lane][j];
+			const u32 grp = __match_any_sync(am, key);
+			const int leader = __ffs(grp) - 1;
+			u32 sl = 0, base = 0;
+			if ((int) lane == leader) {
+				sl = kd_insert(dk, key);
+				if (sl != U32_MAX) { base = atomicAdd(dk.cnt + sl, (u32) __popc(grp)); atomicMin(dk.first + sl, p0 + j); }
+			}
+			sl = __shfl_sync(grp, sl, leader); base = __shfl_sync(grp, base, leader);
+			sS[lane][j] = sl; sO[lane][j] = base + (u32) __popc(grp & lanemask_lt());
+		}
+	}
+	__syncthreads();
+	// phase 3: rows
+#pragma unroll
+	for (u32 k = 0; k < 4; k++) {
+		const u32 rr = w + 8 * k;
+		if (lane < (u32) __popc(sNG[rr])) {
+			const u64 p = (u64) sP0[rr] + lane;
+			__stcs(dk.slot_of + p, sS[rr][lane]); __stcs(dk.ord_of + p, sO[rr][lane]);
+		}
+	}
+}
+__global__ void k1_kmer_ends_kernel(const u8 *__restrict__ T, u64 N, CodeTable tab, int K, int b, KmerDict dk, const u32 *__restrict__ start, const u32 *__restrict__ rowlen, u64 m) {
+	const u64 i = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i > m) return;
+	const u64 p = i < m ? (u64) start[i] + rowlen[i] : N - 1;
+	const u64 kmask = (K * b >= 64) ? ~0ull : ((1ull << (K * b)) - 1ull);
+	u64 key = 0;
+	for (int c = 0; c < K; c++) key = (key << b) | (p + c < N ? tab.code[T[p + c]] : (u8) 0);
+	key &= kmask;
+	const u32 sl = kd_insert(dk, key);
+	if (sl == U32_MAX) return;
+	dk.slot_of[p] = sl; dk.ord_of[p] = atomicAdd(dk.cnt + sl, 1u);
+	atomicMin(dk.first + sl, (u32) p);
+}
+
 // ---- the same emission in TILE order (one GPU): a CTA takes 32 rows x the 32 columns of one bitmap word.
 // In text order a warp's 32 positions belong to 32 different buckets: 32 sectors of info[], 32 of rank_of_slot[] and
 // 3 x 32 of the lists per warp instruction -- ncu: 38 GB of DRAM traffic for 14 GB of algorithmic bytes, L2-bound.
@@ -1462,7 +1573,10 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	FBG_CUDA(cudaMemsetAsync(dk.first, 0xFF, (u64) cap * sizeof(u32), d.stream));
 	KmerShard sh;
 	sh.bin_lo = 0; sh.bin_hi = 0; sh.hshift = 0; sh.block_off = nullptr; sh.hist = nullptr; sh.block_cnt = nullptr;
-	k1_kmer_kernel<4><<<km_grid, KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, sh, nullptr, nullptr, dk);
+	if (p.gaps != 0 && p.RK && p.NG && div_up(p.m, 32) * p.W <= 0x7FFFFFFFull && !getenv("FBG_KMER_TEXT_ORDER")) { // FBG_KMER_TEXT_ORDER=1: the text-order insert, for comparison
+		k1_kmer_tile_kernel<<<(u32) (div_up(p.m, 32) * p.W), 256, 0, d.stream>>>(p.T, N, tab, K, b, dk, p.RK, p.NG, p.start, p.m, p.W);
+		k1_kmer_ends_kernel<<<div_up(p.m + 1, 256), 256, 0, d.stream>>>(p.T, N, tab, K, b, dk, p.start, p.rowlen, p.m);
+	} else k1_kmer_kernel<4><<<km_grid, KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, sh, nullptr, nullptr, dk);
 	FBG_LAUNCH_CHECK();
 	d.end((double) N * (1.0 + 8.0 + 8.0));
 	d.begin(K_DOUBLING_AUX);
@@ -1559,7 +1673,7 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 		u32 *own_a = d.alloc<u32>(p.m), *own_b = d.alloc<u32>(p.m);
 		k1_own_ranges_kernel<<<div_up(p.m, 256), 256, 0, d.stream>>>(p.RK, p.NG, p.start, p.rowlen, p.m, p.n, x0, x1, last, own_a, own_b);
 		const SaOut sao{p.SA, p.have_bwt ? p.BWT : nullptr, p.T};
-		if (p.gaps != 0 && !getenv("FBG_EMIT_TEXT_ORDER")) { // tile order over this GPU's columns (a gapless text has no RK / NG tables)
+		if (p.gaps != 0 && p.RK && p.NG && !getenv("FBG_EMIT_TEXT_ORDER")) { // tile order over this GPU's columns (a gapless text has no RK / NG tables)
 			const u32 xe = x1 < (u32) p.n ? x1 : (u32) p.n;
 			if (xe > x0) {
 				const u64 gt = div_up(p.m, 32) * (((u64) xe + 31) / 32 - x0 / 32);
@@ -1573,7 +1687,7 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 		}
 		k1_dict_emit_kernel<2><<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, sao, o, pv->notmine, spans, own_a, own_b, sc + 6);
 		d.note_launches(K_DOUBLING_AUX, 2);
-	} else if (p.gaps != 0 && div_up(p.m, 32) * p.W <= 0x7FFFFFFFull && !getenv("FBG_EMIT_TEXT_ORDER")) {
+	} else if (p.gaps != 0 && p.RK && p.NG && div_up(p.m, 32) * p.W <= 0x7FFFFFFFull && !getenv("FBG_EMIT_TEXT_ORDER")) {
 		// (a gapless text has no RK / NG tables; FBG_EMIT_TEXT_ORDER=1: the text-order kernel, for comparison)
 		const SaOut sao{p.SA, p.have_bwt ? p.BWT : nullptr, p.T};
 		const u32 gt = (u32) (div_up(p.m, 32) * p.W);
