@@ -1654,7 +1654,7 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	device_scan<OpSumU32, true>(d, zm, zm, nd, sc + 5);
 	if (pv) {
 		// the lists were sized for this GPU's share of the columns: check before anything is written into them
-		FBG_CUDA(cudaMemcpyAsync(h_sc, sc, 6 * sizeof(u32), cudaMemcpyDeviceToHost, d.stream));
+		FBG_CUDA(cudaMemcpyAsync(h_sc, sc, 7 * sizeof(u32), cudaMemcpyDeviceToHost, d.stream)); // [6]: buckets that span GPUs
 		FBG_CUDA(cudaStreamSynchronize(d.stream));
 		// (all GPUs decide alike: the build changes form if any of them is short of room)
 		p.h_scalars[63] = ((u64) h_sc[2] + h_sc[5] + h_sc[3] > list_cap) ? 1 : 0;
@@ -1685,7 +1685,8 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 			const dim3 g1((u32) div_up((u64) (x1 - x0) + 2, 256), (u32) p.m); // a row has at most x1 - x0 characters in these columns (+ '#', + the sentinel)
 			k1_dict_emit_kernel<1><<<g1, 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, sao, o, pv->notmine, spans, own_a, own_b, sc + 6);
 		}
-		k1_dict_emit_kernel<2><<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, sao, o, pv->notmine, spans, own_a, own_b, sc + 6);
+		// (nothing to do -- the usual case -- costs 2 ms of empty blocks at 5e8 positions: not launched then)
+		if (h_sc[6]) k1_dict_emit_kernel<2><<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, ord_of, info, rank_of_slot, N, hnext, nbits, mid_min, p.ISA, sao, o, pv->notmine, spans, own_a, own_b, sc + 6);
 		d.note_launches(K_DOUBLING_AUX, 2);
 	} else if (p.gaps != 0 && p.RK && p.NG && div_up(p.m, 32) * p.W <= 0x7FFFFFFFull && !getenv("FBG_EMIT_TEXT_ORDER")) {
 		// (a gapless text has no RK / NG tables; FBG_EMIT_TEXT_ORDER=1: the text-order kernel, for comparison)
