@@ -1165,23 +1165,23 @@ __global__ void k1_owner_table_kernel(u32 ncols, PeerView pv, u8 *__restrict__ o
 	u32 c = blockIdx.x * blockDim.x + threadIdx.x;
 	if (c < ncols) ownc[c] = (u8) pv.owner(c);
 }
-__global__ void k1_dict_own1_kernel(const u32 *__restrict__ lv, const u32 *__restrict__ first, const u32 *__restrict__ col, const u8 *__restrict__ ownc, u32 nd, u8 *__restrict__ own1) {
+__global__ void k1_dict_own1_kernel(const u32 *__restrict__ lv, const u32 *__restrict__ first, const u32 *__restrict__ col, const u8 *__restrict__ ownc, u32 nd, u32 *__restrict__ own1) {
 	u32 t = blockIdx.x * blockDim.x + threadIdx.x;
 	if (t >= nd) return;
 	const u32 s = lv[t];
 	own1[s] = ownc[col[first[s]]];
 }
-__global__ void k1_dict_spans_kernel(const u32 *__restrict__ slot_of, const u32 *__restrict__ col, const u8 *__restrict__ ownc, const u8 *__restrict__ own1, u64 N, u8 *__restrict__ spans) {
+__global__ void k1_dict_spans_kernel(const u32 *__restrict__ slot_of, const u32 *__restrict__ col, const u8 *__restrict__ ownc, const u32 *__restrict__ own1, u64 N, u8 *__restrict__ spans) {
 	u64 p = (u64) blockIdx.x * blockDim.x + threadIdx.x;
 	if (p >= N) return;
 	const u32 s = __ldcs(slot_of + p);
 	if (__ldg(ownc + __ldcs(col + p)) != __ldg(own1 + s)) spans[s] = 1;
 }
-__global__ void k1_dict_mine_kernel(const u32 *__restrict__ lv, const u8 *__restrict__ own1, const u8 *__restrict__ spans, u32 nd, int me, u8 *__restrict__ mine, u32 *__restrict__ nspan) {
+__global__ void k1_dict_mine_kernel(const u32 *__restrict__ lv, const u32 *__restrict__ own1, const u8 *__restrict__ spans, u32 nd, int me, u8 *__restrict__ mine, u32 *__restrict__ nspan) {
 	u32 t = blockIdx.x * blockDim.x + threadIdx.x;
 	if (t >= nd) return;
 	const u32 s = lv[t];
-	mine[t] = (spans[s] || own1[s] == (u8) me) ? 1 : 0;
+	mine[t] = (spans[s] || own1[s] == (u32) me) ? 1 : 0;
 	if (spans[s]) atomicAdd(nspan, 1u);
 }
 // bucket sizes in k-mer order: all of them (their exclusive scan = the ranks) and the big ones (B list offsets);
@@ -1304,7 +1304,10 @@ __device__ __forceinline__ u32 kd_insert(const KmerDict &dk, u64 key) {
 	return s;
 }
 __global__ void __launch_bounds__(256) k1_kmer_tile_kernel(const u8 *__restrict__ T, u64 N, CodeTable tab, int K, int b, KmerDict dk,
-                                                           const u32 *__restrict__ RK, const u32 *__restrict__ NG, const u32 *__restrict__ start, u64 m, u64 W) {
+                                                           const u32 *__restrict__ RK, const u32 *__restrict__ NG, const u32 *__restrict__ start, u64 m, u64 W,
+                                                           const u8 *__restrict__ ownc, u32 *__restrict__ own1, u8 *__restrict__ spans) {
+	// peer mode (ownc != null): the leader also leaves the GPU that owns its column with the bucket (first come) and
+	// raises spans[slot] when the bucket already belongs to another GPU -- the N-wide span test for free
 	__shared__ u64 sK[32][33];
 	__shared__ u32 sS[32][33], sO[32][33];
 	__shared__ u8 sT[32][64]; // the codes of a row's 32 + K - 1 <= 63 characters from its first position in this word
@@ -1360,7 +1363,14 @@ __global__ void __launch_bounds__(256) k1_kmer_tile_kernel(const u8 *__restrict_
 			u32 sl = 0, base = 0;
 			if ((int) lane == leader) {
 				sl = kd_insert(dk, key);
-				if (sl != U32_MAX) { base = atomicAdd(dk.cnt + sl, (u32) __popc(grp)); atomicMin(dk.first + sl, p0 + j); }
+				if (sl != U32_MAX) {
+					base = atomicAdd(dk.cnt + sl, (u32) __popc(grp)); atomicMin(dk.first + sl, p0 + j);
+					if (ownc) {
+						const u32 ow = ownc[(u32) t * 32u + c];
+						const u32 prev = atomicCAS(own1 + sl, U32_MAX, ow);
+						if (prev != U32_MAX && prev != ow) spans[sl] = 1;
+					}
+				}
 			}
 			sl = __shfl_sync(grp, sl, leader); base = __shfl_sync(grp, base, leader);
 			sS[lane][j] = sl; sO[lane][j] = base + (u32) __popc(grp & lanemask_lt());
@@ -1377,7 +1387,8 @@ __global__ void __launch_bounds__(256) k1_kmer_tile_kernel(const u8 *__restrict_
 		}
 	}
 }
-__global__ void k1_kmer_ends_kernel(const u8 *__restrict__ T, u64 N, CodeTable tab, int K, int b, KmerDict dk, const u32 *__restrict__ start, const u32 *__restrict__ rowlen, u64 m) {
+__global__ void k1_kmer_ends_kernel(const u8 *__restrict__ T, u64 N, CodeTable tab, int K, int b, KmerDict dk, const u32 *__restrict__ start, const u32 *__restrict__ rowlen, u64 m,
+                                    u32 ncols, const u8 *__restrict__ ownc, u32 *__restrict__ own1, u8 *__restrict__ spans) {
 	const u64 i = (u64) blockIdx.x * blockDim.x + threadIdx.x;
 	if (i > m) return;
 	const u64 p = i < m ? (u64) start[i] + rowlen[i] : N - 1;
@@ -1389,6 +1400,11 @@ __global__ void k1_kmer_ends_kernel(const u8 *__restrict__ T, u64 N, CodeTable t
 	if (sl == U32_MAX) return;
 	dk.slot_of[p] = sl; dk.ord_of[p] = atomicAdd(dk.cnt + sl, 1u);
 	atomicMin(dk.first + sl, (u32) p);
+	if (ownc) { // '#' has column n, the sentinel n + 1
+		const u32 ow = ownc[i < m ? ncols : ncols + 1u];
+		const u32 prev = atomicCAS(own1 + sl, U32_MAX, ow);
+		if (prev != U32_MAX && prev != ow) spans[sl] = 1;
+	}
 }
 
 // ---- the same emission in TILE order (one GPU): a CTA takes 32 rows x the 32 columns of one bitmap word.
@@ -1487,7 +1503,7 @@ static u32 dict_capacity(u64 N) {
 }
 static u64 dict_scratch_bytes(u64 N) {
 	u64 cap = dict_capacity(N);
-	return cap * (8 + 4 + 4 + 16 + 4 + 1 + 1) + (cap / 2) * (16 + 8 + 8 + 16 + 8 + 1) + (cap / SCAN_TILE + 2) * 24 + (cap / 2 / RS_TILE + 2) * RS_BINS * 12 + (1u << 16) + N + (1u << 12);
+	return cap * (8 + 4 + 4 + 16 + 4 + 1 + 4) + (cap / 2) * (16 + 8 + 8 + 16 + 8 + 1) + (cap / SCAN_TILE + 2) * 24 + (cap / 2 / RS_TILE + 2) * RS_BINS * 12 + (1u << 16) + N + (1u << 12);
 }
 
 // Returns false (nothing written that matters) when the text has too many distinct k-mers for
@@ -1573,9 +1589,19 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	FBG_CUDA(cudaMemsetAsync(dk.first, 0xFF, (u64) cap * sizeof(u32), d.stream));
 	KmerShard sh;
 	sh.bin_lo = 0; sh.bin_hi = 0; sh.hshift = 0; sh.block_off = nullptr; sh.hist = nullptr; sh.block_cnt = nullptr;
+	u8 *spans = nullptr, *ownc = nullptr;
+	u32 *own1 = nullptr;
+	bool spans_done = false;
+	if (pv) { // peer mode: which GPU a bucket belongs to, which buckets span GPUs (k1_dict_mine_kernel below)
+		spans = d.alloc<u8>(cap); own1 = d.alloc<u32>(cap); ownc = d.alloc<u8>(p.n + 2);
+		FBG_CUDA(cudaMemsetAsync(spans, 0, cap, d.stream));
+		FBG_CUDA(cudaMemsetAsync(own1, 0xFF, (u64) cap * sizeof(u32), d.stream));
+		k1_owner_table_kernel<<<div_up(p.n + 2, 256), 256, 0, d.stream>>>((u32) p.n + 2u, *pv, ownc);
+	}
 	if (p.gaps != 0 && p.RK && p.NG && div_up(p.m, 32) * p.W <= 0x7FFFFFFFull && !getenv("FBG_KMER_TEXT_ORDER")) { // FBG_KMER_TEXT_ORDER=1: the text-order insert, for comparison
-		k1_kmer_tile_kernel<<<(u32) (div_up(p.m, 32) * p.W), 256, 0, d.stream>>>(p.T, N, tab, K, b, dk, p.RK, p.NG, p.start, p.m, p.W);
-		k1_kmer_ends_kernel<<<div_up(p.m + 1, 256), 256, 0, d.stream>>>(p.T, N, tab, K, b, dk, p.start, p.rowlen, p.m);
+		k1_kmer_tile_kernel<<<(u32) (div_up(p.m, 32) * p.W), 256, 0, d.stream>>>(p.T, N, tab, K, b, dk, p.RK, p.NG, p.start, p.m, p.W, ownc, own1, spans);
+		k1_kmer_ends_kernel<<<div_up(p.m + 1, 256), 256, 0, d.stream>>>(p.T, N, tab, K, b, dk, p.start, p.rowlen, p.m, (u32) p.n, ownc, own1, spans);
+		spans_done = pv != nullptr;
 	} else k1_kmer_kernel<4><<<km_grid, KM_THREADS, 0, d.stream>>>(p.T, N, tab, K, b, sh, nullptr, nullptr, dk);
 	FBG_LAUNCH_CHECK();
 	d.end((double) N * (1.0 + 8.0 + 8.0));
@@ -1595,16 +1621,14 @@ static bool k1_round0_dict(Pipeline &p, const CodeTable &tab, int K, int b, int 
 	const int cur = radix_sort<u64, true>(d, lb, nd, 0, key_bits0);
 	const u32 *lv = lb.v[cur];
 	const u32 gn = div_up(nd, 256);
-	u8 *mine = nullptr, *spans = nullptr;
+	u8 *mine = nullptr;
 	if (pv) {
-		spans = d.alloc<u8>(cap);
 		mine = d.alloc<u8>(ndmax);
-		u8 *own1 = d.alloc<u8>(cap), *ownc = d.alloc<u8>(p.n + 2);
-		FBG_CUDA(cudaMemsetAsync(spans, 0, cap, d.stream));
 		d.begin(K_DOUBLING_AUX);
-		k1_owner_table_kernel<<<div_up(p.n + 2, 256), 256, 0, d.stream>>>((u32) p.n + 2u, *pv, ownc);
-		k1_dict_own1_kernel<<<gn, 256, 0, d.stream>>>(lv, dk.first, p.col, ownc, nd, own1);
-		k1_dict_spans_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, p.col, ownc, own1, N, spans);
+		if (!spans_done) { // (the text-order insert does not look at owners)
+			k1_dict_own1_kernel<<<gn, 256, 0, d.stream>>>(lv, dk.first, p.col, ownc, nd, own1);
+			k1_dict_spans_kernel<<<div_up(N, 256), 256, 0, d.stream>>>(slot_of, p.col, ownc, own1, N, spans);
+		}
 		k1_dict_mine_kernel<<<gn, 256, 0, d.stream>>>(lv, own1, spans, nd, pv->me, mine, sc + 6);
 		FBG_LAUNCH_CHECK();
 		d.end((double) N * 8.0 + (double) nd * 13.0);
