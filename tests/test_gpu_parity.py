@@ -3,6 +3,7 @@
   * the CPU oracle (oracle/fbg_oracle.c) on seeded inputs,
   * size-independent properties at larger sizes.
 Integer work throughout: every comparison is bit-exact."""
+import hashlib
 import os
 
 import numpy as np
@@ -600,3 +601,31 @@ def test_context_usable_after_a_failed_stage(gpu_ctx, monkeypatch):
         f1 = gpu_ctx.compute_f()
         b1, s1 = gpu_ctx.segment()
         assert np.array_equal(f0, f1) and np.array_equal(b0, b1) and s0 == s1
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("switch", ["FBG_KMER_TEXT_ORDER", "FBG_EMIT_TEXT_ORDER", "FBG_FCOL_NO_STAGE", "FBG_LCP_FLAGS", "FBG_FCOL_SORT"])
+def test_older_kernel_forms_give_the_same_result(gpu_ctx, switch, monkeypatch):
+    """The comparison switches of INTEGRATION.md select the form a kernel had before it was rewritten (round 0 in text
+    order, f(x) kernels gathering for themselves, irreducible ranks through a flag array, f(x) by sorting): index, f,
+    boundaries and xGFA bytes must not depend on them (gapped inputs; gapless ones take the older forms anyway)."""
+    for name, scale, seed in (("cfg3", 0.004, 41), ("cfg4", 0.0008, 42)):
+        msa, c = synth.make_config(name, scale, seed=seed)
+        outs = []
+        for on in (False, True):
+            if on:
+                monkeypatch.setenv(switch, "1")
+            else:
+                monkeypatch.delenv(switch, raising=False)
+            gpu_ctx.set_options(elastic=True, gap_limit=1, ignore_chars=c["ignore"])
+            gpu_ctx.upload(msa)
+            gpu_ctx.build_index()
+            sa, isa, lcp = gpu_ctx.sa().copy(), gpu_ctx.isa().copy(), gpu_ctx.lcp().copy()
+            f = gpu_ctx.compute_f().copy()
+            b, score = gpu_ctx.segment()
+            info = gpu_ctx.format_xgfa(None)
+            outs.append((sa, isa, lcp, f, np.asarray(b).copy(), score, hashlib.sha256(gpu_ctx.read_xgfa(0, info["n_bytes"])).hexdigest()))
+        monkeypatch.delenv(switch, raising=False)
+        for x, y in zip(outs[0][:5], outs[1][:5]):
+            assert np.array_equal(x, y)
+        assert outs[0][5:] == outs[1][5:]
