@@ -13,7 +13,11 @@
  * no exceptions across the boundary, int status (0 = FBG_OK, < 0 = error with text
  * in fbg_last_error()).  One context per host thread; calls on one context are
  * serialised by the caller.  There is NO CPU fallback: every compute entry point
- * fails with FBG_ERR_CUDA when no sm_100 device is usable.
+ * fails with FBG_ERR_CUDA when no sm_100 device is usable.  A call that returns an
+ * error leaves the context usable: its device work has been waited for and its
+ * scratch memory released; what the failed stage was producing is absent, the
+ * uploaded MSA and the options stay (tests/test_gpu_parity.py,
+ * test_context_usable_after_a_failed_stage).
  */
 #ifndef FBG_CUDA_H
 #define FBG_CUDA_H
