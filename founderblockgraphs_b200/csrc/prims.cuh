@@ -127,8 +127,8 @@ struct OpMax2x32 {
 	}
 };
 
-constexpr int SCAN_THREADS = 256;
-constexpr int SCAN_ITEMS = 16;
+constexpr int SCAN_THREADS = 512;
+constexpr int SCAN_ITEMS = 32;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 
 template <class Op> __device__ __forceinline__ typename Op::T warp_incl_scan(typename Op::T v) {
